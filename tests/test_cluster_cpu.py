@@ -1,0 +1,106 @@
+"""Config 2: 1 ps + 2 workers as three OS processes on CPU/gloo, launched like m / w1 / w2."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from tensorflow_distributed_b200 import checkpoint, data
+from tensorflow_distributed_b200.models.spec import make_spec
+from tensorflow_distributed_b200.ops import oracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _launch(script, port, extra, env_extra=None):
+    args = [sys.executable, os.path.join(ROOT, script), "--ps_hosts=127.0.0.1:%d" % port,
+            "--worker_hosts=127.0.0.1:%d,127.0.0.1:%d" % (port + 1, port + 2), "--backend=cpu",
+            "--step_timeout_secs=90"] + extra
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2")
+    env.update(env_extra or {})
+    return subprocess.Popen(args, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, cwd=ROOT)
+
+
+def _run3(port, extra, timeout=240):
+    procs = [_launch(s, port, extra) for s in ("mnist_python_m.py", "mnist_python_w1.py", "mnist_python_w2.py")]
+    outs = []
+    for p in procs:
+        try:
+            o, _ = p.communicate(timeout=timeout)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        outs.append(o)
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+    return outs
+
+
+@pytest.mark.timeout(300)
+def test_sync_two_workers_equals_large_batch_single_process(tmp_path, free_port):
+    steps = 3
+    extra = ["--model=mlp", "--hidden_units=32", "--init_stddev=0.1", "--train_steps=%d" % steps, "--keep_prob=1.0",
+             "--sync_init_tokens=0", "--batch_size=64", "--validation_batch_size=200", "--train_dir=%s" % tmp_path,
+             "--log_device_placement"]
+    ps_out, w1_out, w2_out = _run3(free_port, extra)
+    # log lines of the reference
+    assert "job name = ps" in ps_out and "task index = 0" in ps_out
+    assert "Worker 0: Initializing session..." in w1_out
+    assert "Worker 1: Waiting for session to be initialized..." in w2_out
+    for o, t in ((w1_out, 0), (w2_out, 1)):
+        assert "Worker %d: Session initialization complete." % t in o
+        assert "Training begins @" in o and "Training elapsed time:" in o and "Mean Accuracy :" in o
+        assert o.count(": training step") == steps
+        assert "training step %d done (global step: %d)" % (steps, steps) in o
+    assert "weights/h1" in w1_out  # placement table
+    # oracle: one process, both workers' batches, averaged gradient, one TF-Adam apply per global step
+    spec = make_spec("mlp", 32, 1)
+    p = oracle.init_params(spec, 0, 0.1)
+    adam = oracle.TFAdam(0.01)
+    streams = [data.read_data_sets("", synthetic=True, seed=101 * w).train for w in range(2)]
+    for _ in range(steps):
+        gs = []
+        for s in streams:
+            x, y = s.next_batch(64)
+            _, g, _ = oracle.loss_and_grads("mlp", torch.from_numpy(x), torch.from_numpy(y), p)
+            gs.append(g)
+        adam.apply(p, {k: (gs[0][k] + gs[1][k]) / 2 for k in p})
+    blob = checkpoint.load(checkpoint.latest_checkpoint(str(tmp_path)), spec)
+    assert blob["global_step"] == steps and blob["adam"]["t"] == steps
+    for k in p:
+        assert torch.allclose(blob["variables"][k], p[k], atol=1e-6), k
+
+
+@pytest.mark.timeout(300)
+def test_async_two_workers_counts_every_update(free_port):
+    steps = 6
+    extra = ["--model=mlp", "--hidden_units=16", "--init_stddev=0.1", "--train_steps=%d" % steps,
+             "--sync_replicas=False", "--batch_size=32", "--validation_batch_size=100"]
+    ps_out, w1_out, w2_out = _run3(free_port, extra)
+    n = w1_out.count(": training step") + w2_out.count(": training step")
+    # global_step counts worker updates (m:301): total applies >= train_steps, and nobody waits for anybody
+    assert n >= steps
+    assert "global step: %d" % n in (w1_out + w2_out) or n > steps
+
+
+@pytest.mark.timeout(300)
+def test_cnn_default_tokens_two_ps_shards(free_port):
+    """The reference's CNN with TF's default token preload, wd1 split across two ps tasks."""
+    port = free_port
+    common = ["--ps_hosts=127.0.0.1:%d,127.0.0.1:%d" % (port, port + 3), "--train_steps=2", "--batch_size=16",
+              "--validation_batch_size=50", "--validation_batches=1"]
+    scripts = [("mnist_python_m.py", []), ("mnist_python_m.py", ["--task_index=1"]),
+               ("mnist_python_w1.py", []), ("mnist_python_w2.py", [])]
+    procs = []
+    for s, e in scripts:
+        args = [sys.executable, os.path.join(ROOT, s), "--worker_hosts=127.0.0.1:%d,127.0.0.1:%d" % (port + 1, port + 2),
+                "--backend=cpu", "--step_timeout_secs=90"] + common + e
+        procs.append(subprocess.Popen(args, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                                      env=dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2"), cwd=ROOT))
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+    assert "Mean Accuracy :" in outs[2] and "Mean Accuracy :" in outs[3]
