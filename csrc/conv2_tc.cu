@@ -1,0 +1,382 @@
+// conv2 (5x5, SAME, 32 -> 64 on 14x14 maps) on tcgen05: forward, data gradient and filter gradient as
+// implicit GEMMs.  Replaces tf.nn.conv2d + bias_add + relu + max_pool of /root/reference/mnist_python_m.py:
+// 93-101,114-116 and the conv gradients TF's autodiff generates at m:222.
+//
+// im2col never touches memory: for filter tap (kh,kw) the A tile of 128 output pixels is ONE 4-D TMA box
+// {C, 16 w, 2 h, 4 n} of the NHWC activation, shifted by (kh-2, kw-2); TMA zero-fills everything outside the
+// image, which is exactly SAME padding.  The box is 16 wide on a 14-wide map, so 2 of 16 accumulator rows per
+// image row are padding (never stored); in exchange a 2x2 pooling window lives inside one warp's 32 TMEM lanes
+// (lane = hh*16 + ww) and the pool is two shuffles.  The whole bf16 filter (100 KB) stays resident in shared
+// memory; CTAs are persistent over pixel tiles with double-buffered TMEM accumulators.
+#include "../include/tfd_b200.h"
+#include "tfd_common.cuh"
+
+namespace {
+
+using namespace tfd;
+typedef __nv_bfloat16 bf16;
+
+constexpr int kThreads = 192;
+constexpr int kFilterBytes = 25 * 4096;  // [800][64] bf16
+
+__device__ __forceinline__ void load_filter(uint8_t* filt, const CUtensorMap* tmW, uint64_t* bar) {
+  mbar_arrive_expect_tx(bar, kFilterBytes);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) tma_load_2d(filt + i * 25600, tmW, bar, 0, i * 200);
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward / dgrad share one kernel shape.  kFwd: A = in [B,14,14,32] (64 B rows, SW64), N = 64, fused
+// bias+ReLU+pool epilogue.  !kFwd: A = dy [B,14,14,64] (128 B rows, SW128), N = 32, fp32 store epilogue.
+// ------------------------------------------------------------------------------------------------
+template <bool kFwd>
+struct ConvCfg {
+  static constexpr int kABytes = kFwd ? 8192 : 16384;
+  static constexpr int kStages = kFwd ? 8 : 6;
+  static constexpr int kN = kFwd ? 64 : 32;
+  static constexpr int kKSteps = kFwd ? 2 : 4;  // UMMA K=16 steps per tap
+  static constexpr int kSmem = kFilterBytes + kStages * kABytes + 1024 + 512;
+};
+
+template <bool kFwd>
+__global__ void __launch_bounds__(kThreads, 1)
+conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                const float* __restrict__ bias, bf16* __restrict__ pool_out, unsigned char* __restrict__ amax,
+                float* __restrict__ dx, int B, int num_tiles) {
+  using C = ConvCfg<kFwd>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* filt = smem;
+  uint8_t* abuf = smem + kFilterBytes;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(abuf + C::kStages * C::kABytes);
+  uint64_t* a_empty = a_full + C::kStages;
+  uint64_t* filt_full = a_empty + C::kStages;
+  uint64_t* acc_full = filt_full + 1;   // [2]
+  uint64_t* acc_empty = acc_full + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmW);
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    mbar_init(filt_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+    fence_barrier_init();
+    fence_proxy_async_smem();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * C::kN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      load_filter(filt, &tmW, filt_full);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int nb = tile / 7, hp = tile % 7;
+        for (int tap = 0; tap < 25; ++tap) {
+          const int kh = tap / 5, kw = tap % 5;
+          mbar_wait(&a_empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&a_full[stage], C::kABytes);
+          const int w0 = kFwd ? kw - 2 : 2 - kw;
+          const int h0 = kFwd ? 2 * hp + kh - 2 : 2 * hp + 2 - kh;
+          tma_load_4d(abuf + stage * C::kABytes, &tmA, &a_full[stage], 0, w0, h0, nb * 4);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, C::kN, 0, kFwd ? 1 : 0);
+      mbar_wait(filt_full, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * C::kN;
+        for (int tap = 0; tap < 25; ++tap) {
+          mbar_wait(&a_full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(abuf + stage * C::kABytes);
+          const uint32_t sw = smem_u32(filt + tap * 4096);
+#pragma unroll
+          for (int ks = 0; ks < C::kKSteps; ++ks) {
+            uint64_t da, db;
+            if (kFwd) {
+              da = make_smem_desc(sa + ks * 32, 16, 512, kSwz64);         // [128 px][32 ci]  K-major, 64 B rows
+              db = make_smem_desc(sw + ks * 2048, 4096, 1024, kSwz128);   // [32 ci][64 co]   MN-major (co contiguous)
+            } else {
+              da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);       // [128 px][64 co]  K-major, 128 B rows
+              db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);       // [32 ci][64 co]   K-major  (co = K)
+            }
+            umma_bf16(tacc, da, db, idesc, (tap > 0 || ks > 0) ? 1u : 0u);
+          }
+          umma_commit(&a_empty[stage]);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    const int q = warp & 3;  // image inside the tile; also the TMEM lane quadrant
+    const int hh = lane >> 4, ww = lane & 15;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const int nb = tile / 7, hp = tile % 7;
+      const int n = nb * 4 + q;
+      mbar_wait(&acc_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + buf * C::kN + ((uint32_t)(q * 32) << 16);
+      if (kFwd) {
+        const int self = hh * 2 + (ww & 1);
+#pragma unroll 1
+        for (int j = 0; j < 4; ++j) {
+          float v[16];
+          tmem_ld16(tacc + j * 16, v);
+          uint32_t packed[8];
+          uint32_t am[4] = {0, 0, 0, 0};
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float x = fmaxf(v[i] + __ldg(bias + j * 16 + i), 0.f);
+            int xi = self;
+            float y = __shfl_xor_sync(0xffffffffu, x, 1);
+            int yi = self ^ 1;
+            if (y > x || (y == x && yi < xi)) { x = y; xi = yi; }
+            y = __shfl_xor_sync(0xffffffffu, x, 16);
+            yi = __shfl_xor_sync(0xffffffffu, xi, 16);
+            if (y > x || (y == x && yi < xi)) { x = y; xi = yi; }
+            v[i] = x;
+            am[i >> 2] |= (uint32_t)xi << ((i & 3) * 8);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) packed[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+          if (j == self && ww < 14 && n < B) {
+            const long long o = ((((long long)n * 7 + hp) * 7) + (ww >> 1)) * 64 + j * 16;
+            *reinterpret_cast<uint4*>(pool_out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+            *reinterpret_cast<uint4*>(pool_out + o + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            *reinterpret_cast<uint4*>(amax + o) = make_uint4(am[0], am[1], am[2], am[3]);
+          }
+        }
+      } else {
+        const bool ok = (ww < 14) && (n < B);
+        float* o = dx + ((((long long)n * 14 + 2 * hp + hh) * 14) + ww) * 32;
+#pragma unroll 1
+        for (int j = 0; j < 2; ++j) {
+          float v[16];
+          tmem_ld16(tacc + j * 16, v);
+          if (ok) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4)
+              *reinterpret_cast<float4*>(o + j * 16 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * C::kN);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// filter gradient: dW[(tap,ci), co] += sum_px in[px + shift(tap), ci] * dy[px, co].
+// GEMM view per tap group g (4 taps): M = 4*32 (tap_local, ci), N = 64 co, K = 128 pixels of the tile.
+//   A: four [128 px][32 ci] SW64 tiles (one TMA box per tap) read MN-major, stacked along M through LBO
+//   B: the [128 px][64 co] SW128 dy tile read MN-major
+// 7 accumulator groups x 64 columns = 448 TMEM columns; they persist over all pixel tiles of the CTA and are
+// reduced across CTAs with red.global.add.v4.f32.
+// ------------------------------------------------------------------------------------------------
+constexpr int kWgStages = 4;
+constexpr int kWgStageBytes = 4 * 8192;
+constexpr int kWgSmem = kWgStages * kWgStageBytes + 2 * 16384 + 1024 + 512;
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmDy,
+                      float* __restrict__ dw, int num_tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* abuf = smem;
+  uint8_t* dybuf = smem + kWgStages * kWgStageBytes;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(dybuf + 2 * 16384);
+  uint64_t* a_empty = a_full + kWgStages;
+  uint64_t* dy_full = a_empty + kWgStages;  // [2]
+  uint64_t* dy_empty = dy_full + 2;         // [2]
+  uint64_t* acc_full = dy_empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmIn);
+    prefetch_tmap(&tmDy);
+    for (int s = 0; s < kWgStages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&dy_full[i], 1); mbar_init(&dy_empty[i], 1); }
+    mbar_init(acc_full, 1);
+    fence_barrier_init();
+    fence_proxy_async_smem();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0, it = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int nb = tile / 7, hp = tile % 7;
+        const int db = it & 1;
+        mbar_wait(&dy_empty[db], ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(&dy_full[db], 16384);
+        tma_load_4d(dybuf + db * 16384, &tmDy, &dy_full[db], 0, 0, 2 * hp, nb * 4);
+        for (int g = 0; g < 7; ++g) {
+          const int ntap = (g == 6) ? 1 : 4;
+          mbar_wait(&a_empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&a_full[stage], ntap * 8192);
+          for (int tl = 0; tl < ntap; ++tl) {
+            const int tap = g * 4 + tl, kh = tap / 5, kw = tap % 5;
+            tma_load_4d(abuf + stage * kWgStageBytes + tl * 8192, &tmIn, &a_full[stage], 0, kw - 2, 2 * hp + kh - 2, nb * 4);
+          }
+          if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
+      int stage = 0, it = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int db = it & 1;
+        mbar_wait(&dy_full[db], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t sdy = smem_u32(dybuf + db * 16384);
+        for (int g = 0; g < 7; ++g) {
+          mbar_wait(&a_full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(abuf + stage * kWgStageBytes);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t da = make_smem_desc(sa + ks * 1024, 8192, 512, kSwz64);    // 16 px = two 512 B atoms
+            const uint64_t dbb = make_smem_desc(sdy + ks * 2048, 8192, 1024, kSwz128); // 16 px = two 1024 B atoms
+            umma_bf16(tmem_base + g * 64, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+          }
+          umma_commit(&a_empty[stage]);
+          if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&dy_empty[db]);
+      }
+      umma_commit(acc_full);
+    }
+  } else {
+    const int q = warp & 3;
+    mbar_wait(acc_full, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int g = 0; g < 7; ++g) {
+      const int tap = g * 4 + q;
+#pragma unroll 1
+      for (int j = 0; j < 4; ++j) {
+        float v[16];
+        tmem_ld16(tmem_base + g * 64 + j * 16 + ((uint32_t)(q * 32) << 16), v);
+        if (tap < 25) {
+          float* o = dw + ((long long)(tap * 32 + lane)) * 64 + j * 16;
+#pragma unroll
+          for (int i = 0; i < 16; i += 4) red_add_v4_f32(o + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+}  // namespace
+
+extern "C" int tfd_conv2_fwd(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
+                             void* stream) {
+  CUtensorMap tmA, tmW;
+  int rc = tfd_make_tmap_nhwc_bf16(&tmA, in, B, 14, 14, 32, 4, 2, 16, 64);
+  if (rc) return rc;
+  rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
+  if (rc) return rc;
+  using C = ConvCfg<true>;
+  static bool attr = false;
+  if (!attr) {
+    TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
+    attr = true;
+  }
+  const int tiles = ((B + 3) / 4) * 7;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  conv2_tc_kernel<true><<<grid, kThreads, C::kSmem, static_cast<cudaStream_t>(stream)>>>(
+      tmA, tmW, b, static_cast<bf16*>(pool_out), argmax, nullptr, B, tiles);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, void* stream) {
+  CUtensorMap tmA, tmW;
+  int rc = tfd_make_tmap_nhwc_bf16(&tmA, dy, B, 14, 14, 64, 4, 2, 16, 128);
+  if (rc) return rc;
+  rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
+  if (rc) return rc;
+  using C = ConvCfg<false>;
+  static bool attr = false;
+  if (!attr) {
+    TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
+    attr = true;
+  }
+  const int tiles = ((B + 3) / 4) * 7;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  conv2_tc_kernel<false><<<grid, kThreads, C::kSmem, static_cast<cudaStream_t>(stream)>>>(
+      tmA, tmW, nullptr, nullptr, nullptr, dx, B, tiles);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv2_wgrad(const void* in, const void* dy, float* dw, int B, void* stream) {
+  CUtensorMap tmIn, tmDy;
+  int rc = tfd_make_tmap_nhwc_bf16(&tmIn, in, B, 14, 14, 32, 4, 2, 16, 64);
+  if (rc) return rc;
+  rc = tfd_make_tmap_nhwc_bf16(&tmDy, dy, B, 14, 14, 64, 4, 2, 16, 128);
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
+    attr = true;
+  }
+  const int tiles = ((B + 3) / 4) * 7;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  conv2_wgrad_tc_kernel<<<grid, kThreads, kWgSmem, static_cast<cudaStream_t>(stream)>>>(tmIn, tmDy, dw, tiles);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,562 @@
+// CUDA-core kernels: casts, Philox init, conv1 (Cin=1, tensor-core hostile), pooling backward, the fused
+// output head, and slow reference kernels used only to validate the tcgen05 paths.
+//
+// Call sites replaced (all /root/reference/mnist_python_m.py): conv1+bias+relu+pool :109-111, dropout :124,
+// output matmul :127, softmax cross entropy :205, accuracy :206-207, tf.random_normal :186-195.
+#include "../include/tfd_b200.h"
+#include "tfd_common.cuh"
+
+namespace {
+
+using namespace tfd;
+typedef __nv_bfloat16 bf16;
+
+// ------------------------------------------------------------------------------------------------
+// Philox4x32-10
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+    const uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += W0;
+    k.y += W1;
+  }
+  return c;
+}
+__device__ __forceinline__ float u01(uint32_t x) { return ((float)x + 0.5f) * 2.3283064365386963e-10f; }
+
+__global__ void random_normal_kernel(float* __restrict__ out, long long n, unsigned long long seed, float stddev) {
+  const long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // 4 values per thread
+  if (i4 * 4 >= n) return;
+  uint4 r = philox4x32_10(make_uint4((uint32_t)i4, (uint32_t)(i4 >> 32), 0x5eed, 0),
+                          make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+  float z[4];
+  const float r0 = sqrtf(-2.f * logf(u01(r.x))), r1 = sqrtf(-2.f * logf(u01(r.z)));
+  sincosf(6.283185307179586f * u01(r.y), &z[1], &z[0]);
+  sincosf(6.283185307179586f * u01(r.w), &z[3], &z[2]);
+  z[0] *= r0; z[1] *= r0; z[2] *= r1; z[3] *= r1;
+  for (int j = 0; j < 4; ++j)
+    if (i4 * 4 + j < n) out[i4 * 4 + j] = z[j] * stddev;
+}
+
+__global__ void cast_bf16_kernel(const float* __restrict__ src, long long ld_src, bf16* __restrict__ dst,
+                                 long long ld_dst, int rows, int cols) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)rows * ld_dst) return;
+  const int r = (int)(i / ld_dst), c = (int)(i % ld_dst);
+  dst[i] = __float2bfloat16(c < cols ? src[r * ld_src + c] : 0.f);
+}
+
+// ------------------------------------------------------------------------------------------------
+// conv1 forward: 5x5 SAME, 1 -> 32, + bias + ReLU + 2x2 max pool.  grid (B, 2): half image per block.
+// warp = pooled row, lane = output channel; the 6x6 input window is a shared-memory broadcast.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                        const float* __restrict__ b, bf16* __restrict__ out,
+                                                        unsigned char* __restrict__ amax) {
+  __shared__ float patch[18][32];  // input rows 14*half-2 .. +17, cols -2 .. 29
+  const int n = blockIdx.x, half = blockIdx.y;
+  for (int i = threadIdx.x; i < 18 * 32; i += blockDim.x) {
+    const int pr = i >> 5, pc = i & 31;
+    const int r = 14 * half - 2 + pr, c = pc - 2;
+    patch[pr][pc] = (r >= 0 && r < 28 && c >= 0 && c < 28) ? x[(long long)n * 784 + r * 28 + c] : 0.f;
+  }
+  const int c = threadIdx.x & 31, prow = threadIdx.x >> 5;  // pooled row inside the half: 0..6
+  float wr[25];
+#pragma unroll
+  for (int t = 0; t < 25; ++t) wr[t] = w[t * 32 + c];
+  const float bias = b[c];
+  __syncthreads();
+  const int ph = half * 7 + prow;
+  for (int pw = 0; pw < 14; ++pw) {
+    float win[6][6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = 0; j < 6; ++j) win[i][j] = patch[2 * prow + i][2 * pw + j];
+    float best = -1.f;
+    int bi = 0;
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        float acc = bias;
+#pragma unroll
+        for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 5; ++kw) acc = fmaf(win[dy + kh][dx + kw], wr[kh * 5 + kw], acc);
+        acc = fmaxf(acc, 0.f);
+        if (acc > best) { best = acc; bi = dy * 2 + dx; }
+      }
+    const long long o = (((long long)n * 14 + ph) * 14 + pw) * 32 + c;
+    out[o] = __float2bfloat16(best);
+    amax[o] = (unsigned char)bi;
+  }
+}
+
+// conv1 filter gradient: pool/ReLU backward folded in (only the arg-max position of each 2x2 window carries
+// gradient).  grid B, 256 threads: lane = channel, 8 pixel groups; block-level reduce, then atomics.
+__global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
+                                                          const bf16* __restrict__ pool, const unsigned char* __restrict__ amax,
+                                                          float* __restrict__ dw, float* __restrict__ db) {
+  __shared__ float img[32][33];
+  __shared__ float red[8][26][32];
+  const int n = blockIdx.x;
+  for (int i = threadIdx.x; i < 32 * 32; i += blockDim.x) {
+    const int r = (i >> 5) - 2, c = (i & 31) - 2;
+    img[i >> 5][i & 31] = (r >= 0 && r < 28 && c >= 0 && c < 28) ? x[(long long)n * 784 + r * 28 + c] : 0.f;
+  }
+  __syncthreads();
+  const int c = threadIdx.x & 31, grp = threadIdx.x >> 5;
+  float acc[25];
+#pragma unroll
+  for (int t = 0; t < 25; ++t) acc[t] = 0.f;
+  float accb = 0.f;
+  for (int pix = grp; pix < 196; pix += 8) {
+    const int ph = pix / 14, pw = pix % 14;
+    const long long idx = (((long long)n * 14 + ph) * 14 + pw) * 32 + c;
+    float g = dpool[idx];
+    if (!(__bfloat162float(pool[idx]) > 0.f)) g = 0.f;
+    const int a = amax[idx];
+    const int h = 2 * ph + (a >> 1), wq = 2 * pw + (a & 1);
+    accb += g;
+#pragma unroll
+    for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(g, img[h + kh][wq + kw], acc[kh * 5 + kw]);
+  }
+#pragma unroll
+  for (int t = 0; t < 25; ++t) red[grp][t][c] = acc[t];
+  red[grp][25][c] = accb;
+  __syncthreads();
+  for (int i = threadIdx.x; i < 26 * 32; i += blockDim.x) {
+    const int t = i >> 5, cc = i & 31;
+    float s = 0.f;
+#pragma unroll
+    for (int gq = 0; gq < 8; ++gq) s += red[gq][t][cc];
+    if (t < 25) atomicAdd(dw + t * 32 + cc, s);
+    else atomicAdd(db + cc, s);
+  }
+}
+
+// pool2 + ReLU backward: dpool fp32 [B,7,7,64] -> dy bf16 [B,14,14,64]; db[64] += sum.
+__global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict__ dpool, const bf16* __restrict__ pool,
+                                                        const unsigned char* __restrict__ amax, bf16* __restrict__ dy,
+                                                        float* __restrict__ db, long long total) {
+  __shared__ float red[256];
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  float g = 0.f;
+  if (idx < total) {
+    const int c = (int)(idx & 63);
+    const long long p = idx >> 6;
+    const int pw = (int)(p % 7), ph = (int)((p / 7) % 7);
+    const long long n = p / 49;
+    g = dpool[idx];
+    if (!(__bfloat162float(pool[idx]) > 0.f)) g = 0.f;
+    const int a = amax[idx];
+    const bf16 gb = __float2bfloat16(g), z = __float2bfloat16(0.f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const long long o = (((n * 14 + 2 * ph + (q >> 1)) * 14) + 2 * pw + (q & 1)) * 64 + c;
+      dy[o] = (q == a) ? gb : z;
+    }
+  }
+  red[threadIdx.x] = g;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    atomicAdd(db + threadIdx.x, red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// head: rows phase
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+head_rows_kernel(const float* __restrict__ pre, const bf16* __restrict__ hid_in, const float* __restrict__ hid_bias,
+                 const float* __restrict__ out_w, const float* __restrict__ out_b, const float* __restrict__ labels,
+                 int B, int H, long long ld_h, float keep_prob, unsigned long long seed, unsigned long long step_base,
+                 const unsigned* __restrict__ step_ptr, int training, bf16* __restrict__ hid_out, bf16* __restrict__ dhid, float* __restrict__ dlogits,
+                 float* __restrict__ loss_row, unsigned char* __restrict__ hit, unsigned char* __restrict__ keep_out) {
+  extern __shared__ float sh[];  // H hidden values, then 8*10 partials, then 10 dlogits
+  float* part = sh + H;
+  float* dl = part + 80;
+  const int r = blockIdx.x, tid = threadIdx.x;
+  const unsigned long long step = step_base + (step_ptr ? (unsigned long long)*step_ptr : 0ull);
+  const float inv_keep = keep_prob < 1.f ? 1.f / keep_prob : 1.f;
+  for (int k = tid; k < H; k += 256) {
+    float a;
+    if (pre) {
+      a = fmaxf(pre[(long long)r * H + k] + hid_bias[k], 0.f);
+      if (keep_prob < 1.f) {
+        const unsigned long long e = (unsigned long long)r * H + k;
+        const uint4 rn = philox4x32_10(make_uint4((uint32_t)e, (uint32_t)(e >> 32), (uint32_t)step, (uint32_t)(step >> 32)),
+                                       make_uint2((uint32_t)seed, (uint32_t)(seed >> 32) ^ 0xd509u));
+        const bool keep = u01(rn.x) < keep_prob;
+        a = keep ? a * inv_keep : 0.f;
+        if (keep_out) keep_out[(long long)r * H + k] = keep;
+      }
+      // the value every consumer sees is the bf16-rounded one
+      const bf16 ab = __float2bfloat16(a);
+      hid_out[(long long)r * ld_h + k] = ab;
+      a = __bfloat162float(ab);
+    } else {
+      a = __bfloat162float(hid_in[(long long)r * ld_h + k]);
+    }
+    sh[k] = a;
+  }
+  __syncthreads();
+  float p[10];
+#pragma unroll
+  for (int j = 0; j < 10; ++j) p[j] = 0.f;
+  for (int k = tid; k < H; k += 256) {
+    const float a = sh[k];
+    const float* wr = out_w + (long long)k * 10;
+#pragma unroll
+    for (int j = 0; j < 10; ++j) p[j] = fmaf(a, __ldg(wr + j), p[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < 10; ++j) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) p[j] += __shfl_xor_sync(0xffffffffu, p[j], o);
+  }
+  if ((tid & 31) == 0) {
+#pragma unroll
+    for (int j = 0; j < 10; ++j) part[(tid >> 5) * 10 + j] = p[j];
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float lg[10], mx = -INFINITY;
+    int am = 0, al = 0;
+    float lmax = -INFINITY;
+    for (int j = 0; j < 10; ++j) {
+      float s = out_b[j];
+      for (int wv = 0; wv < 8; ++wv) s += part[wv * 10 + j];
+      lg[j] = s;
+      if (s > mx) { mx = s; am = j; }
+      const float y = labels[(long long)r * 10 + j];
+      if (y > lmax) { lmax = y; al = j; }
+    }
+    float se = 0.f;
+    for (int j = 0; j < 10; ++j) se += expf(lg[j] - mx);
+    const float lse = mx + logf(se);
+    float loss = 0.f, ysum = 0.f;
+    for (int j = 0; j < 10; ++j) {
+      const float y = labels[(long long)r * 10 + j];
+      loss += y * (lse - lg[j]);
+      ysum += y;
+    }
+    for (int j = 0; j < 10; ++j) {
+      const float y = labels[(long long)r * 10 + j];
+      // d/dlogit of mean_r sum_j -y_j log softmax_j  (dense labels: sum(y) need not be 1)
+      const float d = (expf(lg[j] - lse) * ysum - y) / (float)B;
+      dl[j] = d;
+      dlogits[(long long)r * 10 + j] = d;
+    }
+    loss_row[r] = loss;
+    hit[r] = (am == al);
+  }
+  if (!training) return;
+  __syncthreads();
+  float d[10];
+#pragma unroll
+  for (int j = 0; j < 10; ++j) d[j] = dl[j];
+  for (int k = tid; k < H; k += 256) {
+    const float* wr = out_w + (long long)k * 10;
+    float g = 0.f;
+#pragma unroll
+    for (int j = 0; j < 10; ++j) g = fmaf(d[j], __ldg(wr + j), g);
+    g = (sh[k] > 0.f) ? g * (pre ? inv_keep : 1.f) : 0.f;  // ReLU' and the dropout mask (kept <=> sh>0 or relu==0)
+    dhid[(long long)r * ld_h + k] = __float2bfloat16(g);
+  }
+}
+
+// head: columns phase
+__global__ void __launch_bounds__(256)
+head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, long long ld_h,
+                 const float* __restrict__ dlogits, const float* __restrict__ loss_row,
+                 const unsigned char* __restrict__ hit, int B, int H, float* __restrict__ d_out_w,
+                 float* __restrict__ d_hid_bias, float* __restrict__ d_out_b, float* __restrict__ scalars) {
+  extern __shared__ float dls[];  // [B][10]
+  const int tid = threadIdx.x;
+  for (int i = tid; i < B * 10; i += 256) dls[i] = dlogits[i];
+  __syncthreads();
+  const int k = blockIdx.x * 256 + tid;
+  if (hid != nullptr && k < H) {
+    float acc[10];
+#pragma unroll
+    for (int j = 0; j < 10; ++j) acc[j] = 0.f;
+    float sb = 0.f;
+    for (int r = 0; r < B; ++r) {
+      const float hv = __bfloat162float(hid[(long long)r * ld_h + k]);
+      sb += __bfloat162float(dhid[(long long)r * ld_h + k]);
+#pragma unroll
+      for (int j = 0; j < 10; ++j) acc[j] = fmaf(hv, dls[r * 10 + j], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 10; ++j) d_out_w[(long long)k * 10 + j] = acc[j];
+    d_hid_bias[k] = sb;
+  }
+  if (blockIdx.x == 0) {
+    if (tid < 10 && d_out_b) {
+      float s = 0.f;
+      for (int r = 0; r < B; ++r) s += dls[r * 10 + tid];
+      d_out_b[tid] = s;
+    }
+    if (tid == 32) {
+      float s = 0.f;
+      for (int r = 0; r < B; ++r) s += loss_row[r];
+      scalars[0] = s / (float)B;
+    }
+    if (tid == 64) {
+      int s = 0;
+      for (int r = 0; r < B; ++r) s += hit[r];
+      scalars[1] = (float)s / (float)B;
+    }
+  }
+}
+
+__global__ void colsum_bf16_kernel(const bf16* __restrict__ x, long long ld, int rows, int cols, float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.f;
+  for (int r = 0; r < rows; ++r) s += __bfloat162float(x[(long long)r * ld + c]);
+  out[c] = s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// reference kernels (validation only)
+// ------------------------------------------------------------------------------------------------
+__global__ void gemm_ref_kernel(const bf16* A, long long lda, const bf16* Bm, long long ldb, int M, int N, int K,
+                                float* out, long long ld_out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x, m = blockIdx.y;
+  if (n >= N || m >= M) return;
+  float s = 0.f;
+  for (int k = 0; k < K; ++k) s = fmaf(__bfloat162float(A[m * lda + k]), __bfloat162float(Bm[k * ldb + n]), s);
+  out[m * ld_out + n] = s;
+}
+
+__global__ void conv2_fwd_ref_kernel(const bf16* __restrict__ in, const bf16* __restrict__ w, const float* __restrict__ b,
+                                     bf16* __restrict__ out, unsigned char* __restrict__ amax, long long total) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int co = (int)(idx & 63);
+  const long long p = idx >> 6;
+  const int pw = (int)(p % 7), ph = (int)((p / 7) % 7);
+  const long long n = p / 49;
+  float best = -1.f;
+  int bi = 0;
+  for (int q = 0; q < 4; ++q) {
+    const int h = 2 * ph + (q >> 1), wq = 2 * pw + (q & 1);
+    float acc = b[co];
+    for (int kh = 0; kh < 5; ++kh) {
+      const int ih = h + kh - 2;
+      if (ih < 0 || ih >= 14) continue;
+      for (int kw = 0; kw < 5; ++kw) {
+        const int iw = wq + kw - 2;
+        if (iw < 0 || iw >= 14) continue;
+        const bf16* ip = in + ((n * 14 + ih) * 14 + iw) * 32;
+        const bf16* wp = w + ((kh * 5 + kw) * 32) * 64 + co;
+        for (int ci = 0; ci < 32; ++ci) acc = fmaf(__bfloat162float(ip[ci]), __bfloat162float(wp[ci * 64]), acc);
+      }
+    }
+    acc = fmaxf(acc, 0.f);
+    if (acc > best) { best = acc; bi = q; }
+  }
+  out[idx] = __float2bfloat16(best);
+  amax[idx] = (unsigned char)bi;
+}
+
+__global__ void conv2_dgrad_ref_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ w, float* __restrict__ dx,
+                                       long long total) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int ci = (int)(idx & 31);
+  const long long p = idx >> 5;
+  const int wq = (int)(p % 14), h = (int)((p / 14) % 14);
+  const long long n = p / 196;
+  float acc = 0.f;
+  for (int kh = 0; kh < 5; ++kh) {
+    const int oh = h + 2 - kh;
+    if (oh < 0 || oh >= 14) continue;
+    for (int kw = 0; kw < 5; ++kw) {
+      const int ow = wq + 2 - kw;
+      if (ow < 0 || ow >= 14) continue;
+      const bf16* gp = dy + ((n * 14 + oh) * 14 + ow) * 64;
+      const bf16* wp = w + ((kh * 5 + kw) * 32 + ci) * 64;
+      for (int co = 0; co < 64; ++co) acc = fmaf(__bfloat162float(gp[co]), __bfloat162float(wp[co]), acc);
+    }
+  }
+  dx[idx] = acc;
+}
+
+// grid (800*64/256, chunks): each block sums a chunk of images, then atomics
+__global__ void conv2_wgrad_ref_kernel(const bf16* __restrict__ in, const bf16* __restrict__ dy, float* __restrict__ dw,
+                                       int B, int imgs_per_chunk) {
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;  // (tap*32+ci)*64+co
+  const int co = o & 63, ci = (o >> 6) & 31, tap = o >> 11;
+  const int kh = tap / 5, kw = tap % 5;
+  const int n0 = blockIdx.y * imgs_per_chunk, n1 = min(B, n0 + imgs_per_chunk);
+  float acc = 0.f;
+  for (int n = n0; n < n1; ++n)
+    for (int h = 0; h < 14; ++h) {
+      const int ih = h + kh - 2;
+      if (ih < 0 || ih >= 14) continue;
+      for (int wq = 0; wq < 14; ++wq) {
+        const int iw = wq + kw - 2;
+        if (iw < 0 || iw >= 14) continue;
+        acc = fmaf(__bfloat162float(in[(((long long)n * 14 + ih) * 14 + iw) * 32 + ci]),
+                   __bfloat162float(dy[(((long long)n * 14 + h) * 14 + wq) * 64 + co]), acc);
+      }
+    }
+  atomicAdd(dw + o, acc);
+}
+
+struct ZeroTable {
+  float* p[16];
+  long long n[16];
+  int cnt;
+};
+__global__ void zero_multi_kernel(const __grid_constant__ ZeroTable t) {
+  float* p = t.p[blockIdx.y];
+  const long long n = t.n[blockIdx.y], n4 = n >> 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x)
+    reinterpret_cast<float4*>(p)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    p[i] = 0.f;
+}
+
+}  // namespace
+
+#define ST(s) static_cast<cudaStream_t>(s)
+
+extern "C" int tfd_random_normal(float* out, long long n, unsigned long long seed, float stddev, void* stream) {
+  const long long n4 = (n + 3) / 4;
+  random_normal_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, ST(stream)>>>(out, n, seed, stddev);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long long ld_dst, int rows, int cols,
+                             void* stream) {
+  const long long total = (long long)rows * ld_dst;
+  cast_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ST(stream)>>>(src, ld_src, (bf16*)dst, ld_dst, rows, cols);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv1_fwd(const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
+                             void* stream) {
+  conv1_fwd_kernel<<<dim3(B, 2), 224, 0, ST(stream)>>>(x, w, b, (bf16*)pool_out, argmax);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv1_wgrad(const float* x, const float* dpool, const void* pool_out, const unsigned char* argmax,
+                               float* dw, float* db, int B, void* stream) {
+  conv1_wgrad_kernel<<<B, 256, 0, ST(stream)>>>(x, dpool, (const bf16*)pool_out, argmax, dw, db);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_pool2_bwd(const float* dpool, const void* pool_out, const unsigned char* argmax, void* dy, float* db,
+                             int B, void* stream) {
+  const long long total = (long long)B * 49 * 64;
+  pool2_bwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ST(stream)>>>(dpool, (const bf16*)pool_out, argmax, (bf16*)dy,
+                                                                          db, total);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_head_rows(const float* pre_f32, const void* hid_bf16, const float* hid_bias, const float* out_w,
+                             const float* out_b, const float* labels, int B, int H, long long ld_h, float keep_prob,
+                             unsigned long long seed, unsigned long long step, const unsigned* step_ptr, int training,
+                             void* hid_out, void* dhid, float* dlogits, float* loss_row, unsigned char* hit,
+                             unsigned char* keep_mask_out, void* stream) {
+  TFD_REQUIRE((pre_f32 != nullptr) != (hid_bf16 != nullptr), "head_rows: exactly one of pre_f32 / hid_bf16");
+  TFD_REQUIRE(!pre_f32 || (hid_bias && hid_out), "head_rows: pre_f32 mode needs hid_bias and hid_out");
+  TFD_REQUIRE(!training || dhid, "head_rows: training needs dhid");
+  const size_t smem = (size_t)(H + 96) * sizeof(float);
+  TFD_REQUIRE(smem <= 200 * 1024, "head_rows: H=%d too large", H);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    TFD_CUDA_CHECK(cudaFuncSetAttribute(head_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  head_rows_kernel<<<B, 256, smem, ST(stream)>>>(pre_f32, (const bf16*)hid_bf16, hid_bias, out_w, out_b, labels, B, H, ld_h,
+                                                 keep_prob, seed, step, step_ptr, training, (bf16*)hid_out, (bf16*)dhid, dlogits,
+                                                 loss_row, hit, keep_mask_out);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_head_cols(const void* hid, const void* dhid, long long ld_h, const float* dlogits,
+                             const float* loss_row, const unsigned char* hit, int B, int H, float* d_out_w,
+                             float* d_hid_bias, float* d_out_b, float* scalars, void* stream) {
+  const size_t smem = (size_t)B * 10 * sizeof(float);
+  TFD_REQUIRE(smem <= 48 * 1024, "head_cols: batch %d too large for the dlogits tile", B);
+  const int blocks = hid ? (H + 255) / 256 : 1;
+  head_cols_kernel<<<blocks, 256, smem, ST(stream)>>>((const bf16*)hid, (const bf16*)dhid, ld_h, dlogits, loss_row, hit, B,
+                                                      H, d_out_w, d_hid_bias, d_out_b, scalars);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out, void* stream) {
+  colsum_bf16_kernel<<<(cols + 255) / 256, 256, 0, ST(stream)>>>((const bf16*)x, ld, rows, cols, out);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_gemm_ref(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, float* out,
+                            long long ld_out, void* stream) {
+  gemm_ref_kernel<<<dim3((N + 127) / 128, M), 128, 0, ST(stream)>>>((const bf16*)A, lda, (const bf16*)B, ldb, M, N, K, out,
+                                                                   ld_out);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv2_fwd_ref(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax,
+                                 int B, void* stream) {
+  const long long total = (long long)B * 49 * 64;
+  conv2_fwd_ref_kernel<<<(unsigned)((total + 127) / 128), 128, 0, ST(stream)>>>((const bf16*)in, (const bf16*)w, b,
+                                                                              (bf16*)pool_out, argmax, total);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv2_dgrad_ref(const void* dy, const void* w, float* dx, int B, void* stream) {
+  const long long total = (long long)B * 196 * 32;
+  conv2_dgrad_ref_kernel<<<(unsigned)((total + 127) / 128), 128, 0, ST(stream)>>>((const bf16*)dy, (const bf16*)w, dx, total);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv2_wgrad_ref(const void* in, const void* dy, float* dw, int B, void* stream) {
+  const int per = 4;
+  conv2_wgrad_ref_kernel<<<dim3(800 * 64 / 256, (B + per - 1) / per), 256, 0, ST(stream)>>>((const bf16*)in, (const bf16*)dy,
+                                                                                           dw, B, per);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_zero_multi(float* const* ptrs, const long long* ns, int count, void* stream) {
+  TFD_REQUIRE(count >= 1 && count <= 16, "zero_multi: bad count %d", count);
+  ZeroTable t;
+  t.cnt = count;
+  long long maxn = 0;
+  for (int i = 0; i < count; ++i) {
+    TFD_REQUIRE(((uintptr_t)ptrs[i] & 15) == 0, "zero_multi: pointer %d not 16B aligned", i);
+    t.p[i] = ptrs[i];
+    t.n[i] = ns[i];
+    if (ns[i] > maxn) maxn = ns[i];
+  }
+  long long bx = (maxn / 4 + 255) / 256;
+  if (bx < 1) bx = 1;
+  if (bx > 296) bx = 296;
+  zero_multi_kernel<<<dim3((unsigned)bx, count), 256, 0, ST(stream)>>>(t);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,100 @@
+// Host utilities: error string, TMA tensor-map construction, device info.
+#include <stdarg.h>
+#include <string.h>
+
+#include "../include/tfd_b200.h"
+#include "tfd_common.cuh"
+
+static thread_local char g_err[1024] = "";
+
+void tfd_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* tfd_last_error(void) { return g_err; }
+
+extern "C" int tfd_version(void) { return 100; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess || !p) {
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+static CUtensorMapSwizzle swz(int bytes) {
+  switch (bytes) {
+    case 128: return CU_TENSOR_MAP_SWIZZLE_128B;
+    case 64: return CU_TENSOR_MAP_SWIZZLE_64B;
+    case 32: return CU_TENSOR_MAP_SWIZZLE_32B;
+    default: return CU_TENSOR_MAP_SWIZZLE_NONE;
+  }
+}
+
+int tfd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                          uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+  EncodeTiledFn fn = get_encode_tiled();
+  TFD_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  TFD_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
+  TFD_REQUIRE((ld * 2) % 16 == 0, "TMA row pitch %llu B not a multiple of 16", (unsigned long long)(ld * 2));
+  TFD_REQUIRE(box_cols * 2 <= (uint32_t)(swizzle_bytes ? swizzle_bytes : 256) && box_rows <= 256 && box_cols <= 256,
+              "TMA box %ux%u does not fit swizzle %d", box_rows, box_cols, swizzle_bytes);
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstr[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TFD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2d %llux%llu ld %llu box %ux%u) failed: %d",
+              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols, (int)r);
+  return 0;
+}
+
+int tfd_make_tmap_nhwc_bf16(CUtensorMap* out, const void* base, uint64_t N, uint64_t H, uint64_t W, uint64_t C,
+                            uint32_t bn, uint32_t bh, uint32_t bw, int swizzle_bytes) {
+  EncodeTiledFn fn = get_encode_tiled();
+  TFD_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  TFD_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
+  TFD_REQUIRE((C * 2) % 16 == 0 && (int)(C * 2) <= swizzle_bytes, "NHWC channel bytes %llu unsupported",
+              (unsigned long long)(C * 2));
+  cuuint64_t gdim[4] = {C, W, H, N};
+  cuuint64_t gstr[3] = {C * 2, W * C * 2, H * W * C * 2};
+  cuuint32_t box[4] = {(cuuint32_t)C, bw, bh, bn};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TFD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(nhwc %llu,%llu,%llu,%llu box %u,%u,%u) failed: %d",
+              (unsigned long long)N, (unsigned long long)H, (unsigned long long)W, (unsigned long long)C, bn, bh, bw,
+              (int)r);
+  return 0;
+}
+
+extern "C" int tfd_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin) {
+  cudaDeviceProp p;
+  TFD_CUDA_CHECK(cudaGetDeviceProperties(&p, device));
+  if (sm_count) *sm_count = p.multiProcessorCount;
+  if (cc_major) *cc_major = p.major;
+  if (cc_minor) *cc_minor = p.minor;
+  if (smem_optin) *smem_optin = p.sharedMemPerBlockOptin;
+  return 0;
+}
+
+extern "C" int tfd_set_device(int device) {
+  TFD_CUDA_CHECK(cudaSetDevice(device));
+  return 0;
+}

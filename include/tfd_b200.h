@@ -1,0 +1,151 @@
+/* C ABI of libtfd_b200.so -- the native sm_100a runtime of tensorflow_distributed_b200.
+ *
+ * Every entry point returns 0 on success; otherwise tfd_last_error() describes the failure.
+ * Pointers are device pointers unless stated; `stream` is a cudaStream_t (NULL = default stream).
+ * Layouts follow the reference: NHWC activations, HWIO filters, [in,out] dense weights
+ * (/root/reference/mnist_python_m.py:93-128, :185-196).
+ */
+#ifndef TFD_B200_H_
+#define TFD_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* tfd_last_error(void);
+int tfd_version(void);
+int tfd_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin);
+
+/* ---- GEMM epilogues (tfd_gemm_bf16 `mode`) ---- */
+#define TFD_EPI_STORE_F32 0      /* out fp32 = alpha*acc (+bias)                                    */
+#define TFD_EPI_ATOMIC_F32 1     /* out fp32 += alpha*acc via red.global.add (split-K, push-reduce) */
+#define TFD_EPI_BIAS_RELU_BF16 2 /* out bf16 = relu(alpha*acc + bias)                               */
+#define TFD_EPI_STORE_BF16 3     /* out bf16 = alpha*acc (+bias)                                    */
+#define TFD_EPI_RELUMASK_BF16 4  /* out bf16 = mask>0 ? alpha*acc : 0   (dgrad through a ReLU)      */
+
+/* tcgen05/TMEM/TMA GEMM, bf16 operands, fp32 accumulation: D[M,N] = A[M,K] * B[K,N].
+ * a_mn=0: A stored [M,K] (K contiguous); a_mn=1: A stored [K,M].  b_mn=0: B stored [N,K]; b_mn=1: B stored [K,N].
+ * Leading dimensions in elements, multiples of 8.  A/B may be peer-mapped addresses (fused parameter pull);
+ * `out` may be a peer-mapped staging buffer (fused gradient push).  wait_flag (optional): the TMA producer
+ * spins until *wait_flag >= wait_value before loading (parameter-version gate).
+ * Replaces tf.matmul at mnist_python_m.py:121,127 and the matmul gradients generated at m:222. */
+int tfd_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M, int N, int K,
+                  int bn, int splits, int mode, float alpha, void* out, long long ld_out, const float* bias,
+                  const void* relu_mask, long long ld_mask, const unsigned* wait_flag, unsigned wait_value,
+                  void* stream);
+
+/* CUDA-core fp32 reference GEMM (validation only): D[M,N] = A[M,K](bf16,row) * B[K,N](bf16,row). */
+int tfd_gemm_ref(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, float* out,
+                 long long ld_out, void* stream);
+
+/* ---- elementwise / CUDA-core kernels ---- */
+/* fp32 [rows,cols] -> bf16 [rows,ld_dst] (pad columns zeroed). */
+int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long long ld_dst, int rows, int cols, void* stream);
+/* tf.random_normal (m:186-195): Philox4x32-10 + Box-Muller, mean 0. */
+int tfd_random_normal(float* out, long long n, unsigned long long seed, float stddev, void* stream);
+
+/* conv1 5x5 SAME 1->32 + bias + ReLU + 2x2 max-pool (m:109-111).  x fp32 [B,784]; w fp32 [25,32] (HWIO);
+ * out bf16 [B,14,14,32]; argmax u8 [B,14,14,32] (0..3 = position inside the 2x2 window). */
+int tfd_conv1_fwd(const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
+                  void* stream);
+/* conv1 filter/bias gradient with pool+ReLU backward folded in.  dpool fp32 [B,14,14,32] is d(loss)/d(pool1).
+ * dw fp32 [25,32] and db fp32 [32] are ACCUMULATED with atomics (zero them first). */
+int tfd_conv1_wgrad(const float* x, const float* dpool, const void* pool_out, const unsigned char* argmax, float* dw,
+                    float* db, int B, void* stream);
+
+/* conv2 5x5 SAME 32->64 + bias + ReLU + 2x2 max-pool (m:114-116) on tcgen05: implicit GEMM, im2col by TMA
+ * 4-D boxes with out-of-bounds zero fill, filter resident in shared memory.  in bf16 [B,14,14,32];
+ * w bf16 [800,64] (HWIO flattened; may be a peer pointer); out bf16 [B,7,7,64]; argmax u8 [B,7,7,64]. */
+int tfd_conv2_fwd(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
+                  void* stream);
+/* d(loss)/d(pool1) fp32 [B,14,14,32] = conv2 data gradient of dy bf16 [B,14,14,64] (tcgen05 implicit GEMM). */
+int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, void* stream);
+/* dW fp32 [800,64] += im2col(in)^T dy (tcgen05, split over pixel tiles, red.add epilogue; zero dW first). */
+int tfd_conv2_wgrad(const void* in, const void* dy, float* dw, int B, void* stream);
+/* CUDA-core references of the three conv2 kernels (validation only; same argument meaning). */
+int tfd_conv2_fwd_ref(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
+                      void* stream);
+int tfd_conv2_dgrad_ref(const void* dy, const void* w, float* dx, int B, void* stream);
+int tfd_conv2_wgrad_ref(const void* in, const void* dy, float* dw, int B, void* stream);
+
+/* max-pool + ReLU backward of the conv2 block: dpool fp32 [B,7,7,64] -> dy bf16 [B,14,14,64] (dense, zeros
+ * written); db fp32 [64] accumulated with atomics. */
+int tfd_pool2_bwd(const float* dpool, const void* pool_out, const unsigned char* argmax, void* dy, float* db, int B,
+                  void* stream);
+
+/* Head, row phase (one block per example): optional fc bias + ReLU + inverted dropout (m:121-124), output
+ * layer (m:127), softmax cross entropy with dense labels (m:205), dlogits=(softmax-y)/B, accuracy hit
+ * (m:206-207) and the gradient flowing back into the hidden layer.
+ *   pre_f32 != NULL: hidden = dropout(relu(pre_f32 + hid_bias))   (CNN fc1; pre_f32 is the split-K sum)
+ *   else           : hidden = hid_bf16 (already bias+ReLU'd by the GEMM epilogue; MLP)
+ * Writes hid_out bf16 [B,ld_h] (post-dropout, for the output-layer wgrad), dhid bf16 [B,ld_h] (training only),
+ * dlogits fp32 [B,10], loss_row fp32 [B], hit u8 [B]. keep_prob>=1 disables dropout.  The dropout stream is
+ * Philox(seed; step + *step_ptr, element): step_ptr (optional, device) lets a captured CUDA graph advance it. */
+int tfd_head_rows(const float* pre_f32, const void* hid_bf16, const float* hid_bias, const float* out_w,
+                  const float* out_b, const float* labels, int B, int H, long long ld_h, float keep_prob,
+                  unsigned long long seed, unsigned long long step, const unsigned* step_ptr, int training,
+                  void* hid_out, void* dhid, float* dlogits, float* loss_row, unsigned char* hit,
+                  unsigned char* keep_mask_out, void* stream);
+/* Head, column phase: d_out_w[H,10] = hid^T dlogits, d_hid_bias[H] = colsum(dhid), d_out_b[10], loss = mean,
+ * acc = mean(hit).  Deterministic (no atomics).  scalars: fp32[2] = {loss, accuracy}. */
+int tfd_head_cols(const void* hid, const void* dhid, long long ld_h, const float* dlogits, const float* loss_row,
+                  const unsigned char* hit, int B, int H, float* d_out_w, float* d_hid_bias, float* d_out_b,
+                  float* scalars, void* stream);
+/* zero up to 16 fp32 buffers in one launch (accumulators of the atomic epilogues). */
+int tfd_zero_multi(float* const* ptrs, const long long* ns, int count, void* stream);
+/* column sums of a bf16 matrix (MLP hidden-layer bias gradients): out[N] = sum_r x[r, :]. */
+int tfd_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out, void* stream);
+
+/* ---- parameter-server kernels ---- */
+/* One piece of a shard arena that has a bf16 shadow for tensor-core consumers. */
+typedef struct {
+  long long arena_off;  /* element offset of the piece in the fp32 arena */
+  long long numel;      /* rows*cols                                      */
+  int cols;             /* logical columns                                */
+  int ld_shadow;        /* leading dimension of the bf16 shadow (>= cols, multiple of 8); 0 = no shadow */
+  long long shadow_off; /* element offset in the bf16 shadow arena        */
+} tfd_piece_t;
+
+/* Gradient reduce + scale + TF-form Adam + bf16 shadow publish on the owning shard (push, X2/X3; m:208,222):
+ *   g = scale * sum_{r<num_slots} slots[r][i];  m,v,w updated in place;  shadow = bf16(w).
+ * slots: device array of num_slots pointers to fp32 gradient arenas (staging slots written by the workers,
+ * possibly through NVLink).  lr_t is computed on the device from the Adam step counter t_counter[0] (u32,
+ * incremented by this kernel), so the kernel can sit in a CUDA graph.  If wait_counter != NULL the kernel first
+ * spins until *wait_counter >= wait_base + num_slots*epoch (gradient arrivals for this step); on completion it
+ * publishes *version_flag = epoch+1 with release semantics.  epoch is read from t_counter. */
+int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots, float scale,
+                   long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1, float beta2,
+                   float eps, unsigned* t_counter, const unsigned* wait_counter, unsigned* version_flag,
+                   unsigned* global_step, void* stream);
+
+/* Gradient push: copy (and scale) a worker's local fp32 gradient arena segment into its staging slot on the
+ * owning shard (dst may be a peer pointer), then signal arrival: atomicAdd(arrive_counter, 1) at system scope
+ * after a release fence, executed once by the last block. */
+int tfd_push_grads(const float* src, float* dst, long long n, float scale, unsigned* arrive_counter,
+                   unsigned* block_counter, void* stream);
+/* Parameter pull of small tensors: wait until *version_flag >= version, then copy n fp32 from src (peer) to dst. */
+int tfd_pull_params(const float* src, float* dst, long long n, const unsigned* version_flag, unsigned version,
+                    void* stream);
+
+/* Table forms: one launch moves every segment (one per destination shard / source tensor).  push: after all
+ * segments are written the last block adds 1 (release, system scope) to each arrive counter.  pull: each
+ * segment first waits for *versions[i] >= want_version (NULL = no wait). */
+int tfd_push_multi(const void* const* srcs, void* const* dsts, const long long* ns, int nseg, unsigned* const* arrive,
+                   int narrive, float scale, unsigned* block_counter, void* stream);
+int tfd_pull_multi(const void* const* srcs, void* const* dsts, const long long* ns, const unsigned* const* versions,
+                   int nseg, unsigned want_version, void* stream);
+
+/* ---- peer memory (symmetric heap over cudaIpc) ---- */
+int tfd_set_device(int device);
+int tfd_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out64);    /* cudaMalloc + cudaIpcGetMemHandle */
+int tfd_ipc_open(const void* handle64, void** dev_ptr);                  /* cudaIpcOpenMemHandle             */
+int tfd_ipc_close(void* dev_ptr);
+int tfd_free(void* dev_ptr);
+int tfd_enable_peer_access(int device, int peer);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TFD_B200_H_ */

@@ -1,0 +1,263 @@
+"""ctypes binding of ``libtfd_b200.so`` (C ABI in ``include/tfd_b200.h``).
+
+The library is built in-tree by ``build_native.py`` (nvcc, sm_100a only) and
+loaded from ``tensorflow_distributed_b200/_native/``.  There is no fallback: on
+a machine with a GPU a missing library is an error, so a silent eager-PyTorch
+path can never stand in for the kernels.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint, c_ulonglong, c_void_p, POINTER
+from typing import Optional
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_native", "libtfd_b200.so")
+_lib: Optional[ctypes.CDLL] = None
+
+EPI_STORE_F32, EPI_ATOMIC_F32, EPI_BIAS_RELU_BF16, EPI_STORE_BF16, EPI_RELUMASK_BF16 = range(5)
+
+#: number of kernel launches issued through this binding (bench.py reports it as gpu_launches)
+launch_count = 0
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class Piece(ctypes.Structure):
+    _fields_ = [("arena_off", c_longlong), ("numel", c_longlong), ("cols", c_int), ("ld_shadow", c_int),
+                ("shadow_off", c_longlong)]
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH)
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise NativeError("native library %s is missing: run `python build_native.py` "
+                              "(or __graft_entry__.build()) first" % _LIB_PATH)
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.tfd_last_error.restype = c_char_p
+        _lib.tfd_version.restype = c_int
+        for name in dir(_lib):
+            pass
+    return _lib
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise NativeError("%s failed (rc=%d): %s" % (what, rc, lib().tfd_last_error().decode()))
+
+
+def _p(t) -> c_void_p:
+    if t is None:
+        return c_void_p(0)
+    if isinstance(t, int):
+        return c_void_p(t)
+    return c_void_p(t.data_ptr())
+
+
+def _stream() -> c_void_p:
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _count(n: int = 1) -> None:
+    global launch_count
+    launch_count += n
+
+
+def set_device(dev: int) -> None:
+    _check(lib().tfd_set_device(c_int(dev)), "tfd_set_device")
+
+
+def device_info(dev: int = 0) -> dict:
+    sm, maj, mnr, sm_opt = c_int(), c_int(), c_int(), c_size_t()
+    _check(lib().tfd_device_info(c_int(dev), ctypes.byref(sm), ctypes.byref(maj), ctypes.byref(mnr),
+                                 ctypes.byref(sm_opt)), "tfd_device_info")
+    return {"sm_count": sm.value, "cc": (maj.value, mnr.value), "smem_optin": sm_opt.value}
+
+
+# ---------------------------------------------------------------------------------------------
+def gemm_bf16(A, a_mn: int, B, b_mn: int, M: int, N: int, K: int, out, *, mode: int, bn: int = 128, splits: int = 1,
+              alpha: float = 1.0, bias=None, relu_mask=None, lda: Optional[int] = None, ldb: Optional[int] = None,
+              ld_out: Optional[int] = None, ld_mask: Optional[int] = None, wait_flag=None, wait_value: int = 0) -> None:
+    lda = lda if lda is not None else A.stride(0)
+    ldb = ldb if ldb is not None else B.stride(0)
+    ld_out = ld_out if ld_out is not None else out.stride(0)
+    ld_mask = ld_mask if ld_mask is not None else (relu_mask.stride(0) if relu_mask is not None else 0)
+    _check(lib().tfd_gemm_bf16(_p(A), c_longlong(lda), c_int(a_mn), _p(B), c_longlong(ldb), c_int(b_mn), c_int(M),
+                               c_int(N), c_int(K), c_int(bn), c_int(splits), c_int(mode), c_float(alpha), _p(out),
+                               c_longlong(ld_out), _p(bias), _p(relu_mask), c_longlong(ld_mask), _p(wait_flag),
+                               c_uint(wait_value), _stream()), "tfd_gemm_bf16")
+    _count()
+
+
+def gemm_ref(A, B, M, N, K, out) -> None:
+    _check(lib().tfd_gemm_ref(_p(A), c_longlong(A.stride(0)), _p(B), c_longlong(B.stride(0)), c_int(M), c_int(N),
+                              c_int(K), _p(out), c_longlong(out.stride(0)), _stream()), "tfd_gemm_ref")
+    _count()
+
+
+def cast_bf16(src, dst, rows: int, cols: int, ld_src: Optional[int] = None, ld_dst: Optional[int] = None) -> None:
+    _check(lib().tfd_cast_bf16(_p(src), c_longlong(ld_src if ld_src is not None else cols), _p(dst),
+                               c_longlong(ld_dst if ld_dst is not None else cols), c_int(rows), c_int(cols), _stream()),
+           "tfd_cast_bf16")
+    _count()
+
+
+def random_normal(out, seed: int, stddev: float = 1.0) -> None:
+    _check(lib().tfd_random_normal(_p(out), c_longlong(out.numel()), c_ulonglong(seed), c_float(stddev), _stream()),
+           "tfd_random_normal")
+    _count()
+
+
+def conv1_fwd(x, w, b, pool_out, argmax, B: int) -> None:
+    _check(lib().tfd_conv1_fwd(_p(x), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), _stream()), "tfd_conv1_fwd")
+    _count()
+
+
+def conv1_wgrad(x, dpool, pool_out, argmax, dw, db, B: int) -> None:
+    _check(lib().tfd_conv1_wgrad(_p(x), _p(dpool), _p(pool_out), _p(argmax), _p(dw), _p(db), c_int(B), _stream()),
+           "tfd_conv1_wgrad")
+    _count()
+
+
+def conv2_fwd(inp, w, b, pool_out, argmax, B: int, ref: bool = False) -> None:
+    fn = lib().tfd_conv2_fwd_ref if ref else lib().tfd_conv2_fwd
+    _check(fn(_p(inp), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), _stream()), "tfd_conv2_fwd")
+    _count()
+
+
+def conv2_dgrad(dy, w, dx, B: int, ref: bool = False) -> None:
+    fn = lib().tfd_conv2_dgrad_ref if ref else lib().tfd_conv2_dgrad
+    _check(fn(_p(dy), _p(w), _p(dx), c_int(B), _stream()), "tfd_conv2_dgrad")
+    _count()
+
+
+def conv2_wgrad(inp, dy, dw, B: int, ref: bool = False) -> None:
+    fn = lib().tfd_conv2_wgrad_ref if ref else lib().tfd_conv2_wgrad
+    _check(fn(_p(inp), _p(dy), _p(dw), c_int(B), _stream()), "tfd_conv2_wgrad")
+    _count()
+
+
+def pool2_bwd(dpool, pool_out, argmax, dy, db, B: int) -> None:
+    _check(lib().tfd_pool2_bwd(_p(dpool), _p(pool_out), _p(argmax), _p(dy), _p(db), c_int(B), _stream()),
+           "tfd_pool2_bwd")
+    _count()
+
+
+def head_rows(pre_f32, hid_bf16, hid_bias, out_w, out_b, labels, B: int, H: int, ld_h: int, keep_prob: float,
+              seed: int, step: int, training: bool, hid_out, dhid, dlogits, loss_row, hit, keep_mask_out=None,
+              step_ptr=None) -> None:
+    _check(lib().tfd_head_rows(_p(pre_f32), _p(hid_bf16), _p(hid_bias), _p(out_w), _p(out_b), _p(labels), c_int(B),
+                               c_int(H), c_longlong(ld_h), c_float(keep_prob), c_ulonglong(seed), c_ulonglong(step),
+                               _p(step_ptr), c_int(int(training)), _p(hid_out), _p(dhid), _p(dlogits), _p(loss_row), _p(hit),
+                               _p(keep_mask_out), _stream()), "tfd_head_rows")
+    _count()
+
+
+def head_cols(hid, dhid, ld_h: int, dlogits, loss_row, hit, B: int, H: int, d_out_w, d_hid_bias, d_out_b,
+              scalars) -> None:
+    _check(lib().tfd_head_cols(_p(hid), _p(dhid), c_longlong(ld_h), _p(dlogits), _p(loss_row), _p(hit), c_int(B),
+                               c_int(H), _p(d_out_w), _p(d_hid_bias), _p(d_out_b), _p(scalars), _stream()),
+           "tfd_head_cols")
+    _count()
+
+
+def zero_multi(tensors) -> None:
+    n = len(tensors)
+    P = (c_void_p * n)(*[c_void_p(t.data_ptr()) for t in tensors])
+    NS = (c_longlong * n)(*[t.numel() for t in tensors])
+    _check(lib().tfd_zero_multi(P, NS, c_int(n), _stream()), "tfd_zero_multi")
+    _count()
+
+
+def colsum_bf16(x, ld: int, rows: int, cols: int, out) -> None:
+    _check(lib().tfd_colsum_bf16(_p(x), c_longlong(ld), c_int(rows), c_int(cols), _p(out), _stream()),
+           "tfd_colsum_bf16")
+    _count()
+
+
+def adam_apply(w, m, v, shadow, slots_dev, num_slots: int, scale: float, n: int, pieces, lr: float, t_counter,
+               wait_counter=None, version_flag=None, global_step=None, beta1: float = 0.9, beta2: float = 0.999,
+               eps: float = 1e-8) -> None:
+    arr = (Piece * max(1, len(pieces)))(*pieces)
+    _check(lib().tfd_adam_apply(_p(w), _p(m), _p(v), _p(shadow), _p(slots_dev), c_int(num_slots), c_float(scale),
+                                c_longlong(n), arr, c_int(len(pieces)), c_float(lr), c_float(beta1), c_float(beta2),
+                                c_float(eps), _p(t_counter), _p(wait_counter), _p(version_flag), _p(global_step),
+                                _stream()), "tfd_adam_apply")
+    _count()
+
+
+def push_multi(srcs, dsts, ns, arrive, scale: float, block_counter) -> None:
+    n = len(srcs)
+    S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
+    D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
+    NS = (c_longlong * n)(*[int(x) for x in ns])
+    A = (c_void_p * max(1, len(arrive)))(*[c_void_p(int(x)) for x in arrive])
+    _check(lib().tfd_push_multi(S, D, NS, c_int(n), A, c_int(len(arrive)), c_float(scale), _p(block_counter),
+                                _stream()), "tfd_push_multi")
+    _count()
+
+
+def pull_multi(srcs, dsts, ns, versions, want_version: int) -> None:
+    n = len(srcs)
+    S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
+    D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
+    NS = (c_longlong * n)(*[int(x) for x in ns])
+    V = (c_void_p * n)(*[c_void_p(int(x) if x else 0) for x in versions]) if versions is not None else None
+    _check(lib().tfd_pull_multi(S, D, NS, V, c_int(n), c_uint(want_version), _stream()), "tfd_pull_multi")
+    _count()
+
+
+# ---- symmetric heap ----
+def ipc_alloc(nbytes: int):
+    ptr = c_void_p()
+    handle = ctypes.create_string_buffer(64)
+    _check(lib().tfd_ipc_alloc(c_size_t(nbytes), ctypes.byref(ptr), handle), "tfd_ipc_alloc")
+    return ptr.value, handle.raw
+
+
+def ipc_open(handle: bytes) -> int:
+    ptr = c_void_p()
+    _check(lib().tfd_ipc_open(ctypes.c_char_p(handle), ctypes.byref(ptr)), "tfd_ipc_open")
+    return ptr.value
+
+
+def ipc_close(ptr: int) -> None:
+    _check(lib().tfd_ipc_close(c_void_p(ptr)), "tfd_ipc_close")
+
+
+def free(ptr: int) -> None:
+    _check(lib().tfd_free(c_void_p(ptr)), "tfd_free")
+
+
+def tensor_from_ptr(ptr: int, numel: int, dtype: torch.dtype, device) -> torch.Tensor:
+    """Wrap raw device memory (e.g. a peer-mapped ipc pointer) as a torch tensor without copying."""
+    esz = torch.empty((), dtype=dtype).element_size()
+
+    class _Holder:
+        pass
+
+    h = _Holder()
+    typestr = {torch.float32: "<f4", torch.bfloat16: "<u2", torch.uint8: "|u1", torch.int32: "<i4",
+               torch.uint32: "<u4"}[dtype]
+    h.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False), "version": 2,
+                                  "strides": None}
+    t = torch.as_tensor(h, device=device)
+    if dtype == torch.bfloat16:
+        t = t.view(torch.int16).view(torch.bfloat16)
+    elif dtype == torch.uint32:
+        t = t.view(torch.int32)
+    assert t.data_ptr() == ptr and t.element_size() == esz or dtype == torch.uint32
+    return t

@@ -1,0 +1,349 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op.
+
+Inputs of tensor-core kernels are rounded to bf16 first and the reference runs in fp32 on those rounded values,
+so the only difference left is accumulation order (and bf16 rounding of bf16 outputs).
+"""
+import math
+
+import pytest
+import torch
+
+from tensorflow_distributed_b200.ops import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from tensorflow_distributed_b200.ops import native
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    native.lib()  # fail loudly if the .so is missing
+    native.set_device(torch.cuda.current_device())
+    return native
+
+
+def bf(x):
+    return x.to(torch.bfloat16)
+
+
+def rel_err(a, b):
+    return (a.float() - b.float()).abs().max().item() / (b.float().abs().max().item() + 1e-20)
+
+
+DEV = "cuda"
+
+
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K,bn,splits", [(128, 1024, 3136, 128, 16), (128, 1024, 3136, 128, 1), (100, 72, 200, 64, 1),
+                                             (256, 512, 128, 256, 1), (1000, 1024, 3136, 128, 2)])
+def test_gemm_fwd_kmajor_a_mnmajor_b(nat, M, N, K, bn, splits):
+    torch.manual_seed(0)
+    A = bf(torch.randn(M, K, device=DEV))
+    W = bf(torch.randn(K, N, device=DEV))
+    ref = A.float() @ W.float()
+    out = torch.zeros(M, N, device=DEV)
+    mode = nat.EPI_ATOMIC_F32 if splits > 1 else nat.EPI_STORE_F32
+    nat.gemm_bf16(A, 0, W, 1, M, N, K, out, mode=mode, bn=bn, splits=splits)
+    torch.cuda.synchronize()
+    assert rel_err(out, ref) < 2e-3
+    # the CUDA-core reference kernel agrees too
+    out2 = torch.zeros(M, N, device=DEV)
+    nat.gemm_ref(A, W, M, N, K, out2)
+    assert rel_err(out2, ref) < 2e-3
+
+
+def test_gemm_dgrad_both_kmajor(nat):
+    torch.manual_seed(1)
+    B_, H, Kin = 128, 1024, 3136
+    dy = bf(torch.randn(B_, H, device=DEV))
+    W = bf(torch.randn(Kin, H, device=DEV))  # [in, out]; dgrad reads it as [N=in, K=out], K contiguous
+    ref = dy.float() @ W.float().t()
+    out = torch.zeros(B_, Kin, device=DEV)
+    nat.gemm_bf16(dy, 0, W, 0, B_, Kin, H, out, mode=nat.EPI_ATOMIC_F32, bn=64, splits=3)
+    torch.cuda.synchronize()
+    assert rel_err(out, ref) < 2e-3
+
+
+@pytest.mark.parametrize("Bsz", [128, 96])
+def test_gemm_wgrad_both_mnmajor(nat, Bsz):
+    torch.manual_seed(2)
+    Kin, H = 3136, 1024
+    x = bf(torch.randn(Bsz, Kin, device=DEV))
+    dy = bf(torch.randn(Bsz, H, device=DEV))
+    ref = x.float().t() @ dy.float()
+    out = torch.zeros(Kin, H, device=DEV)
+    nat.gemm_bf16(x, 1, dy, 1, Kin, H, Bsz, out, mode=nat.EPI_STORE_F32, bn=128)
+    torch.cuda.synchronize()
+    assert rel_err(out, ref) < 2e-3
+
+
+def test_gemm_mnmajor_a_kmajor_b(nat):
+    torch.manual_seed(3)
+    M, N, K = 256, 192, 320
+    At = bf(torch.randn(K, M, device=DEV))
+    Bt = bf(torch.randn(N, K, device=DEV))
+    ref = At.float().t() @ Bt.float().t()
+    out = torch.zeros(M, N, device=DEV)
+    nat.gemm_bf16(At, 1, Bt, 0, M, N, K, out, mode=nat.EPI_STORE_F32, bn=64)
+    torch.cuda.synchronize()
+    assert rel_err(out, ref) < 2e-3
+
+
+def test_gemm_epilogues_bias_relu_and_relumask_and_padded_ld(nat):
+    torch.manual_seed(4)
+    M, N, K, ld = 128, 100, 784, 104
+    A = bf(torch.randn(M, K, device=DEV))
+    W = torch.zeros(K, ld, device=DEV, dtype=torch.bfloat16)
+    W[:, :N] = bf(torch.randn(K, N, device=DEV))
+    bias = torch.randn(N, device=DEV)
+    ref = torch.relu(A.float() @ W[:, :N].float() + bias)
+    out = torch.full((M, ld), 7.0, device=DEV, dtype=torch.bfloat16)
+    nat.gemm_bf16(A, 0, W, 1, M, N, K, out, mode=nat.EPI_BIAS_RELU_BF16, bn=64, bias=bias)
+    torch.cuda.synchronize()
+    assert rel_err(out[:, :N], ref) < 1e-2
+    assert torch.all(out[:, N:] == 7.0)  # pad columns untouched
+    # dgrad through a ReLU: mask from an activation tensor
+    dy = bf(torch.randn(M, N, device=DEV))
+    dyp = torch.zeros(M, ld, device=DEV, dtype=torch.bfloat16)
+    dyp[:, :N] = dy
+    act = bf(torch.randn(M, K, device=DEV))
+    ref2 = (dy.float() @ W[:, :N].float().t()) * (act.float() > 0)
+    out2 = torch.zeros(M, K, device=DEV, dtype=torch.bfloat16)
+    nat.gemm_bf16(dyp, 0, W, 0, M, K, N, out2, mode=nat.EPI_RELUMASK_BF16, bn=64, relu_mask=act)
+    torch.cuda.synchronize()
+    assert rel_err(out2, ref2) < 1e-2
+
+
+# ------------------------------------------------------------------------------------------------
+def _conv1_ref(x, w, b):
+    y = torch.relu(oracle.conv2d_same_nhwc(x.reshape(-1, 28, 28, 1), w) + b)
+    return oracle.maxpool2x2_nhwc(y), y
+
+
+@pytest.mark.parametrize("B", [128, 5])
+def test_conv1_fwd_and_wgrad(nat, B):
+    torch.manual_seed(5)
+    x = torch.rand(B, 784, device=DEV)
+    w = torch.randn(5, 5, 1, 32, device=DEV)
+    b = torch.randn(32, device=DEV)
+    pool = torch.empty(B, 14, 14, 32, device=DEV, dtype=torch.bfloat16)
+    am = torch.empty(B, 14, 14, 32, device=DEV, dtype=torch.uint8)
+    nat.conv1_fwd(x, w, b, pool, am, B)
+    torch.cuda.synchronize()
+    ref, pre = _conv1_ref(x, w, b)
+    assert rel_err(pool, ref) < 1e-2
+    assert int(am.max()) <= 3
+    # backward: oracle gradient of sum(pool * dpool) w.r.t. w and b
+    dpool = torch.randn(B, 14, 14, 32, device=DEV)
+    wl, bl = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    r2, _ = _conv1_ref(x, wl, bl)
+    (r2 * dpool).sum().backward()
+    dw = torch.zeros(25, 32, device=DEV)
+    db = torch.zeros(32, device=DEV)
+    nat.conv1_wgrad(x, dpool, pool, am, dw, db, B)
+    torch.cuda.synchronize()
+    assert rel_err(dw, wl.grad.reshape(25, 32)) < 2e-3
+    assert rel_err(db, bl.grad) < 2e-3
+
+
+def _conv2_inputs(B, seed):
+    torch.manual_seed(seed)
+    inp = bf(torch.rand(B, 14, 14, 32, device=DEV))
+    w = bf(torch.randn(5, 5, 32, 64, device=DEV) * 0.1)
+    b = torch.randn(64, device=DEV) * 0.1
+    return inp, w, b
+
+
+@pytest.mark.parametrize("ref_kernel", [True, False])
+@pytest.mark.parametrize("B", [128, 6])
+def test_conv2_fwd(nat, B, ref_kernel):
+    inp, w, b = _conv2_inputs(B, 6)
+    pool = torch.zeros(B, 7, 7, 64, device=DEV, dtype=torch.bfloat16)
+    am = torch.zeros(B, 7, 7, 64, device=DEV, dtype=torch.uint8)
+    nat.conv2_fwd(inp, w.reshape(800, 64), b, pool, am, B, ref=ref_kernel)
+    torch.cuda.synchronize()
+    pre = torch.relu(oracle.conv2d_same_nhwc(inp.float(), w.float()) + b)
+    ref = oracle.maxpool2x2_nhwc(pre)
+    assert rel_err(pool, ref) < 1e-2
+    # argmax points at a maximal element of its window
+    win = pre.reshape(B, 7, 2, 7, 2, 64).permute(0, 1, 3, 5, 2, 4).reshape(B, 7, 7, 64, 4)
+    picked = torch.gather(win, 4, am.long().unsqueeze(-1)).squeeze(-1)
+    assert (picked - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("ref_kernel", [True, False])
+@pytest.mark.parametrize("B", [128, 6])
+def test_conv2_dgrad(nat, B, ref_kernel):
+    inp, w, b = _conv2_inputs(B, 7)
+    dy = bf(torch.randn(B, 14, 14, 64, device=DEV))
+    xin = inp.float().requires_grad_(True)
+    (oracle.conv2d_same_nhwc(xin, w.float()) * dy.float()).sum().backward()
+    dx = torch.zeros(B, 14, 14, 32, device=DEV)
+    nat.conv2_dgrad(dy, w.reshape(800, 64), dx, B, ref=ref_kernel)
+    torch.cuda.synchronize()
+    assert rel_err(dx, xin.grad) < 2e-3
+
+
+@pytest.mark.parametrize("ref_kernel", [True, False])
+@pytest.mark.parametrize("B", [128, 6])
+def test_conv2_wgrad(nat, B, ref_kernel):
+    inp, w, b = _conv2_inputs(B, 8)
+    dy = bf(torch.randn(B, 14, 14, 64, device=DEV))
+    wl = w.float().requires_grad_(True)
+    (oracle.conv2d_same_nhwc(inp.float(), wl) * dy.float()).sum().backward()
+    dw = torch.zeros(800, 64, device=DEV)
+    nat.conv2_wgrad(inp, dy, dw, B, ref=ref_kernel)
+    torch.cuda.synchronize()
+    assert rel_err(dw, wl.grad.reshape(800, 64)) < 2e-3
+
+
+def test_pool2_bwd(nat):
+    torch.manual_seed(9)
+    B = 16
+    pre = torch.randn(B, 14, 14, 64, device=DEV)
+    act = torch.relu(pre).requires_grad_(True)
+    pooled = oracle.maxpool2x2_nhwc(act)
+    dpool = torch.randn(B, 7, 7, 64, device=DEV)
+    win = act.detach().reshape(B, 7, 2, 7, 2, 64).permute(0, 1, 3, 5, 2, 4).reshape(B, 7, 7, 64, 4)
+    am = win.argmax(dim=4).to(torch.uint8)
+    pool_bf = bf(pooled.detach())
+    dy = torch.empty(B, 14, 14, 64, device=DEV, dtype=torch.bfloat16)
+    db = torch.zeros(64, device=DEV)
+    nat.pool2_bwd(dpool, pool_bf, am, dy, db, B)
+    torch.cuda.synchronize()
+    g = dpool * (pooled.detach() > 0)
+    ref = torch.zeros(B, 7, 7, 64, 4, device=DEV).scatter_(4, am.long().unsqueeze(-1), g.unsqueeze(-1))
+    ref = ref.reshape(B, 7, 7, 64, 2, 2).permute(0, 1, 4, 2, 5, 3).reshape(B, 14, 14, 64)
+    assert rel_err(dy, ref) < 1e-2
+    assert rel_err(db, g.sum(dim=(0, 1, 2))) < 1e-3
+
+
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("keep_prob", [1.0, 0.75])
+def test_head_cnn_mode_matches_oracle(nat, keep_prob):
+    torch.manual_seed(10)
+    B, H = 128, 1024
+    pre = torch.randn(B, H, device=DEV) * 3
+    bias = torch.randn(H, device=DEV)
+    ow = torch.randn(H, 10, device=DEV) * 0.1
+    ob = torch.randn(10, device=DEV)
+    y = torch.eye(10, device=DEV)[torch.randint(0, 10, (B,), device=DEV)]
+    hid = torch.empty(B, H, device=DEV, dtype=torch.bfloat16)
+    dhid = torch.empty(B, H, device=DEV, dtype=torch.bfloat16)
+    dl = torch.empty(B, 10, device=DEV)
+    lr_ = torch.empty(B, device=DEV)
+    hit = torch.empty(B, device=DEV, dtype=torch.uint8)
+    mask = torch.ones(B, H, device=DEV, dtype=torch.uint8)
+    nat.head_rows(pre, None, bias, ow, ob, y, B, H, H, keep_prob, 123, 5, True, hid, dhid, dl, lr_, hit, mask)
+    dow = torch.empty(H, 10, device=DEV)
+    dhb = torch.empty(H, device=DEV)
+    dob = torch.empty(10, device=DEV)
+    sc = torch.empty(2, device=DEV)
+    nat.head_cols(hid, dhid, H, dl, lr_, hit, B, H, dow, dhb, dob, sc)
+    torch.cuda.synchronize()
+    if keep_prob < 1:
+        frac = mask.float().mean().item()
+        assert abs(frac - keep_prob) < 0.01
+    # oracle with the same mask
+    prel = pre.clone().requires_grad_(True)
+    owl, obl, bl = ow.clone().requires_grad_(True), ob.clone().requires_grad_(True), bias.clone().requires_grad_(True)
+    h = oracle.dropout_with_mask(torch.relu(prel + bl), mask.bool(), keep_prob)
+    logits = h @ owl + obl
+    loss = oracle.softmax_xent_mean(logits, y)
+    loss.backward()
+    assert abs(sc[0].item() - loss.item()) < 2e-2 * max(1.0, abs(loss.item()))
+    assert abs(sc[1].item() - oracle.accuracy(logits, y).item()) < 2.0 / B
+    assert rel_err(hid, h) < 1e-2
+    assert rel_err(dhid, prel.grad) < 2e-2
+    assert rel_err(dow, owl.grad) < 2e-2
+    assert rel_err(dob, obl.grad) < 1e-3
+    assert rel_err(dhb, bl.grad) < 2e-2
+
+
+def test_head_mlp_mode_and_eval(nat):
+    torch.manual_seed(11)
+    B, H, ld = 64, 100, 104
+    act = torch.zeros(B, ld, device=DEV, dtype=torch.bfloat16)
+    act[:, :H] = bf(torch.relu(torch.randn(B, H, device=DEV)))
+    ow = torch.randn(H, 10, device=DEV)
+    ob = torch.randn(10, device=DEV)
+    y = torch.eye(10, device=DEV)[torch.randint(0, 10, (B,), device=DEV)]
+    dhid = torch.zeros(B, ld, device=DEV, dtype=torch.bfloat16)
+    dl, lr_, hit = torch.empty(B, 10, device=DEV), torch.empty(B, device=DEV), torch.empty(B, device=DEV, dtype=torch.uint8)
+    nat.head_rows(None, act, None, ow, ob, y, B, H, ld, 1.0, 0, 0, True, None, dhid, dl, lr_, hit)
+    dow, dhb, dob, sc = torch.empty(H, 10, device=DEV), torch.empty(H, device=DEV), torch.empty(10, device=DEV), torch.empty(2, device=DEV)
+    nat.head_cols(act, dhid, ld, dl, lr_, hit, B, H, dow, dhb, dob, sc)
+    torch.cuda.synchronize()
+    a = act[:, :H].float().requires_grad_(True)
+    owl = ow.clone().requires_grad_(True)
+    logits = a @ owl + ob
+    loss = oracle.softmax_xent_mean(logits, y)
+    loss.backward()
+    assert abs(sc[0].item() - loss.item()) < 1e-3 * max(1.0, loss.item())
+    assert rel_err(dhid[:, :H], a.grad * (a.detach() > 0)) < 1e-2
+    assert rel_err(dow, owl.grad) < 1e-3
+    # eval: scalars only
+    sc2 = torch.zeros(2, device=DEV)
+    nat.head_rows(None, act, None, ow, ob, y, B, H, ld, 1.0, 0, 0, False, None, None, dl, lr_, hit)
+    nat.head_cols(None, None, ld, dl, lr_, hit, B, H, None, None, None, sc2)
+    torch.cuda.synchronize()
+    assert abs(sc2[0].item() - loss.item()) < 1e-3 * max(1.0, loss.item())
+    assert abs(sc2[1].item() - oracle.accuracy(logits, y).item()) < 1e-6
+
+
+def test_colsum_cast_random_normal(nat):
+    x = bf(torch.randn(128, 200, device=DEV))
+    out = torch.empty(200, device=DEV)
+    nat.colsum_bf16(x, 200, 128, 200, out)
+    src = torch.randn(7, 100, device=DEV)
+    dst = torch.full((7, 104), 3.0, device=DEV, dtype=torch.bfloat16)
+    nat.cast_bf16(src, dst, 7, 100, 100, 104)
+    r = torch.empty(3274634, device=DEV)
+    nat.random_normal(r, 42, 1.0)
+    r2 = torch.empty(1000, device=DEV)
+    nat.random_normal(r2, 42, 1.0)
+    torch.cuda.synchronize()
+    assert rel_err(out, x.float().sum(0)) < 1e-3
+    assert torch.equal(dst[:, :100], bf(src)) and torch.all(dst[:, 100:] == 0)
+    assert abs(r.mean().item()) < 5e-3 and abs(r.std().item() - 1.0) < 5e-3  # tf.random_normal: N(0,1) (m:186-195)
+    assert torch.equal(r[:1000], r2)  # deterministic in the seed
+    k = ((r - r.mean()) ** 4).mean().item() / r.var().item() ** 2
+    assert abs(k - 3.0) < 0.05
+
+
+def test_adam_apply_matches_tf_form_and_publishes_shadow(nat):
+    torch.manual_seed(12)
+    from tensorflow_distributed_b200.ops.native import Piece
+    n = 64 * 40 + 64 * 2  # piece A [40,64] with a flat shadow; piece B [1,100] padded to 104; tail pad
+    w0 = torch.randn(n, device=DEV)
+    w, m, v = w0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    shadow = torch.zeros(40 * 64 + 104, device=DEV, dtype=torch.bfloat16)
+    pieces = [Piece(0, 40 * 64, 64, 64, 0), Piece(40 * 64, 100, 100, 104, 40 * 64)]
+    slots = [torch.randn(n, device=DEV) for _ in range(3)]
+    ptrs = torch.tensor([s.data_ptr() for s in slots], dtype=torch.int64, device=DEV)
+    ctrl = torch.zeros(8, dtype=torch.int32, device=DEV)  # [0]=t [1]=scratch [2]=version [3]=global_step
+    ref = {"w": w0.clone().cpu()}
+    opt = oracle.TFAdam(0.01)
+    for step in range(3):
+        nat.adam_apply(w, m, v, shadow, ptrs, 3, 1.0 / 3, n, pieces, 0.01, ctrl[0:], None, ctrl[2:], ctrl[3:])
+        opt.apply(ref, {"w": (sum(s for s in slots) / 3).cpu()})
+    torch.cuda.synchronize()
+    assert torch.allclose(w.cpu(), ref["w"], atol=1e-5, rtol=1e-5)
+    assert ctrl[0].item() == 3 and ctrl[2].item() == 3 and ctrl[3].item() == 3
+    assert torch.equal(shadow[:40 * 64], bf(w[:40 * 64]))
+    assert torch.equal(shadow[40 * 64:40 * 64 + 100], bf(w[40 * 64:40 * 64 + 100]))
+
+
+def test_push_pull_single_gpu(nat):
+    src = [torch.randn(1000, device=DEV), torch.randn(4096 + 3, device=DEV)]
+    dst = [torch.zeros_like(s) for s in src]
+    ctrl = torch.zeros(4, dtype=torch.int32, device=DEV)
+    nat.push_multi([s.data_ptr() for s in src], [d.data_ptr() for d in dst], [s.numel() for s in src],
+                   [ctrl[0:].data_ptr(), ctrl[1:].data_ptr()], 0.5, ctrl[2:])
+    back = [torch.zeros_like(s) for s in src]
+    nat.pull_multi([d.data_ptr() for d in dst], [b.data_ptr() for b in back], [s.numel() for s in src],
+                   [ctrl[0:].data_ptr(), None], 1)
+    torch.cuda.synchronize()
+    for s, d, b in zip(src, dst, back):
+        assert torch.allclose(d, 0.5 * s) and torch.equal(d, b)
+    assert ctrl[0].item() == 1 and ctrl[1].item() == 1 and ctrl[2].item() == 0
