@@ -1,0 +1,129 @@
+"""Headline benchmark: MNIST-CNN training images/sec on N B200s (BASELINE.json metric).
+
+    python bench.py --gpus 1 --steps 50 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+One JSON line on rank 0.  `value` is device-timed (CUDA events per step, L2 flushed between steps, max over
+ranks); `e2e` goes through the public API (`engine.train_step(numpy_x, numpy_y, fetch_loss=True)`): pinned-host
+H2D of the inputs and a D2H of the loss every step.  Synthetic 28x28 data, random-init weights (reference init
+N(0,1), /root/reference/mnist_python_m.py:186-195), batch 128 per worker (m:70), Adam lr 0.01 (m:71), keep 0.75.
+
+--impl reference: the reference is six TensorFlow-1.x scripts with nothing installable and TensorFlow is not in
+this image (no network), so that arm reports itself unavailable.  --impl ddp is this repo's own second baseline:
+the same CNN in stock PyTorch (cuDNN/cuBLAS, autograd, torch.optim.Adam, DDP over NCCL when N > 1).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BASELINE_IMG_S_PER_REPLICA = 128.0 / 4.875  # BASELINE.md section 1 (derived from performance:2-6; unit assumed s)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._halt = index, [], threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def stop(self) -> dict:
+        self._halt.set()
+        self.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp"])
+    ap.add_argument("--model", default="cnn", choices=["cnn", "mlp"])
+    ap.add_argument("--hidden", type=int, default=8192)
+    ap.add_argument("--layers", type=int, default=4)
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--layout", default="colocated", choices=["colocated", "dedicated"])
+    ap.add_argument("--ps", type=int, default=0, help="ps shards (0: one per GPU when colocated, 1 when dedicated)")
+    ap.add_argument("--async", dest="async_mode", action="store_true")
+    ap.add_argument("--no-l2-flush", action="store_true")
+    ap.add_argument("--init-stddev", type=float, default=1.0)
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def main():
+    a = parse()
+    rank, world, local = dist_env()
+    if a.impl == "reference":
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "reference = 6 TensorFlow-1.x scripts (tf.app.flags, "
+                              "tf.train.Supervisor, tensorflow.examples.tutorials.mnist); tensorflow is not installed, "
+                              "not in /opt/wheelhouse and there is no network; /root/reference has no setup.py/pyproject "
+                              "so pip cannot install it either"}))
+        return 0
+    import torch
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device", "impl": a.impl}))
+        return 1
+    if a.gpus != world:
+        if world == 1 and a.gpus > 1:
+            # convenience: re-launch ourselves under torchrun
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(a.gpus),
+                   "--master-addr", "127.0.0.1", "--master-port", str(29400 + os.getpid() % 500), __file__] + sys.argv[1:]
+            return subprocess.call(cmd)
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (a.gpus, world))
+    torch.cuda.set_device(local)
+    if a.impl == "ddp":
+        from baseline.ddp_baseline import run_ddp
+        res = run_ddp(a, rank, world, local)
+    else:
+        from tensorflow_distributed_b200.benchmark import run_ours
+        res = run_ours(a, rank, world, local)
+    if rank == 0 and res is not None:
+        print(json.dumps(res))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,362 @@
+"""NativeEngine: the sm_100a execution engine (single GPU: one ps shard + one worker on the same device).
+
+What the reference delegates to ``tf.Session.run`` on a graph TF differentiated for it
+(``/root/reference/mnist_single.py:92-112``, ``/root/reference/mnist_python_m.py:202-222``) is spelled out here
+as an explicit forward + hand-written backward over the kernels of ``libtfd_b200.so``, captured once per
+(batch, mode) in a CUDA graph and replayed: one graph launch per training step, no host round trip inside.
+
+Precision policy: fp32 master weights, Adam slots and accumulators on the ps shard; bf16
+tensor-core operands (activations, and a bf16 shadow of the weights the ps publishes from inside the Adam
+kernel); fp32 gradients.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from .models.spec import ModelSpec
+from .ops import native as nat
+from .parallel.placement import Placement
+
+CTRL_T, CTRL_SCRATCH, CTRL_VERSION, CTRL_GSTEP, CTRL_ARRIVE, CTRL_PUSHBLK = 0, 1, 2, 3, 4, 5
+
+
+def _pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+def needs_shadow(spec: ModelSpec, name: str) -> bool:
+    """Tensors consumed by tensor-core kernels get a bf16 shadow; the rest are read in fp32."""
+    if spec.kind == "cnn":
+        return name in ("weights/wc2", "weights/wd1")
+    return name.startswith("weights/h")
+
+
+class ShardState:
+    """One parameter-server shard in HBM: fp32 arena + Adam slots + bf16 shadow + control words."""
+
+    def __init__(self, spec: ModelSpec, placement: Placement, shard: int, device, alloc=None):
+        self.spec, self.placement, self.shard, self.device = spec, placement, shard, device
+        n = placement.shard_sizes[shard]
+        self.n = n
+        alloc = alloc or (lambda numel, dtype: torch.zeros(numel, dtype=dtype, device=device))
+        self.w = alloc(n, torch.float32)
+        self.m = alloc(n, torch.float32)
+        self.v = alloc(n, torch.float32)
+        self.pieces: List[nat.Piece] = []
+        self.shadow_off: Dict[str, int] = {}
+        self.shadow_ld: Dict[str, int] = {}
+        off = 0
+        for p in placement.shard_pieces(shard):
+            if needs_shadow(spec, p.var):
+                ld = _pad8(p.cols)
+                self.pieces.append(nat.Piece(p.offset, p.numel, p.cols, ld, off))
+                self.shadow_off[p.var], self.shadow_ld[p.var] = off, ld
+                off += (p.row_end - p.row_start) * ld
+                off = (off + 63) // 64 * 64
+            else:
+                self.pieces.append(nat.Piece(p.offset, p.numel, p.cols, 0, 0))
+        self.shadow_n = max(off, 64)
+        self.shadow = alloc(self.shadow_n, torch.bfloat16)
+        self.ctrl = alloc(16, torch.int32)
+
+    def piece_of(self, var: str):
+        for p in self.placement.pieces[var]:
+            if p.shard == self.shard:
+                return p
+        return None
+
+    def view(self, arena: torch.Tensor, var: str) -> torch.Tensor:
+        p = self.piece_of(var)
+        return arena[p.offset:p.offset + p.numel].view(p.row_end - p.row_start, p.cols)
+
+    def shadow_view(self, var: str) -> torch.Tensor:
+        p = self.piece_of(var)
+        ld = self.shadow_ld[var]
+        o = self.shadow_off[var]
+        return self.shadow[o:o + (p.row_end - p.row_start) * ld].view(p.row_end - p.row_start, ld)
+
+    def publish_shadow(self) -> None:
+        """(Re)build the bf16 shadow from the fp32 arena (init / restore; steady state is done by the Adam kernel)."""
+        for var in self.shadow_off:
+            p = self.piece_of(var)
+            nat.cast_bf16(self.view(self.w, var), self.shadow_view(var), p.row_end - p.row_start, p.cols,
+                          p.cols, self.shadow_ld[var])
+
+
+class Workspace:
+    """Activations / gradients-of-activations for one batch size (all static: graph-capturable)."""
+
+    def __init__(self, spec: ModelSpec, B: int, device):
+        self.B = B
+        z = lambda *s, dtype=torch.float32: torch.zeros(*s, dtype=dtype, device=device)  # noqa: E731
+        self.x = z(B, 784)
+        self.y = z(B, 10)
+        self.x_host = torch.zeros(B, 784, dtype=torch.float32).pin_memory()
+        self.y_host = torch.zeros(B, 10, dtype=torch.float32).pin_memory()
+        self.scalars = z(2)
+        self.scalars_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        self.dlogits, self.loss_row = z(B, 10), z(B)
+        self.hit = z(B, dtype=torch.uint8)
+        if spec.kind == "cnn":
+            self.pool1 = z(B, 14, 14, 32, dtype=torch.bfloat16)
+            self.am1 = z(B, 14, 14, 32, dtype=torch.uint8)
+            self.pool2 = z(B, 7, 7, 64, dtype=torch.bfloat16)
+            self.am2 = z(B, 7, 7, 64, dtype=torch.uint8)
+            self.fc1acc = z(B, 1024)
+            self.hid = z(B, 1024, dtype=torch.bfloat16)
+            self.dhid = z(B, 1024, dtype=torch.bfloat16)
+            self.dpool2 = z(B, 3136)
+            self.dy2 = z(B, 14, 14, 64, dtype=torch.bfloat16)
+            self.dpool1 = z(B, 14, 14, 32)
+            self.keep_mask = None
+        else:
+            dims = [784] + list(spec.hidden)
+            self.act = [z(B, _pad8(d), dtype=torch.bfloat16) for d in dims]
+            self.dact = [None] + [z(B, _pad8(d), dtype=torch.bfloat16) for d in dims[1:]]
+        self.graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
+
+
+class NativeEngine:
+    """Single-GPU engine: parameters live in one ShardState on the same device as the worker kernels."""
+
+    name = "native-sm100a"
+
+    def __init__(self, spec: ModelSpec, learning_rate: float = 0.01, seed: int = 0, init_stddev: float = 1.0,
+                 device: Optional[str] = None, use_graphs: bool = True, conv2_ref: bool = False):
+        if not torch.cuda.is_available():
+            raise nat.NativeError("NativeEngine needs a CUDA device (backend=cpu selects the oracle engine)")
+        nat.lib()
+        self.spec = spec
+        self.device = torch.device(device or ("cuda:%d" % torch.cuda.current_device()))
+        torch.cuda.set_device(self.device)
+        nat.set_device(self.device.index or 0)
+        self.lr, self.seed = learning_rate, seed
+        self.use_graphs, self.conv2_ref = use_graphs, conv2_ref
+        self.placement = Placement(spec, 1)
+        self.shard = ShardState(spec, self.placement, 0, self.device)
+        self.grad = torch.zeros(self.shard.n, dtype=torch.float32, device=self.device)
+        self.slot_ptrs = torch.tensor([self.grad.data_ptr()], dtype=torch.int64, device=self.device)
+        self.ws: Dict[int, Workspace] = {}
+        self.init_variables(seed, init_stddev)
+
+    # ---- variables -------------------------------------------------------------------------
+    def init_variables(self, seed: int, stddev: float) -> None:
+        """tf.global_variables_initializer(): every parameter ~ N(0, stddev) from the device Philox stream."""
+        s = self.shard
+        for i, v in enumerate(self.spec.variables):
+            nat.random_normal(s.view(s.w, v.name), (seed << 8) + i, stddev)
+        s.m.zero_(); s.v.zero_(); s.ctrl.zero_()
+        s.publish_shadow()
+        torch.cuda.synchronize(self.device)
+
+    @property
+    def global_step(self) -> int:
+        return int(self.shard.ctrl[CTRL_GSTEP].item())
+
+    @global_step.setter
+    def global_step(self, v: int) -> None:
+        self.shard.ctrl[CTRL_GSTEP] = int(v)
+
+    def P(self, name: str) -> torch.Tensor:
+        return self.shard.view(self.shard.w, name)
+
+    def S(self, name: str) -> torch.Tensor:
+        return self.shard.shadow_view(name)
+
+    def G(self, name: str) -> torch.Tensor:
+        return self.shard.view(self.grad, name)
+
+    def get_params(self) -> Dict[str, torch.Tensor]:
+        return {v.name: self.P(v.name).detach().cpu().reshape(v.shape).clone() for v in self.spec.variables}
+
+    def set_params(self, params: Dict[str, torch.Tensor]) -> None:
+        for v in self.spec.variables:
+            self.P(v.name).copy_(params[v.name].to(self.device, torch.float32).reshape(self.P(v.name).shape))
+        self.shard.publish_shadow()
+        torch.cuda.synchronize(self.device)
+
+    def get_grads(self) -> Dict[str, torch.Tensor]:
+        return {v.name: self.G(v.name).detach().cpu().reshape(v.shape).clone() for v in self.spec.variables}
+
+    def get_adam_state(self) -> dict:
+        s = self.shard
+        t = int(s.ctrl[CTRL_T].item())
+        return {"t": t, "beta1_power": 0.9 ** t, "beta2_power": 0.999 ** t,
+                "m": {v.name: s.view(s.m, v.name).cpu().reshape(v.shape).clone() for v in self.spec.variables},
+                "v": {v.name: s.view(s.v, v.name).cpu().reshape(v.shape).clone() for v in self.spec.variables}}
+
+    def set_adam_state(self, sd: dict) -> None:
+        s = self.shard
+        for v in self.spec.variables:
+            s.view(s.m, v.name).copy_(sd["m"][v.name].to(self.device).reshape(s.view(s.m, v.name).shape))
+            s.view(s.v, v.name).copy_(sd["v"][v.name].to(self.device).reshape(s.view(s.v, v.name).shape))
+        s.ctrl[CTRL_T] = int(sd["t"])
+
+    def synchronize(self) -> None:
+        torch.cuda.synchronize(self.device)
+
+    def workspace(self, B: int) -> Workspace:
+        if B not in self.ws:
+            self.ws[B] = Workspace(self.spec, B, self.device)
+        return self.ws[B]
+
+    # ---- kernel sequences ------------------------------------------------------------------
+    def _splits(self, mtiles: int, ntiles: int, kblocks: int, cap: int = 16) -> int:
+        return max(1, min(cap, kblocks, 148 // max(1, mtiles * ntiles)))
+
+    def _cnn_forward(self, ws: Workspace, training: bool, keep_prob: float, mask_out=None) -> None:
+        B = ws.B
+        zeros = [ws.fc1acc]
+        if training:
+            zeros += [ws.dpool2, self.G("weights/wc1"), self.G("biases/bc1"), self.G("weights/wc2"),
+                      self.G("biases/bc2")]
+        nat.zero_multi(zeros)
+        nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, B)
+        nat.conv2_fwd(ws.pool1, self.S("weights/wc2"), self.P("biases/bc2"), ws.pool2, ws.am2, B, ref=self.conv2_ref)
+        mt = (B + 127) // 128
+        nat.gemm_bf16(ws.pool2.view(B, 3136), 0, self.S("weights/wd1"), 1, B, 1024, 3136, ws.fc1acc,
+                      mode=nat.EPI_ATOMIC_F32, bn=128, splits=self._splits(mt, 8, 49))
+        nat.head_rows(ws.fc1acc, None, self.P("biases/bd1"), self.P("weights/out"), self.P("biases/out"), ws.y, B,
+                      1024, 1024, keep_prob if training else 1.0, self.seed, 0, training, ws.hid,
+                      ws.dhid if training else None, ws.dlogits, ws.loss_row, ws.hit, mask_out,
+                      step_ptr=self.shard.ctrl[CTRL_T:] if training else None)
+
+    def _cnn_backward(self, ws: Workspace) -> None:
+        B = ws.B
+        nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, self.G("weights/out"),
+                      self.G("biases/bd1"), self.G("biases/out"), ws.scalars)
+        # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
+        nat.gemm_bf16(ws.pool2.view(B, 3136), 1, ws.dhid, 1, 3136, 1024, B, self.G("weights/wd1"),
+                      mode=nat.EPI_STORE_F32, bn=128)
+        # fc1 dgrad: dpool2[B,3136] = dhid wd1^T    (wd1 read K-major in place)
+        mt = (B + 127) // 128
+        nat.gemm_bf16(ws.dhid, 0, self.S("weights/wd1"), 0, B, 3136, 1024, ws.dpool2, mode=nat.EPI_ATOMIC_F32, bn=64,
+                      splits=self._splits(mt, 49, 16, cap=3))
+        nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"), B)
+        nat.conv2_wgrad(ws.pool1, ws.dy2, self.G("weights/wc2"), B, ref=self.conv2_ref)
+        nat.conv2_dgrad(ws.dy2, self.S("weights/wc2"), ws.dpool1, B, ref=self.conv2_ref)
+        nat.conv1_wgrad(ws.x, ws.dpool1, ws.pool1, ws.am1, self.G("weights/wc1"), self.G("biases/bc1"), B)
+
+    def _mlp_forward(self, ws: Workspace, training: bool) -> None:
+        B, dims = ws.B, [784] + list(self.spec.hidden)
+        L = len(dims) - 1
+        nat.cast_bf16(ws.x, ws.act[0], B, 784, 784, 784)
+        for l in range(1, L + 1):
+            H, K = dims[l], dims[l - 1]
+            nat.gemm_bf16(ws.act[l - 1], 0, self.S("weights/h%d" % l), 1, B, H, K, ws.act[l],
+                          mode=nat.EPI_BIAS_RELU_BF16, bn=64, bias=self.P("biases/b%d" % l))
+        H = dims[L]
+        nat.head_rows(None, ws.act[L], None, self.P("weights/out"), self.P("biases/out"), ws.y, B, H, _pad8(H), 1.0,
+                      self.seed, 0, training, None, ws.dact[L] if training else None, ws.dlogits, ws.loss_row, ws.hit)
+
+    def _mlp_backward(self, ws: Workspace) -> None:
+        B, dims = ws.B, [784] + list(self.spec.hidden)
+        L = len(dims) - 1
+        H = dims[L]
+        nat.head_cols(ws.act[L], ws.dact[L], _pad8(H), ws.dlogits, ws.loss_row, ws.hit, B, H, self.G("weights/out"),
+                      self.G("biases/b%d" % L), self.G("biases/out"), ws.scalars)
+        for l in range(L, 0, -1):
+            H, K = dims[l], dims[l - 1]
+            nat.gemm_bf16(ws.act[l - 1], 1, ws.dact[l], 1, K, H, B, self.G("weights/h%d" % l), mode=nat.EPI_STORE_F32,
+                          bn=128 if H >= 128 else 64)
+            if l > 1:
+                nat.gemm_bf16(ws.dact[l], 0, self.S("weights/h%d" % l), 0, B, K, H, ws.dact[l - 1],
+                              mode=nat.EPI_RELUMASK_BF16, bn=64, relu_mask=ws.act[l - 1])
+                nat.colsum_bf16(ws.dact[l - 1], _pad8(K), B, K, self.G("biases/b%d" % (l - 1)))
+
+    def _apply(self) -> None:
+        s = self.shard
+        nat.adam_apply(s.w, s.m, s.v, s.shadow, self.slot_ptrs, 1, 1.0, s.n, s.pieces, self.lr, s.ctrl[CTRL_T:], None,
+                       s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:])
+
+    def _sequence(self, ws: Workspace, mode: str, keep_prob: float, mask_out=None) -> None:
+        training = mode in ("train", "grads")
+        if self.spec.kind == "cnn":
+            self._cnn_forward(ws, training, keep_prob, mask_out)
+            if training:
+                self._cnn_backward(ws)
+        else:
+            self._mlp_forward(ws, training)
+            if training:
+                self._mlp_backward(ws)
+        if not training:
+            nat.head_cols(None, None, 0, ws.dlogits, ws.loss_row, ws.hit, ws.B, 1, None, None, None, ws.scalars)
+        if mode == "train":
+            self._apply()
+
+    def _run(self, ws: Workspace, mode: str, keep_prob: float = 1.0, mask_out=None) -> None:
+        """Launch one step: eager the first time (sets kernel attributes), then capture + replay a CUDA graph."""
+        key = (mode, round(float(keep_prob), 6))
+        if not self.use_graphs or mask_out is not None:
+            self._sequence(ws, mode, keep_prob, mask_out)
+            return
+        g = ws.graphs.get(key)
+        if g is None:
+            if key not in getattr(ws, "_warm", set()):
+                ws._warm = getattr(ws, "_warm", set()) | {key}
+                self._sequence(ws, mode, keep_prob)
+                return
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            before = nat.launch_count
+            with torch.cuda.graph(g):
+                self._sequence(ws, mode, keep_prob)
+            ws.graphs[key] = g
+            ws.graph_kernels = getattr(ws, "graph_kernels", {})
+            ws.graph_kernels[key] = nat.launch_count - before
+            nat.launch_count = before  # capture records, it does not execute
+        g.replay()
+        nat.launch_count += ws.graph_kernels[key]
+
+    # ---- public API: the fetches the reference asks a session for ---------------------------
+    def load_batch(self, ws: Workspace, x, y) -> None:
+        """feed_dict: host numpy -> pinned staging -> device (X7 in SURVEY.md 2.4)."""
+        if isinstance(x, torch.Tensor) and x.is_cuda:
+            ws.x.copy_(x.reshape(ws.B, 784)); ws.y.copy_(y.reshape(ws.B, 10))
+            return
+        ws.x_host.copy_(torch.as_tensor(np.ascontiguousarray(x) if isinstance(x, np.ndarray) else x).reshape(ws.B, 784))
+        ws.y_host.copy_(torch.as_tensor(np.ascontiguousarray(y) if isinstance(y, np.ndarray) else y).reshape(ws.B, 10))
+        ws.x.copy_(ws.x_host, non_blocking=True)
+        ws.y.copy_(ws.y_host, non_blocking=True)
+
+    def _fetch_scalars(self, ws: Workspace):
+        ws.scalars_host.copy_(ws.scalars, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(ws.scalars_host[0]), float(ws.scalars_host[1])
+
+    def train_step(self, x, y, keep_prob: float = 0.75, fetch_loss: bool = False):
+        """sess.run(train_op): forward, backward, Adam apply.  Returns the loss only when asked (a D2H sync)."""
+        ws = self.workspace(len(x))
+        self.load_batch(ws, x, y)
+        self._run(ws, "train", keep_prob)
+        return self._fetch_scalars(ws)[0] if fetch_loss else None
+
+    def train_step_resident(self, ws: Workspace, keep_prob: float = 0.75) -> None:
+        """Step on the batch already resident in ws.x / ws.y (device-timed benchmark loop)."""
+        self._run(ws, "train", keep_prob)
+
+    def eval_loss(self, x, y) -> float:
+        ws = self.workspace(len(x))
+        self.load_batch(ws, x, y)
+        self._run(ws, "eval", 1.0)
+        return self._fetch_scalars(ws)[0]
+
+    def eval_accuracy(self, x, y) -> float:
+        ws = self.workspace(len(x))
+        self.load_batch(ws, x, y)
+        self._run(ws, "eval", 1.0)
+        return self._fetch_scalars(ws)[1]
+
+    def loss_and_grads(self, x, y, keep_prob: float = 1.0):
+        """Forward + backward without the apply (tests; cluster workers).  Returns (loss, grads, keep_mask)."""
+        ws = self.workspace(len(x))
+        self.load_batch(ws, x, y)
+        mask = None
+        if self.spec.kind == "cnn" and keep_prob < 1.0:
+            mask = torch.ones(ws.B, 1024, dtype=torch.uint8, device=self.device)
+        self._sequence(ws, "grads", keep_prob, mask)
+        loss, _ = self._fetch_scalars(ws)
+        return loss, self.get_grads(), mask
