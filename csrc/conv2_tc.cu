@@ -196,38 +196,36 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 // GEMM view per tap group g (4 taps): M = 4*32 (tap_local, ci), N = 64 co, K = 128 pixels of the tile.
 //   A: four [128 px][32 ci] SW64 tiles (one TMA box per tap) read MN-major, stacked along M through LBO
 //   B: the [128 px][64 co] SW128 dy tile read MN-major
-// 7 accumulator groups x 64 columns = 448 TMEM columns; they persist over all pixel tiles of the CTA and are
-// reduced across CTAs with red.global.add.v4.f32.
+// grid = (pixel chunks, 7 tap groups): a CTA owns ONE 128x64 accumulator (64 TMEM columns) over its share of
+// the pixel tiles, so only `chunks` CTAs ever red.add to the same dW element (7x fewer atomics than splitting
+// by pixels alone).
 // ------------------------------------------------------------------------------------------------
 constexpr int kWgStages = 4;
-constexpr int kWgStageBytes = 4 * 8192;
-constexpr int kWgSmem = kWgStages * kWgStageBytes + 2 * 16384 + 1024 + 512;
+constexpr int kWgStageBytes = 16384 + 4 * 8192;  // dy tile + up to four tap tiles
+constexpr int kWgSmem = kWgStages * kWgStageBytes + 1024 + 512;
 
 __global__ void __launch_bounds__(kThreads, 1)
 conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmDy,
                       float* __restrict__ dw, int num_tiles) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* abuf = smem;
-  uint8_t* dybuf = smem + kWgStages * kWgStageBytes;
-  uint64_t* a_full = reinterpret_cast<uint64_t*>(dybuf + 2 * 16384);
-  uint64_t* a_empty = a_full + kWgStages;
-  uint64_t* dy_full = a_empty + kWgStages;  // [2]
-  uint64_t* dy_empty = dy_full + 2;         // [2]
-  uint64_t* acc_full = dy_empty + 2;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
+  uint64_t* empty = full + kWgStages;
+  uint64_t* acc_full = empty + kWgStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.y;
+  const int ntap = (g == 6) ? 1 : 4;
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmIn);
     prefetch_tmap(&tmDy);
-    for (int s = 0; s < kWgStages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&dy_full[i], 1); mbar_init(&dy_empty[i], 1); }
+    for (int s = 0; s < kWgStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
     fence_barrier_init();
     fence_proxy_async_smem();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 1) tmem_alloc(tmem_slot, 64);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -235,24 +233,19 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
 
   if (warp == 0) {
     if (lane == 0) {
-      int stage = 0, it = 0;
+      int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int nb = tile / 7, hp = tile % 7;
-        const int db = it & 1;
-        mbar_wait(&dy_empty[db], ((it >> 1) & 1) ^ 1);
-        mbar_arrive_expect_tx(&dy_full[db], 16384);
-        tma_load_4d(dybuf + db * 16384, &tmDy, &dy_full[db], 0, 0, 2 * hp, nb * 4);
-        for (int g = 0; g < 7; ++g) {
-          const int ntap = (g == 6) ? 1 : 4;
-          mbar_wait(&a_empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&a_full[stage], ntap * 8192);
-          for (int tl = 0; tl < ntap; ++tl) {
-            const int tap = g * 4 + tl, kh = tap / 5, kw = tap % 5;
-            tma_load_4d(abuf + stage * kWgStageBytes + tl * 8192, &tmIn, &a_full[stage], 0, kw - 2, 2 * hp + kh - 2, nb * 4);
-          }
-          if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        uint8_t* st = smem + stage * kWgStageBytes;
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full[stage], 16384 + ntap * 8192);
+        tma_load_4d(st, &tmDy, &full[stage], 0, 0, 2 * hp, nb * 4);
+        for (int tl = 0; tl < ntap; ++tl) {
+          const int tap = g * 4 + tl, kh = tap / 5, kw = tap % 5;
+          tma_load_4d(st + 16384 + tl * 8192, &tmIn, &full[stage], 0, kw - 2, 2 * hp + kh - 2, nb * 4);
         }
+        if (++stage == kWgStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -261,43 +254,34 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
       int stage = 0, it = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int db = it & 1;
-        mbar_wait(&dy_full[db], (it >> 1) & 1);
+        mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const uint32_t sdy = smem_u32(dybuf + db * 16384);
-        for (int g = 0; g < 7; ++g) {
-          mbar_wait(&a_full[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(abuf + stage * kWgStageBytes);
+        const uint32_t sdy = smem_u32(smem + stage * kWgStageBytes);
+        const uint32_t sa = sdy + 16384;
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint64_t da = make_smem_desc(sa + ks * 1024, 8192, 512, kSwz64);    // 16 px = two 512 B atoms
-            const uint64_t dbb = make_smem_desc(sdy + ks * 2048, 8192, 1024, kSwz128); // 16 px = two 1024 B atoms
-            umma_bf16(tmem_base + g * 64, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
-          }
-          umma_commit(&a_empty[stage]);
-          if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint64_t da = make_smem_desc(sa + ks * 1024, 8192, 512, kSwz64);     // 16 px = two 512 B atoms
+          const uint64_t dbb = make_smem_desc(sdy + ks * 2048, 8192, 1024, kSwz128);  // 16 px = two 1024 B atoms
+          umma_bf16(tmem_base, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
         }
-        umma_commit(&dy_empty[db]);
+        umma_commit(&empty[stage]);
+        if (++stage == kWgStages) { stage = 0; phase ^= 1; }
       }
       umma_commit(acc_full);
     }
   } else {
     const int q = warp & 3;
+    const int tap = g * 4 + q;
     mbar_wait(acc_full, 0);
     tc_fence_after();
 #pragma unroll 1
-    for (int g = 0; g < 7; ++g) {
-      const int tap = g * 4 + q;
-#pragma unroll 1
-      for (int j = 0; j < 4; ++j) {
-        float v[16];
-        tmem_ld16(tmem_base + g * 64 + j * 16 + ((uint32_t)(q * 32) << 16), v);
-        if (tap < 25) {
-          float* o = dw + ((long long)(tap * 32 + lane)) * 64 + j * 16;
+    for (int j = 0; j < 4; ++j) {
+      float v[16];
+      tmem_ld16(tmem_base + j * 16 + ((uint32_t)(q * 32) << 16), v);
+      if (tap < 25) {
+        float* o = dw + ((long long)(tap * 32 + lane)) * 64 + j * 16;
 #pragma unroll
-          for (int i = 0; i < 16; i += 4) red_add_v4_f32(o + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
-        }
+        for (int i = 0; i < 16; i += 4) red_add_v4_f32(o + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
       }
     }
   }
@@ -305,7 +289,7 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    tmem_dealloc(tmem_base, 64);
   }
 }
 
@@ -375,8 +359,10 @@ extern "C" int tfd_conv2_wgrad(const void* in, const void* dy, float* dw, int B,
     attr = true;
   }
   const int tiles = ((B + 3) / 4) * 7;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv2_wgrad_tc_kernel<<<grid, kThreads, kWgSmem, static_cast<cudaStream_t>(stream)>>>(tmIn, tmDy, dw, tiles);
+  int chunks = num_sms() / 7;
+  if (chunks > tiles) chunks = tiles;
+  if (chunks < 1) chunks = 1;
+  conv2_wgrad_tc_kernel<<<dim3(chunks, 7), kThreads, kWgSmem, static_cast<cudaStream_t>(stream)>>>(tmIn, tmDy, dw, tiles);
   TFD_LAUNCH_CHECK();
   return 0;
 }

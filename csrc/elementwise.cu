@@ -28,10 +28,12 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 }
 __device__ __forceinline__ float u01(uint32_t x) { return ((float)x + 0.5f) * 2.3283064365386963e-10f; }
 
-__global__ void random_normal_kernel(float* __restrict__ out, long long n, unsigned long long seed, float stddev) {
+__global__ void random_normal_kernel(float* __restrict__ out, long long n, unsigned long long seed, float stddev,
+                                     long long off4) {
   const long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // 4 values per thread
   if (i4 * 4 >= n) return;
-  uint4 r = philox4x32_10(make_uint4((uint32_t)i4, (uint32_t)(i4 >> 32), 0x5eed, 0),
+  const long long c4 = i4 + off4;  // counter = global index of the 4-element group (shard-independent stream)
+  uint4 r = philox4x32_10(make_uint4((uint32_t)c4, (uint32_t)(c4 >> 32), 0x5eed, 0),
                           make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
   float z[4];
   const float r0 = sqrtf(-2.f * logf(u01(r.x))), r1 = sqrtf(-2.f * logf(u01(r.z)));
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
 }
 
 // conv1 filter gradient: pool/ReLU backward folded in (only the arg-max position of each 2x2 window carries
-// gradient).  grid B, 256 threads: lane = channel, 8 pixel groups; block-level reduce, then atomics.
+// gradient).  grid (B, 2 pixel halves), 256 threads: lane = channel, 8 pixel groups; block-level reduce, then atomics.
 __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
                                                           const bf16* __restrict__ pool, const unsigned char* __restrict__ amax,
                                                           float* __restrict__ dw, float* __restrict__ db) {
@@ -115,7 +117,8 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
 #pragma unroll
   for (int t = 0; t < 25; ++t) acc[t] = 0.f;
   float accb = 0.f;
-  for (int pix = grp; pix < 196; pix += 8) {
+  const int pbeg = blockIdx.y * 98;
+  for (int pix = pbeg + grp; pix < pbeg + 98; pix += 8) {
     const int ph = pix / 14, pw = pix % 14;
     const long long idx = (((long long)n * 14 + ph) * 14 + pw) * 32 + c;
     float g = dpool[idx];
@@ -142,40 +145,56 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
   }
 }
 
-// pool2 + ReLU backward: dpool fp32 [B,7,7,64] -> dy bf16 [B,14,14,64]; db[64] += sum.
-__global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict__ dpool, const bf16* __restrict__ pool,
-                                                        const unsigned char* __restrict__ amax, bf16* __restrict__ dy,
-                                                        float* __restrict__ db, long long total) {
+// pool2 + ReLU backward: dpool fp32 [nsplit][B,7,7,64] (split-K partials of the fc1 dgrad, summed here)
+// -> dy bf16 [B,14,14,64]; db[64] += sum.  Block = 64 channels x 4 pixel lanes, 16 pooled pixels per block.
+__global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict__ dpool, int nsplit, long long split_stride,
+                                                        const bf16* __restrict__ pool, const unsigned char* __restrict__ amax,
+                                                        bf16* __restrict__ dy, float* __restrict__ db, long long npix) {
   __shared__ float red[256];
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  float g = 0.f;
-  if (idx < total) {
-    const int c = (int)(idx & 63);
-    const long long p = idx >> 6;
+  const int c = threadIdx.x & 63, pl = threadIdx.x >> 6;
+  float gsum = 0.f;
+  float g[4];
+  float pv[4];
+  int am[4];
+  long long pp[4];
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    pp[it] = (long long)blockIdx.x * 16 + it * 4 + pl;
+    const long long idx = pp[it] * 64 + c;
+    g[it] = 0.f; pv[it] = 0.f; am[it] = 0;
+    if (pp[it] < npix) {
+      for (int sp = 0; sp < nsplit; ++sp) g[it] += dpool[sp * split_stride + idx];
+      pv[it] = __bfloat162float(pool[idx]);
+      am[it] = amax[idx];
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    if (pp[it] >= npix) continue;
+    const long long p = pp[it];
+    const float gg = pv[it] > 0.f ? g[it] : 0.f;
     const int pw = (int)(p % 7), ph = (int)((p / 7) % 7);
     const long long n = p / 49;
-    g = dpool[idx];
-    if (!(__bfloat162float(pool[idx]) > 0.f)) g = 0.f;
-    const int a = amax[idx];
-    const bf16 gb = __float2bfloat16(g), z = __float2bfloat16(0.f);
+    const bf16 gb = __float2bfloat16(gg), z = __float2bfloat16(0.f);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const long long o = (((n * 14 + 2 * ph + (q >> 1)) * 14) + 2 * pw + (q & 1)) * 64 + c;
-      dy[o] = (q == a) ? gb : z;
+      dy[o] = (q == am[it]) ? gb : z;
     }
+    gsum += gg;
   }
-  red[threadIdx.x] = g;
+  red[threadIdx.x] = gsum;
   __syncthreads();
-  if (threadIdx.x < 64) {
+  if (threadIdx.x < 64)
     atomicAdd(db + threadIdx.x, red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192]);
-  }
 }
 
 // ------------------------------------------------------------------------------------------------
 // head: rows phase
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-head_rows_kernel(const float* __restrict__ pre, const bf16* __restrict__ hid_in, const float* __restrict__ hid_bias,
+head_rows_kernel(const float* __restrict__ pre, int pre_nsplit, long long pre_split_stride,
+                 const bf16* __restrict__ hid_in, const float* __restrict__ hid_bias,
                  const float* __restrict__ out_w, const float* __restrict__ out_b, const float* __restrict__ labels,
                  int B, int H, long long ld_h, float keep_prob, unsigned long long seed, unsigned long long step_base,
                  const unsigned* __restrict__ step_ptr, int training, bf16* __restrict__ hid_out, bf16* __restrict__ dhid, float* __restrict__ dlogits,
@@ -189,7 +208,10 @@ head_rows_kernel(const float* __restrict__ pre, const bf16* __restrict__ hid_in,
   for (int k = tid; k < H; k += 256) {
     float a;
     if (pre) {
-      a = fmaxf(pre[(long long)r * H + k] + hid_bias[k], 0.f);
+      a = hid_bias[k];
+#pragma unroll 8
+      for (int sp = 0; sp < pre_nsplit; ++sp) a += pre[sp * pre_split_stride + (long long)r * H + k];
+      a = fmaxf(a, 0.f);
       if (keep_prob < 1.f) {
         const unsigned long long e = (unsigned long long)r * H + k;
         const uint4 rn = philox4x32_10(make_uint4((uint32_t)e, (uint32_t)(e >> 32), (uint32_t)step, (uint32_t)(step >> 32)),
@@ -273,31 +295,46 @@ head_rows_kernel(const float* __restrict__ pre, const bf16* __restrict__ hid_in,
   }
 }
 
-// head: columns phase
+// head: columns phase.  32 columns per block: lane = column, warp = row group; the 8 row groups are reduced
+// through shared memory in a fixed order (deterministic, no atomics).
 __global__ void __launch_bounds__(256)
 head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, long long ld_h,
                  const float* __restrict__ dlogits, const float* __restrict__ loss_row,
                  const unsigned char* __restrict__ hit, int B, int H, float* __restrict__ d_out_w,
                  float* __restrict__ d_hid_bias, float* __restrict__ d_out_b, float* __restrict__ scalars) {
-  extern __shared__ float dls[];  // [B][10]
-  const int tid = threadIdx.x;
+  extern __shared__ float dls[];  // [B][10], then [8][11][32] partials
+  float* part = dls + B * 10;
+  const int tid = threadIdx.x, lane = tid & 31, wv = tid >> 5;
   for (int i = tid; i < B * 10; i += 256) dls[i] = dlogits[i];
   __syncthreads();
-  const int k = blockIdx.x * 256 + tid;
-  if (hid != nullptr && k < H) {
+  const int k = blockIdx.x * 32 + lane;
+  if (hid != nullptr) {
     float acc[10];
 #pragma unroll
     for (int j = 0; j < 10; ++j) acc[j] = 0.f;
     float sb = 0.f;
-    for (int r = 0; r < B; ++r) {
-      const float hv = __bfloat162float(hid[(long long)r * ld_h + k]);
-      sb += __bfloat162float(dhid[(long long)r * ld_h + k]);
+    if (k < H) {
+      for (int r = wv; r < B; r += 8) {
+        const float hv = __bfloat162float(hid[(long long)r * ld_h + k]);
+        sb += __bfloat162float(dhid[(long long)r * ld_h + k]);
 #pragma unroll
-      for (int j = 0; j < 10; ++j) acc[j] = fmaf(hv, dls[r * 10 + j], acc[j]);
+        for (int j = 0; j < 10; ++j) acc[j] = fmaf(hv, dls[r * 10 + j], acc[j]);
+      }
     }
 #pragma unroll
-    for (int j = 0; j < 10; ++j) d_out_w[(long long)k * 10 + j] = acc[j];
-    d_hid_bias[k] = sb;
+    for (int j = 0; j < 10; ++j) part[(wv * 11 + j) * 32 + lane] = acc[j];
+    part[(wv * 11 + 10) * 32 + lane] = sb;
+    __syncthreads();
+    for (int i = tid; i < 11 * 32; i += 256) {
+      const int j = i >> 5, c = i & 31, kk = blockIdx.x * 32 + c;
+      float sum = 0.f;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) sum += part[(g * 11 + j) * 32 + c];
+      if (kk < H) {
+        if (j < 10) d_out_w[(long long)kk * 10 + j] = sum;
+        else d_hid_bias[kk] = sum;
+      }
+    }
   }
   if (blockIdx.x == 0) {
     if (tid < 10 && d_out_b) {
@@ -305,15 +342,19 @@ head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, lo
       for (int r = 0; r < B; ++r) s += dls[r * 10 + tid];
       d_out_b[tid] = s;
     }
-    if (tid == 32) {
+    if (wv == 1) {
       float s = 0.f;
-      for (int r = 0; r < B; ++r) s += loss_row[r];
-      scalars[0] = s / (float)B;
+      for (int r = lane; r < B; r += 32) s += loss_row[r];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) scalars[0] = s / (float)B;
     }
-    if (tid == 64) {
-      int s = 0;
-      for (int r = 0; r < B; ++r) s += hit[r];
-      scalars[1] = (float)s / (float)B;
+    if (wv == 2) {
+      float s = 0.f;
+      for (int r = lane; r < B; r += 32) s += (float)hit[r];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) scalars[1] = s / (float)B;
     }
   }
 }
@@ -432,9 +473,11 @@ __global__ void zero_multi_kernel(const __grid_constant__ ZeroTable t) {
 
 #define ST(s) static_cast<cudaStream_t>(s)
 
-extern "C" int tfd_random_normal(float* out, long long n, unsigned long long seed, float stddev, void* stream) {
+extern "C" int tfd_random_normal(float* out, long long n, unsigned long long seed, float stddev, long long elem_offset,
+                                 void* stream) {
+  TFD_REQUIRE(elem_offset % 4 == 0, "random_normal: element offset %lld not a multiple of 4", elem_offset);
   const long long n4 = (n + 3) / 4;
-  random_normal_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, ST(stream)>>>(out, n, seed, stddev);
+  random_normal_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, ST(stream)>>>(out, n, seed, stddev, elem_offset / 4);
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -456,21 +499,21 @@ extern "C" int tfd_conv1_fwd(const float* x, const float* w, const float* b, voi
 
 extern "C" int tfd_conv1_wgrad(const float* x, const float* dpool, const void* pool_out, const unsigned char* argmax,
                                float* dw, float* db, int B, void* stream) {
-  conv1_wgrad_kernel<<<B, 256, 0, ST(stream)>>>(x, dpool, (const bf16*)pool_out, argmax, dw, db);
+  conv1_wgrad_kernel<<<dim3(B, 2), 256, 0, ST(stream)>>>(x, dpool, (const bf16*)pool_out, argmax, dw, db);
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int tfd_pool2_bwd(const float* dpool, const void* pool_out, const unsigned char* argmax, void* dy, float* db,
-                             int B, void* stream) {
-  const long long total = (long long)B * 49 * 64;
-  pool2_bwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ST(stream)>>>(dpool, (const bf16*)pool_out, argmax, (bf16*)dy,
-                                                                          db, total);
+extern "C" int tfd_pool2_bwd(const float* dpool, int nsplit, long long split_stride, const void* pool_out,
+                             const unsigned char* argmax, void* dy, float* db, int B, void* stream) {
+  const long long npix = (long long)B * 49;
+  pool2_bwd_kernel<<<(unsigned)((npix + 15) / 16), 256, 0, ST(stream)>>>(dpool, nsplit < 1 ? 1 : nsplit, split_stride,
+                                                                       (const bf16*)pool_out, argmax, (bf16*)dy, db, npix);
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int tfd_head_rows(const float* pre_f32, const void* hid_bf16, const float* hid_bias, const float* out_w,
+extern "C" int tfd_head_rows(const float* pre_f32, int pre_nsplit, long long pre_split_stride, const void* hid_bf16, const float* hid_bias, const float* out_w,
                              const float* out_b, const float* labels, int B, int H, long long ld_h, float keep_prob,
                              unsigned long long seed, unsigned long long step, const unsigned* step_ptr, int training,
                              void* hid_out, void* dhid, float* dlogits, float* loss_row, unsigned char* hit,
@@ -485,7 +528,8 @@ extern "C" int tfd_head_rows(const float* pre_f32, const void* hid_bf16, const f
     TFD_CUDA_CHECK(cudaFuncSetAttribute(head_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  head_rows_kernel<<<B, 256, smem, ST(stream)>>>(pre_f32, (const bf16*)hid_bf16, hid_bias, out_w, out_b, labels, B, H, ld_h,
+  head_rows_kernel<<<B, 256, smem, ST(stream)>>>(pre_f32, pre_nsplit < 1 ? 1 : pre_nsplit, pre_split_stride,
+                                                 (const bf16*)hid_bf16, hid_bias, out_w, out_b, labels, B, H, ld_h,
                                                  keep_prob, seed, step, step_ptr, training, (bf16*)hid_out, (bf16*)dhid, dlogits,
                                                  loss_row, hit, keep_mask_out);
   TFD_LAUNCH_CHECK();
@@ -495,9 +539,14 @@ extern "C" int tfd_head_rows(const float* pre_f32, const void* hid_bf16, const f
 extern "C" int tfd_head_cols(const void* hid, const void* dhid, long long ld_h, const float* dlogits,
                              const float* loss_row, const unsigned char* hit, int B, int H, float* d_out_w,
                              float* d_hid_bias, float* d_out_b, float* scalars, void* stream) {
-  const size_t smem = (size_t)B * 10 * sizeof(float);
-  TFD_REQUIRE(smem <= 48 * 1024, "head_cols: batch %d too large for the dlogits tile", B);
-  const int blocks = hid ? (H + 255) / 256 : 1;
+  const size_t smem = ((size_t)B * 10 + 8 * 11 * 32) * sizeof(float);
+  TFD_REQUIRE(smem <= 200 * 1024, "head_cols: batch %d too large for the dlogits tile", B);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    TFD_CUDA_CHECK(cudaFuncSetAttribute(head_cols_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  const int blocks = hid ? (H + 31) / 32 : 1;
   head_cols_kernel<<<blocks, 256, smem, ST(stream)>>>((const bf16*)hid, (const bf16*)dhid, ld_h, dlogits, loss_row, hit, B,
                                                       H, d_out_w, d_hid_bias, d_out_b, scalars);
   TFD_LAUNCH_CHECK();

@@ -9,9 +9,16 @@
 //   wgrad    dW = x^T dy    A = x [K=batch, M] MN-major  B = dy [K=batch, N] MN-major
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
-// warps 2..5 = epilogue (TMEM -> registers -> global).  Operand pointers may be peer-mapped (NVLink) addresses:
-// TMA pulls B tiles straight from the owning ps GPU (fused parameter pull), and the epilogue may store /
-// red.add to a peer staging buffer (fused gradient push).
+// warps 2..5 = epilogue (TMEM -> registers -> global).
+//
+// Fused parameter pull / gradient push: the weight matrix is row-sharded over up to 8
+// parameter-server GPUs.  The kernel takes one tensor map (or output pointer) per shard segment and addresses
+// the shards' peer-mapped memory directly:
+//   TFD_SEG_B_K   forward: B's K rows are sharded; K-block kb is TMA-loaded from the shard that owns it, after
+//                 the producer has seen that shard's parameter version flag (acquire, system scope)
+//   TFD_SEG_B_N   dgrad:   B read as [N,K]; the N tile is TMA-loaded from its owner shard
+//   TFD_SEG_OUT_M wgrad:   the output rows are sharded; the epilogue stores each tile straight into this
+//                 worker's staging slot on the owner shard (no local gradient copy, no separate push of it)
 #include "../include/tfd_b200.h"
 #include "tfd_common.cuh"
 
@@ -22,6 +29,21 @@ using namespace tfd;
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kThreads = 192;
+constexpr int kMaxSeg = TFD_MAX_SEG;
+
+struct TmapArray {
+  CUtensorMap m[kMaxSeg];
+};
+
+struct SegInfo {
+  int mode;                         // TFD_SEG_*
+  int nseg;
+  int bound[kMaxSeg + 1];           // segment row boundaries (rows of the sharded dimension)
+  float* out_ptr[kMaxSeg];          // TFD_SEG_OUT_M
+  const uint32_t* wait_flag[kMaxSeg];
+  uint32_t wait_value;
+  const uint32_t* wait_value_ptr;   // optional device word added to wait_value (the worker's step counter)
+};
 
 struct GemmParams {
   int M, N, K;          // logical problem
@@ -35,8 +57,7 @@ struct GemmParams {
   const float* bias;            // [N] or null
   const __nv_bfloat16* mask;    // relu mask source (same shape as out), or null
   long long ld_mask;
-  const uint32_t* wait_flag;    // optional: spin until *wait_flag >= wait_value before touching B (pull gate)
-  uint32_t wait_value;
+  long long split_stride;       // STORE_F32 split-K: plane z at out_f32 + z*split_stride
 };
 
 template <int BN>
@@ -46,9 +67,18 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+__device__ __forceinline__ int find_seg(const SegInfo& sg, int row) {
+  int s = 0;
+#pragma unroll
+  for (int i = 1; i < kMaxSeg; ++i)
+    if (i < sg.nseg && row >= sg.bound[i]) s = i;
+  return s;
+}
+
 template <int A_MN, int B_MN, int BN>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ TmapArray tmBs, GemmParams p,
+               const __grid_constant__ SegInfo sg) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -66,7 +96,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
-    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmBs.m[0]);
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -84,9 +114,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      if (p.wait_flag) spin_until_ge(p.wait_flag, p.wait_value, "gemm pull gate");
       int stage = 0;
       uint32_t phase = 0;
+      int gated = -1;  // last shard whose version flag this producer has already seen
+      const uint32_t want = sg.wait_value + (sg.wait_value_ptr ? *sg.wait_value_ptr : 0u);
+      // dgrad: the whole N tile comes from one shard
+      int seg_n = 0, nrow0 = n0;
+      if (sg.mode == TFD_SEG_B_N) {
+        seg_n = find_seg(sg, n0);
+        nrow0 = n0 - sg.bound[seg_n];
+        if (sg.wait_flag[seg_n]) spin_until_ge(sg.wait_flag[seg_n], want, "gemm pull gate (N)");
+      } else if (sg.mode != TFD_SEG_B_K && sg.wait_flag[0]) {
+        spin_until_ge(sg.wait_flag[0], want, "gemm pull gate");
+      }
       for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * C::kStageBytes;
@@ -100,10 +140,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tma_load_2d(sa + 8192, &tmA, &full_bar[stage], m0 + 64, k0);
         }
         if (B_MN == 0) {
-          tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);            // box [BN rows(n), 64 k]
+          tma_load_2d(sb, &tmBs.m[seg_n], &full_bar[stage], k0, nrow0);  // box [BN rows(n), 64 k]
         } else {
+          int s = 0, krow = k0;
+          if (sg.mode == TFD_SEG_B_K) {
+            s = find_seg(sg, k0);
+            krow = k0 - sg.bound[s];
+            if (s != gated) {
+              if (sg.wait_flag[s]) spin_until_ge(sg.wait_flag[s], want, "gemm pull gate (K)");
+              gated = s;
+            }
+          }
 #pragma unroll
-          for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmB, &full_bar[stage], n0 + c * 64, k0);
+          for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmBs.m[s], &full_bar[stage], n0 + c * 64, krow);
         }
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
@@ -137,6 +186,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===== epilogue: warps 2..5 own TMEM lane quadrants (warp % 4) =====
     const int q = warp & 3;
     const int row = m0 + q * 32 + lane;
+    float* out_f32 = p.out_f32;
+    int out_row = row;
+    if (sg.mode == TFD_SEG_OUT_M) {  // sharded output: this tile lives in one shard's staging slot
+      const int s = find_seg(sg, m0);
+      out_f32 = sg.out_ptr[s];
+      out_row = row - sg.bound[s];
+    }
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const bool row_ok = row < p.M;
@@ -166,7 +222,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (i < ncols && !(__bfloat162float(mrow[i]) > 0.f)) v[i] = 0.f;
       }
       if (p.mode == TFD_EPI_STORE_F32) {
-        float* o = p.out_f32 + (long long)row * p.ld_out + col0;
+        float* o = out_f32 + (long long)blockIdx.z * p.split_stride + (long long)out_row * p.ld_out + col0;
         if (ncols == 16 && vec_ok) {
 #pragma unroll
           for (int i = 0; i < 16; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
@@ -174,7 +230,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int i = 0; i < ncols; ++i) o[i] = v[i];
         }
       } else if (p.mode == TFD_EPI_ATOMIC_F32) {
-        float* o = p.out_f32 + (long long)row * p.ld_out + col0;
+        float* o = out_f32 + (long long)out_row * p.ld_out + col0;
         if (ncols == 16 && vec_ok) {
 #pragma unroll
           for (int i = 0; i < 16; i += 4) red_add_v4_f32(o + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
@@ -206,7 +262,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 }
 
 template <int A_MN, int B_MN, int BN>
-int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t stream) {
+int launch(const CUtensorMap& tmA, const TmapArray& tmBs, const GemmParams& p, const SegInfo& sg, cudaStream_t stream) {
   using C = Cfg<BN>;
   auto kern = gemm_tc_kernel<A_MN, B_MN, BN>;
   static bool attr_set = false;
@@ -215,50 +271,95 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, 
     attr_set = true;
   }
   dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, p.splits);
-  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, p);
+  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmBs, p, sg);
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
 }  // namespace
 
-// a_mn / b_mn: operand major-ness as stored (see header).  A: a_mn=0 -> [M,K] ld=lda ; a_mn=1 -> [K,M].
-// B: b_mn=0 -> [N,K] ; b_mn=1 -> [K,N].
-extern "C" int tfd_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M,
-                             int N, int K, int bn, int splits, int mode, float alpha, void* out, long long ld_out,
-                             const float* bias, const void* relu_mask, long long ld_mask, const unsigned* wait_flag,
-                             unsigned wait_value, void* stream) {
+// Segmented form: the sharded operand is given as nseg pieces.  seg_rows[nseg+1] are the row boundaries of the
+// sharded dimension (K for TFD_SEG_B_K, N for TFD_SEG_B_N, M for TFD_SEG_OUT_M; multiples of 128, first = 0).
+// B_ptrs[s] points at shard s's rows (row 0 of the piece); out_ptrs[s] likewise for TFD_SEG_OUT_M.
+extern "C" int tfd_gemm_bf16_seg(const void* A, long long lda, int a_mn, const void* const* B_ptrs, long long ldb,
+                                 int b_mn, int M, int N, int K, int bn, int splits, int mode, float alpha, void* out,
+                                 long long ld_out, const float* bias, const void* relu_mask, long long ld_mask,
+                                 long long split_stride, int seg_mode, int nseg, const int* seg_rows,
+                                 void* const* out_ptrs, const unsigned* const* wait_flags, unsigned wait_value,
+                                 const unsigned* wait_value_ptr, void* stream) {
   TFD_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
   TFD_REQUIRE(bn == 64 || bn == 128 || bn == 256, "gemm: bn must be 64/128/256, got %d", bn);
+  TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSeg, "gemm: %d segments (max %d)", nseg, kMaxSeg);
+  TFD_REQUIRE(seg_mode == TFD_SEG_NONE || seg_rows != nullptr, "gemm: segmented call without boundaries");
+  TFD_REQUIRE(seg_mode != TFD_SEG_B_K || b_mn == 1, "gemm: TFD_SEG_B_K needs B stored [K,N]");
+  TFD_REQUIRE(seg_mode != TFD_SEG_B_N || b_mn == 0, "gemm: TFD_SEG_B_N needs B stored [N,K]");
+  TFD_REQUIRE(seg_mode != TFD_SEG_OUT_M || (mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32),
+              "gemm: TFD_SEG_OUT_M needs an fp32 epilogue");
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
   p.kblocks = (K + BK - 1) / BK;
   p.splits = splits < 1 ? 1 : (splits > p.kblocks ? p.kblocks : splits);
-  TFD_REQUIRE(p.splits == 1 || mode == TFD_EPI_ATOMIC_F32, "gemm: split-K needs the atomic epilogue");
+  TFD_REQUIRE(p.splits == 1 || mode == TFD_EPI_ATOMIC_F32 || (mode == TFD_EPI_STORE_F32 && split_stride > 0),
+              "gemm: split-K needs the atomic epilogue or fp32 partial planes (split_stride)");
+  TFD_REQUIRE(p.splits == 1 || bias == nullptr, "gemm: bias with split-K would be added once per split");
+  p.split_stride = split_stride;
   p.mode = mode; p.alpha = alpha;
   p.out_f32 = (mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32) ? static_cast<float*>(out) : nullptr;
   p.out_bf16 = p.out_f32 ? nullptr : static_cast<__nv_bfloat16*>(out);
   p.ld_out = ld_out; p.bias = bias;
   p.mask = static_cast<const __nv_bfloat16*>(relu_mask); p.ld_mask = ld_mask;
   TFD_REQUIRE(mode != TFD_EPI_RELUMASK_BF16 || relu_mask, "gemm: relu-mask epilogue without a mask");
-  p.wait_flag = wait_flag; p.wait_value = wait_value;
 
-  CUtensorMap tmA, tmB;
+  SegInfo sg;
+  memset(&sg, 0, sizeof(sg));
+  sg.mode = seg_mode; sg.nseg = nseg; sg.wait_value = wait_value; sg.wait_value_ptr = wait_value_ptr;
+  for (int s = 0; s < nseg; ++s) {
+    sg.bound[s] = seg_rows ? seg_rows[s] : 0;
+    sg.out_ptr[s] = out_ptrs ? static_cast<float*>(out_ptrs[s]) : nullptr;
+    sg.wait_flag[s] = wait_flags ? wait_flags[s] : nullptr;
+    if (seg_mode != TFD_SEG_NONE) {
+      TFD_REQUIRE(sg.bound[s] % 128 == 0, "gemm: segment boundary %d not a multiple of 128", sg.bound[s]);
+      TFD_REQUIRE(s == 0 || sg.bound[s] > sg.bound[s - 1], "gemm: segment boundaries must increase");
+    }
+  }
+  sg.bound[nseg] = seg_rows ? seg_rows[nseg] : 0;
+  TFD_REQUIRE(seg_mode != TFD_SEG_B_N || bn <= 128, "gemm: TFD_SEG_B_N needs bn <= 128 (an N tile must not straddle shards)");
+
+  CUtensorMap tmA;
+  TmapArray tmBs;
   int rc;
   if (a_mn == 0) rc = tfd_make_tmap_2d_bf16(&tmA, A, M, K, lda, BM, BK, 128);
   else           rc = tfd_make_tmap_2d_bf16(&tmA, A, K, M, lda, BK, 64, 128);
   if (rc) return rc;
-  if (b_mn == 0) rc = tfd_make_tmap_2d_bf16(&tmB, B, N, K, ldb, bn, BK, 128);
-  else           rc = tfd_make_tmap_2d_bf16(&tmB, B, K, N, ldb, BK, 64, 128);
-  if (rc) return rc;
+  const bool seg_b = (seg_mode == TFD_SEG_B_K || seg_mode == TFD_SEG_B_N);
+  for (int s = 0; s < (seg_b ? nseg : 1); ++s) {
+    const int rows = seg_b ? (sg.bound[s + 1] - sg.bound[s]) : (b_mn == 0 ? N : K);
+    TFD_REQUIRE(rows > 0, "gemm: empty segment %d", s);
+    if (b_mn == 0) rc = tfd_make_tmap_2d_bf16(&tmBs.m[s], B_ptrs[s], rows, K, ldb, bn, BK, 128);
+    else           rc = tfd_make_tmap_2d_bf16(&tmBs.m[s], B_ptrs[s], rows, N, ldb, BK, 64, 128);
+    if (rc) return rc;
+  }
+  for (int s = (seg_b ? nseg : 1); s < kMaxSeg; ++s) tmBs.m[s] = tmBs.m[0];
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-#define TFD_DISPATCH(AM, BMj)                                              \
-  if (a_mn == AM && b_mn == BMj) {                                         \
-    if (bn == 64) return launch<AM, BMj, 64>(tmA, tmB, p, st);             \
-    if (bn == 128) return launch<AM, BMj, 128>(tmA, tmB, p, st);           \
-    return launch<AM, BMj, 256>(tmA, tmB, p, st);                          \
+#define TFD_DISPATCH(AM, BMj)                                                  \
+  if (a_mn == AM && b_mn == BMj) {                                             \
+    if (bn == 64) return launch<AM, BMj, 64>(tmA, tmBs, p, sg, st);            \
+    if (bn == 128) return launch<AM, BMj, 128>(tmA, tmBs, p, sg, st);          \
+    return launch<AM, BMj, 256>(tmA, tmBs, p, sg, st);                         \
   }
   TFD_DISPATCH(0, 0) TFD_DISPATCH(0, 1) TFD_DISPATCH(1, 0) TFD_DISPATCH(1, 1)
 #undef TFD_DISPATCH
   TFD_REQUIRE(false, "gemm: bad major flags %d %d", a_mn, b_mn);
+}
+
+// a_mn / b_mn: operand major-ness as stored (see header).  A: a_mn=0 -> [M,K] ld=lda ; a_mn=1 -> [K,M].
+// B: b_mn=0 -> [N,K] ; b_mn=1 -> [K,N].
+extern "C" int tfd_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M,
+                             int N, int K, int bn, int splits, int mode, float alpha, void* out, long long ld_out,
+                             const float* bias, const void* relu_mask, long long ld_mask, long long split_stride,
+                             const unsigned* wait_flag, unsigned wait_value, void* stream) {
+  const void* bp[1] = {B};
+  const unsigned* wf[1] = {wait_flag};
+  return tfd_gemm_bf16_seg(A, lda, a_mn, bp, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
+                           ld_mask, split_stride, TFD_SEG_NONE, 1, nullptr, nullptr, wf, wait_value, nullptr, stream);
 }

@@ -22,7 +22,7 @@ struct PieceTable {
 
 struct AdamArgs {
   float* w; float* m; float* v; bf16* shadow;
-  const float* const* slots;
+  const float* slots[TFD_MAX_SLOTS];  // by value: no dependent pointer load in front of the gradient loads
   int num_slots;
   float scale;
   long long n;
@@ -34,41 +34,58 @@ struct AdamArgs {
 };
 
 __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __grid_constant__ PieceTable pt) {
-  __shared__ float s_lr_t;
-  __shared__ unsigned s_t;
-  if (threadIdx.x == 0) {
-    const unsigned t = a.t_counter[0] + 1;  // this update's 1-based index
-    if (a.wait_counter) spin_until_ge(a.wait_counter, (unsigned)a.num_slots * t, "adam: gradient arrivals");
-    s_t = t;
-    const double b1t = pow((double)a.beta1, (double)t), b2t = pow((double)a.beta2, (double)t);
-    s_lr_t = (float)((double)a.lr * sqrt(1.0 - b2t) / (1.0 - b1t));
+  // Every thread derives the step index and lr_t itself (one broadcast load + a few SFU ops): no block barrier
+  // and no serial prologue in front of the streaming loop.  Only one thread per block waits for the arrivals.
+  const unsigned t = a.t_counter[0] + 1;  // this update's 1-based index
+  if (a.wait_counter) {
+    if (threadIdx.x == 0) spin_until_ge(a.wait_counter, (unsigned)a.num_slots * t, "adam: gradient arrivals");
+    __syncthreads();
   }
-  __syncthreads();
-  const float lr_t = s_lr_t;
-  const long long n4 = a.n >> 2;
-  for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += (long long)gridDim.x * blockDim.x) {
-    const long long i = i4 << 2;
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int r = 0; r < a.num_slots; ++r) {
-      const float4 x = *reinterpret_cast<const float4*>(a.slots[r] + i);
-      g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-    }
-    float gv[4] = {g.x * a.scale, g.y * a.scale, g.z * a.scale, g.w * a.scale};
-    float4 w4 = *reinterpret_cast<float4*>(a.w + i);
-    float4 m4 = *reinterpret_cast<float4*>(a.m + i);
-    float4 v4 = *reinterpret_cast<float4*>(a.v + i);
-    float wv[4] = {w4.x, w4.y, w4.z, w4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
+  // 1 - beta^t through expm1 keeps full relative accuracy for small t (where beta^t is close to 1)
+  const float om_b1t = -expm1f((float)t * logf(a.beta1)), om_b2t = -expm1f((float)t * logf(a.beta2));
+  const float lr_t = a.lr * sqrtf(om_b2t) / om_b1t;
+  // 8 elements per thread per iteration; every load is issued before the first use (memory-level parallelism)
+  const long long n8 = a.n >> 3;
+  for (long long i8 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i8 < n8; i8 += (long long)gridDim.x * blockDim.x) {
+    const long long i = i8 << 3;
+    float4 w4[2], m4[2], v4[2], g4[2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int h = 0; h < 2; ++h) {
+      w4[h] = *reinterpret_cast<const float4*>(a.w + i + 4 * h);
+      m4[h] = *reinterpret_cast<const float4*>(a.m + i + 4 * h);
+      v4[h] = *reinterpret_cast<const float4*>(a.v + i + 4 * h);
+      g4[h] = *reinterpret_cast<const float4*>(a.slots[0] + i + 4 * h);
+    }
+    for (int r = 1; r < a.num_slots; ++r) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const float4 x = *reinterpret_cast<const float4*>(a.slots[r] + i + 4 * h);
+        g4[h].x += x.x; g4[h].y += x.y; g4[h].z += x.z; g4[h].w += x.w;
+      }
+    }
+    float wv[8], mv[8], vv[8], gv[8];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      wv[4 * h] = w4[h].x; wv[4 * h + 1] = w4[h].y; wv[4 * h + 2] = w4[h].z; wv[4 * h + 3] = w4[h].w;
+      mv[4 * h] = m4[h].x; mv[4 * h + 1] = m4[h].y; mv[4 * h + 2] = m4[h].z; mv[4 * h + 3] = m4[h].w;
+      vv[4 * h] = v4[h].x; vv[4 * h + 1] = v4[h].y; vv[4 * h + 2] = v4[h].z; vv[4 * h + 3] = v4[h].w;
+      gv[4 * h] = g4[h].x * a.scale; gv[4 * h + 1] = g4[h].y * a.scale;
+      gv[4 * h + 2] = g4[h].z * a.scale; gv[4 * h + 3] = g4[h].w * a.scale;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
       mv[j] = a.beta1 * mv[j] + (1.f - a.beta1) * gv[j];
       vv[j] = a.beta2 * vv[j] + (1.f - a.beta2) * gv[j] * gv[j];
       wv[j] -= lr_t * mv[j] / (sqrtf(vv[j]) + a.eps);  // TF form: epsilon outside the bias correction
     }
-    *reinterpret_cast<float4*>(a.w + i) = make_float4(wv[0], wv[1], wv[2], wv[3]);
-    *reinterpret_cast<float4*>(a.m + i) = make_float4(mv[0], mv[1], mv[2], mv[3]);
-    *reinterpret_cast<float4*>(a.v + i) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      *reinterpret_cast<float4*>(a.w + i + 4 * h) = make_float4(wv[4 * h], wv[4 * h + 1], wv[4 * h + 2], wv[4 * h + 3]);
+      *reinterpret_cast<float4*>(a.m + i + 4 * h) = make_float4(mv[4 * h], mv[4 * h + 1], mv[4 * h + 2], mv[4 * h + 3]);
+      *reinterpret_cast<float4*>(a.v + i + 4 * h) = make_float4(vv[4 * h], vv[4 * h + 1], vv[4 * h + 2], vv[4 * h + 3]);
+    }
     if (a.shadow) {
-      // pieces are 64-element aligned in the arena, so one float4 lies in one piece
+      // pieces are 64-element aligned in the arena, so the 8 elements lie in one piece
       for (int q = 0; q < pt.n; ++q) {
         const tfd_piece_t& pc = pt.p[q];
         if (i >= pc.arena_off && i < pc.arena_off + pc.numel) {
@@ -76,10 +93,11 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
             const long long e0 = i - pc.arena_off;
             if (pc.ld_shadow == pc.cols) {
               bf16* d = a.shadow + pc.shadow_off + e0;
-              *reinterpret_cast<uint2*>(d) = make_uint2(pack_bf16x2(wv[0], wv[1]), pack_bf16x2(wv[2], wv[3]));
+              *reinterpret_cast<uint4*>(d) = make_uint4(pack_bf16x2(wv[0], wv[1]), pack_bf16x2(wv[2], wv[3]),
+                                                        pack_bf16x2(wv[4], wv[5]), pack_bf16x2(wv[6], wv[7]));
             } else {
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
+              for (int j = 0; j < 8; ++j) {
                 const long long e = e0 + j;
                 if (e < pc.numel)
                   a.shadow[pc.shadow_off + (e / pc.cols) * pc.ld_shadow + (e % pc.cols)] = __float2bfloat16(wv[j]);
@@ -98,10 +116,10 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
     const unsigned done = atomicAdd(&a.t_counter[1], 1u);
     if (done == gridDim.x - 1) {
       a.t_counter[1] = 0;
-      a.t_counter[0] = s_t;
+      a.t_counter[0] = t;
       if (a.global_step) *a.global_step = *a.global_step + 1;
       __threadfence_system();
-      if (a.version_flag) st_release_sys_u32(a.version_flag, s_t);
+      if (a.version_flag) st_release_sys_u32(a.version_flag, t);
     }
   }
 }
@@ -119,7 +137,8 @@ struct PushTable {
 };
 
 // grid (blocks_per_seg, nseg)
-__global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushTable t, float scale, unsigned* block_counter) {
+__global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushTable t, float scale, unsigned* block_counter,
+                                                   unsigned* local_step) {
   const PushSeg s = t.seg[blockIdx.y];
   const long long n4 = s.n >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
@@ -137,6 +156,7 @@ __global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushT
       *block_counter = 0;
       __threadfence_system();
       for (int k = 0; k < t.narrive; ++k) atom_add_release_sys_u32(t.arrive[k], 1u);
+      if (local_step) *local_step = *local_step + 1;
     }
   }
 }
@@ -152,8 +172,10 @@ struct PullTable {
   int nseg;
 };
 
-__global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullTable t, unsigned want) {
+__global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullTable t, unsigned want_base,
+                                                   const unsigned* want_ptr) {
   const PullSeg s = t.seg[blockIdx.y];
+  const unsigned want = want_base + (want_ptr ? *want_ptr : 0u);
   if (s.version) {
     if (threadIdx.x == 0) spin_until_ge(s.version, want, "pull: parameter version");
     __syncthreads();
@@ -173,16 +195,20 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
                               float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
                               float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                               unsigned* version_flag, unsigned* global_step, void* stream) {
-  TFD_REQUIRE(n % 4 == 0, "adam: arena length %lld not a multiple of 4", n);
+  TFD_REQUIRE(n % 8 == 0, "adam: arena length %lld not a multiple of 8", n);
   TFD_REQUIRE(num_pieces <= kMaxPieces, "adam: too many pieces (%d)", num_pieces);
   TFD_REQUIRE(num_slots >= 1, "adam: need at least one gradient slot");
   PieceTable pt;
   pt.n = num_pieces;
   for (int i = 0; i < num_pieces; ++i) pt.p[i] = pieces[i];
-  AdamArgs a{w, m, v, static_cast<bf16*>(shadow), slots, num_slots, scale, n, lr, beta1, beta2, eps,
-             t_counter, wait_counter, version_flag, global_step};
-  long long blocks = (n / 4 + 255) / 256;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  TFD_REQUIRE(num_slots <= TFD_MAX_SLOTS, "adam: at most %d gradient slots", TFD_MAX_SLOTS);
+  AdamArgs a;
+  a.w = w; a.m = m; a.v = v; a.shadow = static_cast<bf16*>(shadow);
+  for (int i = 0; i < TFD_MAX_SLOTS; ++i) a.slots[i] = i < num_slots ? slots[i] : nullptr;
+  a.num_slots = num_slots; a.scale = scale; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+  a.t_counter = t_counter; a.wait_counter = wait_counter; a.version_flag = version_flag; a.global_step = global_step;
+  long long blocks = (n / 8 + 255) / 256;
+  if (blocks > 148 * 3) blocks = 148 * 3;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
   adam_apply_kernel<<<(unsigned)blocks, 256, 0, ST(stream)>>>(a, pt);
   TFD_LAUNCH_CHECK();
   return 0;
@@ -191,7 +217,8 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
 /* Multi-segment push: segs[i] = {src, dst, n}; after every segment is written the last block adds 1 to each
  * arrive counter.  (tfd_push_grads is the single-segment convenience form.) */
 extern "C" int tfd_push_multi(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
-                              unsigned* const* arrive, int narrive, float scale, unsigned* block_counter, void* stream) {
+                              unsigned* const* arrive, int narrive, float scale, unsigned* block_counter,
+                              unsigned* local_step, void* stream) {
   TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSegs && narrive <= kMaxSegs, "push: bad segment count %d/%d", nseg, narrive);
   PushTable t;
   t.nseg = nseg; t.narrive = narrive;
@@ -205,7 +232,7 @@ extern "C" int tfd_push_multi(const void* const* srcs, void* const* dsts, const 
   long long bx = (maxn / 4 + 255) / 256;
   if (bx < 1) bx = 1;
   if (bx > 148) bx = 148;
-  push_kernel<<<dim3((unsigned)bx, nseg), 256, 0, ST(stream)>>>(t, scale, block_counter);
+  push_kernel<<<dim3((unsigned)bx, nseg), 256, 0, ST(stream)>>>(t, scale, block_counter, local_step);
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -216,13 +243,15 @@ extern "C" int tfd_push_grads(const float* src, float* dst, long long n, float s
   void* d[1] = {dst};
   long long ns[1] = {n};
   unsigned* a[1] = {arrive_counter};
-  return tfd_push_multi(s, d, ns, 1, a, arrive_counter ? 1 : 0, scale, block_counter, stream);
+  return tfd_push_multi(s, d, ns, 1, a, arrive_counter ? 1 : 0, scale, block_counter, nullptr, stream);
 }
 
 extern "C" int tfd_pull_multi(const void* const* srcs, void* const* dsts, const long long* ns,
-                              const unsigned* const* versions, int nseg, unsigned want_version, void* stream) {
+                              const unsigned* const* versions, int nseg, unsigned want_version,
+                              const unsigned* want_ptr, void* stream) {
   TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSegs, "pull: bad segment count %d", nseg);
   PullTable t;
+  memset(&t, 0, sizeof(t));
   t.nseg = nseg;
   long long maxn = 0;
   for (int i = 0; i < nseg; ++i) {
@@ -232,7 +261,7 @@ extern "C" int tfd_pull_multi(const void* const* srcs, void* const* dsts, const 
   long long bx = (maxn / 4 + 255) / 256;
   if (bx < 1) bx = 1;
   if (bx > 64) bx = 64;
-  pull_kernel<<<dim3((unsigned)bx, nseg), 256, 0, ST(stream)>>>(t, want_version);
+  pull_kernel<<<dim3((unsigned)bx, nseg), 256, 0, ST(stream)>>>(t, want_version, want_ptr);
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -243,7 +272,7 @@ extern "C" int tfd_pull_params(const float* src, float* dst, long long n, const 
   void* d[1] = {dst};
   long long ns[1] = {n};
   const unsigned* v[1] = {version_flag};
-  return tfd_pull_multi(s, d, ns, v, 1, version, stream);
+  return tfd_pull_multi(s, d, ns, v, 1, version, nullptr, stream);
 }
 
 // ---- symmetric heap over cudaIpc ----

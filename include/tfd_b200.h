@@ -29,12 +29,28 @@ int tfd_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, siz
  * a_mn=0: A stored [M,K] (K contiguous); a_mn=1: A stored [K,M].  b_mn=0: B stored [N,K]; b_mn=1: B stored [K,N].
  * Leading dimensions in elements, multiples of 8.  A/B may be peer-mapped addresses (fused parameter pull);
  * `out` may be a peer-mapped staging buffer (fused gradient push).  wait_flag (optional): the TMA producer
- * spins until *wait_flag >= wait_value before loading (parameter-version gate).
+ * spins until *wait_flag >= wait_value before loading (parameter-version gate).  Split-K: with the atomic
+ * epilogue every split red.adds into `out`; with TFD_EPI_STORE_F32 split z stores its partial plane at
+ * out + z*split_stride (the consumer sums the planes: no atomics, deterministic).
  * Replaces tf.matmul at mnist_python_m.py:121,127 and the matmul gradients generated at m:222. */
 int tfd_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M, int N, int K,
                   int bn, int splits, int mode, float alpha, void* out, long long ld_out, const float* bias,
-                  const void* relu_mask, long long ld_mask, const unsigned* wait_flag, unsigned wait_value,
-                  void* stream);
+                  const void* relu_mask, long long ld_mask, long long split_stride, const unsigned* wait_flag,
+                  unsigned wait_value, void* stream);
+
+/* Sharded form (fused parameter pull / gradient push over NVLink peer memory).  The sharded dimension is split
+ * at seg_rows[0..nseg] (multiples of 128, seg_rows[0] = 0): TFD_SEG_B_K shards B's K rows (forward),
+ * TFD_SEG_B_N shards B read as [N,K] (dgrad), TFD_SEG_OUT_M shards the output rows (wgrad: every tile is stored
+ * straight into out_ptrs[shard], i.e. this worker's staging slot on the owning ps GPU).  B_ptrs[s] / out_ptrs[s]
+ * point at row 0 of shard s's piece (peer-mapped addresses are fine); wait_flags[s] (optional) is shard s's
+ * parameter-version word: the TMA producer acquires *wait_flags[s] >= wait_value + *wait_value_ptr (pointer
+ * optional) before its first load from s.
+ * No counterpart in the reference beyond the implicit RecvTensor traffic. */
+int tfd_gemm_bf16_seg(const void* A, long long lda, int a_mn, const void* const* B_ptrs, long long ldb, int b_mn, int M,
+                      int N, int K, int bn, int splits, int mode, float alpha, void* out, long long ld_out,
+                      const float* bias, const void* relu_mask, long long ld_mask, long long split_stride, int seg_mode,
+                      int nseg, const int* seg_rows, void* const* out_ptrs, const unsigned* const* wait_flags,
+                      unsigned wait_value, const unsigned* wait_value_ptr, void* stream);
 
 /* CUDA-core fp32 reference GEMM (validation only): D[M,N] = A[M,K](bf16,row) * B[K,N](bf16,row). */
 int tfd_gemm_ref(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, float* out,
@@ -43,8 +59,10 @@ int tfd_gemm_ref(const void* A, long long lda, const void* B, long long ldb, int
 /* ---- elementwise / CUDA-core kernels ---- */
 /* fp32 [rows,cols] -> bf16 [rows,ld_dst] (pad columns zeroed). */
 int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long long ld_dst, int rows, int cols, void* stream);
-/* tf.random_normal (m:186-195): Philox4x32-10 + Box-Muller, mean 0. */
-int tfd_random_normal(float* out, long long n, unsigned long long seed, float stddev, void* stream);
+/* tf.random_normal (m:186-195): Philox4x32-10 + Box-Muller, mean 0.  out[i] is value (elem_offset + i) of the
+ * stream `seed`, so a ps shard that owns rows [r0,r1) of a variable generates exactly its slice. */
+int tfd_random_normal(float* out, long long n, unsigned long long seed, float stddev, long long elem_offset,
+                      void* stream);
 
 /* conv1 5x5 SAME 1->32 + bias + ReLU + 2x2 max-pool (m:109-111).  x fp32 [B,784]; w fp32 [25,32] (HWIO);
  * out bf16 [B,14,14,32]; argmax u8 [B,14,14,32] (0..3 = position inside the 2x2 window). */
@@ -70,20 +88,21 @@ int tfd_conv2_fwd_ref(const void* in, const void* w, const float* b, void* pool_
 int tfd_conv2_dgrad_ref(const void* dy, const void* w, float* dx, int B, void* stream);
 int tfd_conv2_wgrad_ref(const void* in, const void* dy, float* dw, int B, void* stream);
 
-/* max-pool + ReLU backward of the conv2 block: dpool fp32 [B,7,7,64] -> dy bf16 [B,14,14,64] (dense, zeros
- * written); db fp32 [64] accumulated with atomics. */
-int tfd_pool2_bwd(const float* dpool, const void* pool_out, const unsigned char* argmax, void* dy, float* db, int B,
-                  void* stream);
+/* max-pool + ReLU backward of the conv2 block: dpool fp32 [nsplit][B,7,7,64] (split-K partials, summed here;
+ * split_stride in elements) -> dy bf16 [B,14,14,64] (dense, zeros written); db fp32 [64] accumulated with atomics. */
+int tfd_pool2_bwd(const float* dpool, int nsplit, long long split_stride, const void* pool_out,
+                  const unsigned char* argmax, void* dy, float* db, int B, void* stream);
 
 /* Head, row phase (one block per example): optional fc bias + ReLU + inverted dropout (m:121-124), output
  * layer (m:127), softmax cross entropy with dense labels (m:205), dlogits=(softmax-y)/B, accuracy hit
  * (m:206-207) and the gradient flowing back into the hidden layer.
- *   pre_f32 != NULL: hidden = dropout(relu(pre_f32 + hid_bias))   (CNN fc1; pre_f32 is the split-K sum)
+ *   pre_f32 != NULL: hidden = dropout(relu(sum_s pre_f32[s] + hid_bias))   (CNN fc1; pre_f32 holds pre_nsplit
+ *                    split-K partial planes, pre_split_stride elements apart: the GEMM never needs atomics)
  *   else           : hidden = hid_bf16 (already bias+ReLU'd by the GEMM epilogue; MLP)
  * Writes hid_out bf16 [B,ld_h] (post-dropout, for the output-layer wgrad), dhid bf16 [B,ld_h] (training only),
  * dlogits fp32 [B,10], loss_row fp32 [B], hit u8 [B]. keep_prob>=1 disables dropout.  The dropout stream is
  * Philox(seed; step + *step_ptr, element): step_ptr (optional, device) lets a captured CUDA graph advance it. */
-int tfd_head_rows(const float* pre_f32, const void* hid_bf16, const float* hid_bias, const float* out_w,
+int tfd_head_rows(const float* pre_f32, int pre_nsplit, long long pre_split_stride, const void* hid_bf16, const float* hid_bias, const float* out_w,
                   const float* out_b, const float* labels, int B, int H, long long ld_h, float keep_prob,
                   unsigned long long seed, unsigned long long step, const unsigned* step_ptr, int training,
                   void* hid_out, void* dhid, float* dlogits, float* loss_row, unsigned char* hit,
@@ -99,6 +118,12 @@ int tfd_zero_multi(float* const* ptrs, const long long* ns, int count, void* str
 int tfd_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out, void* stream);
 
 /* ---- parameter-server kernels ---- */
+#define TFD_MAX_SLOTS 8 /* gradient staging slots (= workers) one shard reduces */
+#define TFD_MAX_SEG 8   /* parameter-server shards a fused pull/push GEMM can address */
+#define TFD_SEG_NONE 0
+#define TFD_SEG_B_K 1   /* forward: B's K rows sharded over ps GPUs  */
+#define TFD_SEG_B_N 2   /* dgrad:   B read as [N,K], N rows sharded  */
+#define TFD_SEG_OUT_M 3 /* wgrad:   output rows sharded (fused push) */
 /* One piece of a shard arena that has a bf16 shadow for tensor-core consumers. */
 typedef struct {
   long long arena_off;  /* element offset of the piece in the fp32 arena */
@@ -110,7 +135,7 @@ typedef struct {
 
 /* Gradient reduce + scale + TF-form Adam + bf16 shadow publish on the owning shard (push, X2/X3; m:208,222):
  *   g = scale * sum_{r<num_slots} slots[r][i];  m,v,w updated in place;  shadow = bf16(w).
- * slots: device array of num_slots pointers to fp32 gradient arenas (staging slots written by the workers,
+ * slots: HOST array of num_slots (<= TFD_MAX_SLOTS) device pointers to fp32 gradient arenas (staging slots written by the workers,
  * possibly through NVLink).  lr_t is computed on the device from the Adam step counter t_counter[0] (u32,
  * incremented by this kernel), so the kernel can sit in a CUDA graph.  If wait_counter != NULL the kernel first
  * spins until *wait_counter >= wait_base + num_slots*epoch (gradient arrivals for this step); on completion it
@@ -131,11 +156,13 @@ int tfd_pull_params(const float* src, float* dst, long long n, const unsigned* v
 
 /* Table forms: one launch moves every segment (one per destination shard / source tensor).  push: after all
  * segments are written the last block adds 1 (release, system scope) to each arrive counter.  pull: each
- * segment first waits for *versions[i] >= want_version (NULL = no wait). */
+ * segment first waits for *versions[i] >= want_version + *want_ptr (NULL flag = no wait; want_ptr optional).
+ * push: local_step (optional, device) is incremented by the last block -- the worker's step counter that
+ * want_ptr / wait_value_ptr of the next step read, so a captured CUDA graph advances by itself. */
 int tfd_push_multi(const void* const* srcs, void* const* dsts, const long long* ns, int nseg, unsigned* const* arrive,
-                   int narrive, float scale, unsigned* block_counter, void* stream);
+                   int narrive, float scale, unsigned* block_counter, unsigned* local_step, void* stream);
 int tfd_pull_multi(const void* const* srcs, void* const* dsts, const long long* ns, const unsigned* const* versions,
-                   int nseg, unsigned want_version, void* stream);
+                   int nseg, unsigned want_version, const unsigned* want_ptr, void* stream);
 
 /* ---- peer memory (symmetric heap over cudaIpc) ---- */
 int tfd_set_device(int device);

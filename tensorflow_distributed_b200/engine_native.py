@@ -35,32 +35,39 @@ def needs_shadow(spec: ModelSpec, name: str) -> bool:
 
 
 class ShardState:
-    """One parameter-server shard in HBM: fp32 arena + Adam slots + bf16 shadow + control words."""
+    """One parameter-server shard in HBM: fp32 arena + Adam slots + bf16 shadow + control words.
+
+    ``alloc(name, numel, dtype)`` lets the multi-GPU runtime carve w / m / v / shadow / ctrl out of a
+    peer-mapped (cudaIpc) heap; by default they are ordinary torch allocations.
+    """
 
     def __init__(self, spec: ModelSpec, placement: Placement, shard: int, device, alloc=None):
         self.spec, self.placement, self.shard, self.device = spec, placement, shard, device
-        n = placement.shard_sizes[shard]
-        self.n = n
-        alloc = alloc or (lambda numel, dtype: torch.zeros(numel, dtype=dtype, device=device))
-        self.w = alloc(n, torch.float32)
-        self.m = alloc(n, torch.float32)
-        self.v = alloc(n, torch.float32)
-        self.pieces: List[nat.Piece] = []
-        self.shadow_off: Dict[str, int] = {}
-        self.shadow_ld: Dict[str, int] = {}
+        self.n = placement.shard_sizes[shard]
+        self.pieces, self.shadow_off, self.shadow_ld, self.shadow_n = self.layout(spec, placement, shard)
+        alloc = alloc or (lambda name, numel, dtype: torch.zeros(numel, dtype=dtype, device=device))
+        self.w = alloc("w", self.n, torch.float32)
+        self.m = alloc("m", self.n, torch.float32)
+        self.v = alloc("v", self.n, torch.float32)
+        self.shadow = alloc("shadow", self.shadow_n, torch.bfloat16)
+        self.ctrl = alloc("ctrl", 64, torch.int32)
+
+    @staticmethod
+    def layout(spec: ModelSpec, placement: Placement, shard: int):
+        pieces: List[nat.Piece] = []
+        shadow_off: Dict[str, int] = {}
+        shadow_ld: Dict[str, int] = {}
         off = 0
         for p in placement.shard_pieces(shard):
             if needs_shadow(spec, p.var):
                 ld = _pad8(p.cols)
-                self.pieces.append(nat.Piece(p.offset, p.numel, p.cols, ld, off))
-                self.shadow_off[p.var], self.shadow_ld[p.var] = off, ld
+                pieces.append(nat.Piece(p.offset, p.numel, p.cols, ld, off))
+                shadow_off[p.var], shadow_ld[p.var] = off, ld
                 off += (p.row_end - p.row_start) * ld
                 off = (off + 63) // 64 * 64
             else:
-                self.pieces.append(nat.Piece(p.offset, p.numel, p.cols, 0, 0))
-        self.shadow_n = max(off, 64)
-        self.shadow = alloc(self.shadow_n, torch.bfloat16)
-        self.ctrl = alloc(16, torch.int32)
+                pieces.append(nat.Piece(p.offset, p.numel, p.cols, 0, 0))
+        return pieces, shadow_off, shadow_ld, max(off, 64)
 
     def piece_of(self, var: str):
         for p in self.placement.pieces[var]:
@@ -85,6 +92,16 @@ class ShardState:
             nat.cast_bf16(self.view(self.w, var), self.shadow_view(var), p.row_end - p.row_start, p.cols,
                           p.cols, self.shadow_ld[var])
 
+    def init_variables(self, seed: int, stddev: float) -> None:
+        """tf.global_variables_initializer() for the pieces this shard owns: every parameter ~ N(0, stddev).
+        The Philox stream is indexed by (variable, global element), so the values do not depend on the sharding."""
+        for i, v in enumerate(self.spec.variables):
+            p = self.piece_of(v.name)
+            if p is not None:
+                nat.random_normal(self.view(self.w, v.name), (seed << 8) + i, stddev, p.row_start * p.cols)
+        self.m.zero_(); self.v.zero_(); self.ctrl.zero_()
+        self.publish_shadow()
+
 
 class Workspace:
     """Activations / gradients-of-activations for one batch size (all static: graph-capturable)."""
@@ -105,10 +122,12 @@ class Workspace:
             self.am1 = z(B, 14, 14, 32, dtype=torch.uint8)
             self.pool2 = z(B, 7, 7, 64, dtype=torch.bfloat16)
             self.am2 = z(B, 7, 7, 64, dtype=torch.uint8)
-            self.fc1acc = z(B, 1024)
+            self.fc1_splits = max(1, min(8, 148 // (((B + 127) // 128) * 16)))
+            self.fc1acc = z(self.fc1_splits, B, 1024)   # split-K partial planes (summed by the head kernel)
             self.hid = z(B, 1024, dtype=torch.bfloat16)
             self.dhid = z(B, 1024, dtype=torch.bfloat16)
-            self.dpool2 = z(B, 3136)
+            self.dg_splits = max(1, min(3, 148 // (((B + 127) // 128) * 49)))
+            self.dpool2 = z(self.dg_splits, B, 3136)    # split-K partial planes (summed by pool2_bwd)
             self.dy2 = z(B, 14, 14, 64, dtype=torch.bfloat16)
             self.dpool1 = z(B, 14, 14, 32)
             self.keep_mask = None
@@ -138,18 +157,14 @@ class NativeEngine:
         self.placement = Placement(spec, 1)
         self.shard = ShardState(spec, self.placement, 0, self.device)
         self.grad = torch.zeros(self.shard.n, dtype=torch.float32, device=self.device)
-        self.slot_ptrs = torch.tensor([self.grad.data_ptr()], dtype=torch.int64, device=self.device)
+        self.slot_ptrs = [self.grad.data_ptr()]
         self.ws: Dict[int, Workspace] = {}
         self.init_variables(seed, init_stddev)
 
     # ---- variables -------------------------------------------------------------------------
     def init_variables(self, seed: int, stddev: float) -> None:
         """tf.global_variables_initializer(): every parameter ~ N(0, stddev) from the device Philox stream."""
-        s = self.shard
-        for i, v in enumerate(self.spec.variables):
-            nat.random_normal(s.view(s.w, v.name), (seed << 8) + i, stddev)
-        s.m.zero_(); s.v.zero_(); s.ctrl.zero_()
-        s.publish_shadow()
+        self.shard.init_variables(seed, stddev)
         torch.cuda.synchronize(self.device)
 
     @property
@@ -203,39 +218,67 @@ class NativeEngine:
             self.ws[B] = Workspace(self.spec, B, self.device)
         return self.ws[B]
 
+    # ---- GEMM hooks: the multi-GPU worker overrides these to address ps shards over NVLink ----------
+    def gemm_fwd(self, wname: str, A, M: int, out, *, mode: int, bn: int, splits: int = 1, split_stride: int = 0,
+                 bias=None, ld_out: Optional[int] = None) -> None:
+        """out[M,N] = A[M,K] W[K,N]  (A K-major, W MN-major as stored)."""
+        W = self.S(wname)
+        K, N = W.shape[0], self.P(wname).shape[1]
+        nat.gemm_bf16(A, 0, W, 1, M, N, K, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride, bias=bias,
+                      ld_out=ld_out)
+
+    def gemm_dgrad(self, wname: str, dY, M: int, out, *, mode: int, bn: int, splits: int = 1, split_stride: int = 0,
+                   relu_mask=None, ld_out: Optional[int] = None) -> None:
+        """out[M,K] = dY[M,N] W^T  (W [K,N] read in place as the K-major B operand [N'=K, K'=N])."""
+        W = self.S(wname)
+        K, N = W.shape[0], self.P(wname).shape[1]
+        nat.gemm_bf16(dY, 0, W, 0, M, K, N, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride,
+                      relu_mask=relu_mask, ld_out=ld_out)
+
+    def gemm_wgrad(self, wname: str, X, dY, Bsz: int, *, bn: int) -> None:
+        """dW[K,N] = X^T dY  (both MN-major, contraction over the batch); written where the gradient lives."""
+        G = self.G(wname)
+        nat.gemm_bf16(X, 1, dY, 1, G.shape[0], G.shape[1], Bsz, G, mode=nat.EPI_STORE_F32, bn=bn)
+
+    def step_ptr(self):
+        """Device word that advances once per training step (dropout stream, version gates)."""
+        return self.shard.ctrl[CTRL_T:]
+
+    def _pre_step(self, ws, training: bool) -> None:
+        pass  # multi-GPU worker: pull small parameters / wait for the parameter version
+
+    def _post_backward(self, ws) -> None:
+        pass  # multi-GPU worker: push small gradients, signal arrival
+
     # ---- kernel sequences ------------------------------------------------------------------
     def _splits(self, mtiles: int, ntiles: int, kblocks: int, cap: int = 16) -> int:
         return max(1, min(cap, kblocks, 148 // max(1, mtiles * ntiles)))
 
     def _cnn_forward(self, ws: Workspace, training: bool, keep_prob: float, mask_out=None) -> None:
         B = ws.B
-        zeros = [ws.fc1acc]
-        if training:
-            zeros += [ws.dpool2, self.G("weights/wc1"), self.G("biases/bc1"), self.G("weights/wc2"),
-                      self.G("biases/bc2")]
-        nat.zero_multi(zeros)
+        if training:  # accumulators of the atomic epilogues (all tiny)
+            nat.zero_multi([self.G("weights/wc1"), self.G("biases/bc1"), self.G("weights/wc2"), self.G("biases/bc2")])
         nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, B)
         nat.conv2_fwd(ws.pool1, self.S("weights/wc2"), self.P("biases/bc2"), ws.pool2, ws.am2, B, ref=self.conv2_ref)
-        mt = (B + 127) // 128
-        nat.gemm_bf16(ws.pool2.view(B, 3136), 0, self.S("weights/wd1"), 1, B, 1024, 3136, ws.fc1acc,
-                      mode=nat.EPI_ATOMIC_F32, bn=128, splits=self._splits(mt, 8, 49))
+        self.gemm_fwd("weights/wd1", ws.pool2.view(B, 3136), B, ws.fc1acc, mode=nat.EPI_STORE_F32, bn=64,
+                      splits=ws.fc1_splits, split_stride=B * 1024, ld_out=1024)
         nat.head_rows(ws.fc1acc, None, self.P("biases/bd1"), self.P("weights/out"), self.P("biases/out"), ws.y, B,
                       1024, 1024, keep_prob if training else 1.0, self.seed, 0, training, ws.hid,
                       ws.dhid if training else None, ws.dlogits, ws.loss_row, ws.hit, mask_out,
-                      step_ptr=self.shard.ctrl[CTRL_T:] if training else None)
+                      step_ptr=self.step_ptr() if training else None, pre_nsplit=ws.fc1_splits,
+                      pre_split_stride=B * 1024)
 
     def _cnn_backward(self, ws: Workspace) -> None:
         B = ws.B
         nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, self.G("weights/out"),
                       self.G("biases/bd1"), self.G("biases/out"), ws.scalars)
         # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
-        nat.gemm_bf16(ws.pool2.view(B, 3136), 1, ws.dhid, 1, 3136, 1024, B, self.G("weights/wd1"),
-                      mode=nat.EPI_STORE_F32, bn=128)
+        self.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
         # fc1 dgrad: dpool2[B,3136] = dhid wd1^T    (wd1 read K-major in place)
-        mt = (B + 127) // 128
-        nat.gemm_bf16(ws.dhid, 0, self.S("weights/wd1"), 0, B, 3136, 1024, ws.dpool2, mode=nat.EPI_ATOMIC_F32, bn=64,
-                      splits=self._splits(mt, 49, 16, cap=3))
-        nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"), B)
+        self.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
+                        split_stride=B * 3136, ld_out=3136)
+        nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"), B, nsplit=ws.dg_splits,
+                      split_stride=B * 3136)
         nat.conv2_wgrad(ws.pool1, ws.dy2, self.G("weights/wc2"), B, ref=self.conv2_ref)
         nat.conv2_dgrad(ws.dy2, self.S("weights/wc2"), ws.dpool1, B, ref=self.conv2_ref)
         nat.conv1_wgrad(ws.x, ws.dpool1, ws.pool1, ws.am1, self.G("weights/wc1"), self.G("biases/bc1"), B)
@@ -246,8 +289,8 @@ class NativeEngine:
         nat.cast_bf16(ws.x, ws.act[0], B, 784, 784, 784)
         for l in range(1, L + 1):
             H, K = dims[l], dims[l - 1]
-            nat.gemm_bf16(ws.act[l - 1], 0, self.S("weights/h%d" % l), 1, B, H, K, ws.act[l],
-                          mode=nat.EPI_BIAS_RELU_BF16, bn=64, bias=self.P("biases/b%d" % l))
+            self.gemm_fwd("weights/h%d" % l, ws.act[l - 1], B, ws.act[l], mode=nat.EPI_BIAS_RELU_BF16, bn=64,
+                          bias=self.P("biases/b%d" % l))
         H = dims[L]
         nat.head_rows(None, ws.act[L], None, self.P("weights/out"), self.P("biases/out"), ws.y, B, H, _pad8(H), 1.0,
                       self.seed, 0, training, None, ws.dact[L] if training else None, ws.dlogits, ws.loss_row, ws.hit)
@@ -260,11 +303,10 @@ class NativeEngine:
                       self.G("biases/b%d" % L), self.G("biases/out"), ws.scalars)
         for l in range(L, 0, -1):
             H, K = dims[l], dims[l - 1]
-            nat.gemm_bf16(ws.act[l - 1], 1, ws.dact[l], 1, K, H, B, self.G("weights/h%d" % l), mode=nat.EPI_STORE_F32,
-                          bn=128 if H >= 128 else 64)
+            self.gemm_wgrad("weights/h%d" % l, ws.act[l - 1], ws.dact[l], B, bn=128 if H >= 128 else 64)
             if l > 1:
-                nat.gemm_bf16(ws.dact[l], 0, self.S("weights/h%d" % l), 0, B, K, H, ws.dact[l - 1],
-                              mode=nat.EPI_RELUMASK_BF16, bn=64, relu_mask=ws.act[l - 1])
+                self.gemm_dgrad("weights/h%d" % l, ws.dact[l], B, ws.dact[l - 1], mode=nat.EPI_RELUMASK_BF16, bn=64,
+                                relu_mask=ws.act[l - 1])
                 nat.colsum_bf16(ws.dact[l - 1], _pad8(K), B, K, self.G("biases/b%d" % (l - 1)))
 
     def _apply(self) -> None:
@@ -274,6 +316,7 @@ class NativeEngine:
 
     def _sequence(self, ws: Workspace, mode: str, keep_prob: float, mask_out=None) -> None:
         training = mode in ("train", "grads")
+        self._pre_step(ws, training)
         if self.spec.kind == "cnn":
             self._cnn_forward(ws, training, keep_prob, mask_out)
             if training:
@@ -282,6 +325,8 @@ class NativeEngine:
             self._mlp_forward(ws, training)
             if training:
                 self._mlp_backward(ws)
+        if training:
+            self._post_backward(ws)
         if not training:
             nat.head_cols(None, None, 0, ws.dlogits, ws.loss_row, ws.hit, ws.B, 1, None, None, None, ws.scalars)
         if mode == "train":

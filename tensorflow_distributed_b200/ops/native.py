@@ -90,15 +90,39 @@ def device_info(dev: int = 0) -> dict:
 # ---------------------------------------------------------------------------------------------
 def gemm_bf16(A, a_mn: int, B, b_mn: int, M: int, N: int, K: int, out, *, mode: int, bn: int = 128, splits: int = 1,
               alpha: float = 1.0, bias=None, relu_mask=None, lda: Optional[int] = None, ldb: Optional[int] = None,
-              ld_out: Optional[int] = None, ld_mask: Optional[int] = None, wait_flag=None, wait_value: int = 0) -> None:
+              ld_out: Optional[int] = None, ld_mask: Optional[int] = None, wait_flag=None, wait_value: int = 0,
+              split_stride: int = 0) -> None:
     lda = lda if lda is not None else A.stride(0)
     ldb = ldb if ldb is not None else B.stride(0)
     ld_out = ld_out if ld_out is not None else out.stride(0)
     ld_mask = ld_mask if ld_mask is not None else (relu_mask.stride(0) if relu_mask is not None else 0)
     _check(lib().tfd_gemm_bf16(_p(A), c_longlong(lda), c_int(a_mn), _p(B), c_longlong(ldb), c_int(b_mn), c_int(M),
                                c_int(N), c_int(K), c_int(bn), c_int(splits), c_int(mode), c_float(alpha), _p(out),
-                               c_longlong(ld_out), _p(bias), _p(relu_mask), c_longlong(ld_mask), _p(wait_flag),
+                               c_longlong(ld_out), _p(bias), _p(relu_mask), c_longlong(ld_mask),
+                               c_longlong(split_stride), _p(wait_flag),
                                c_uint(wait_value), _stream()), "tfd_gemm_bf16")
+    _count()
+
+
+SEG_NONE, SEG_B_K, SEG_B_N, SEG_OUT_M = range(4)
+
+
+def gemm_bf16_seg(A, a_mn: int, B_ptrs, b_mn: int, M: int, N: int, K: int, out, *, mode: int, lda: int, ldb: int,
+                  ld_out: int, seg_mode: int, seg_rows, out_ptrs=None, wait_flags=None, wait_value: int = 0,
+                  wait_value_ptr=None,
+                  bn: int = 128, splits: int = 1, alpha: float = 1.0, bias=None, relu_mask=None, ld_mask: int = 0,
+                  split_stride: int = 0) -> None:
+    """Sharded GEMM: B_ptrs / out_ptrs / wait_flags are per-shard raw device pointers (ints), possibly peer-mapped."""
+    nseg = len(seg_rows) - 1
+    BP = (c_void_p * nseg)(*[c_void_p(int(x)) for x in (B_ptrs if B_ptrs is not None else [0] * nseg)])
+    OP = (c_void_p * nseg)(*[c_void_p(int(x)) for x in out_ptrs]) if out_ptrs is not None else None
+    WF = (c_void_p * nseg)(*[c_void_p(int(x) if x else 0) for x in wait_flags]) if wait_flags is not None else None
+    SR = (c_int * (nseg + 1))(*[int(r) for r in seg_rows])
+    _check(lib().tfd_gemm_bf16_seg(_p(A), c_longlong(lda), c_int(a_mn), BP, c_longlong(ldb), c_int(b_mn), c_int(M),
+                                   c_int(N), c_int(K), c_int(bn), c_int(splits), c_int(mode), c_float(alpha), _p(out),
+                                   c_longlong(ld_out), _p(bias), _p(relu_mask), c_longlong(ld_mask),
+                                   c_longlong(split_stride), c_int(seg_mode), c_int(nseg), SR, OP, WF,
+                                   c_uint(wait_value), _p(wait_value_ptr), _stream()), "tfd_gemm_bf16_seg")
     _count()
 
 
@@ -115,8 +139,9 @@ def cast_bf16(src, dst, rows: int, cols: int, ld_src: Optional[int] = None, ld_d
     _count()
 
 
-def random_normal(out, seed: int, stddev: float = 1.0) -> None:
-    _check(lib().tfd_random_normal(_p(out), c_longlong(out.numel()), c_ulonglong(seed), c_float(stddev), _stream()),
+def random_normal(out, seed: int, stddev: float = 1.0, elem_offset: int = 0) -> None:
+    _check(lib().tfd_random_normal(_p(out), c_longlong(out.numel()), c_ulonglong(seed), c_float(stddev),
+                                   c_longlong(elem_offset), _stream()),
            "tfd_random_normal")
     _count()
 
@@ -150,16 +175,16 @@ def conv2_wgrad(inp, dy, dw, B: int, ref: bool = False) -> None:
     _count()
 
 
-def pool2_bwd(dpool, pool_out, argmax, dy, db, B: int) -> None:
-    _check(lib().tfd_pool2_bwd(_p(dpool), _p(pool_out), _p(argmax), _p(dy), _p(db), c_int(B), _stream()),
+def pool2_bwd(dpool, pool_out, argmax, dy, db, B: int, nsplit: int = 1, split_stride: int = 0) -> None:
+    _check(lib().tfd_pool2_bwd(_p(dpool), c_int(nsplit), c_longlong(split_stride), _p(pool_out), _p(argmax), _p(dy), _p(db), c_int(B), _stream()),
            "tfd_pool2_bwd")
     _count()
 
 
 def head_rows(pre_f32, hid_bf16, hid_bias, out_w, out_b, labels, B: int, H: int, ld_h: int, keep_prob: float,
               seed: int, step: int, training: bool, hid_out, dhid, dlogits, loss_row, hit, keep_mask_out=None,
-              step_ptr=None) -> None:
-    _check(lib().tfd_head_rows(_p(pre_f32), _p(hid_bf16), _p(hid_bias), _p(out_w), _p(out_b), _p(labels), c_int(B),
+              step_ptr=None, pre_nsplit: int = 1, pre_split_stride: int = 0) -> None:
+    _check(lib().tfd_head_rows(_p(pre_f32), c_int(pre_nsplit), c_longlong(pre_split_stride), _p(hid_bf16), _p(hid_bias), _p(out_w), _p(out_b), _p(labels), c_int(B),
                                c_int(H), c_longlong(ld_h), c_float(keep_prob), c_ulonglong(seed), c_ulonglong(step),
                                _p(step_ptr), c_int(int(training)), _p(hid_out), _p(dhid), _p(dlogits), _p(loss_row), _p(hit),
                                _p(keep_mask_out), _stream()), "tfd_head_rows")
@@ -192,31 +217,33 @@ def adam_apply(w, m, v, shadow, slots_dev, num_slots: int, scale: float, n: int,
                wait_counter=None, version_flag=None, global_step=None, beta1: float = 0.9, beta2: float = 0.999,
                eps: float = 1e-8) -> None:
     arr = (Piece * max(1, len(pieces)))(*pieces)
-    _check(lib().tfd_adam_apply(_p(w), _p(m), _p(v), _p(shadow), _p(slots_dev), c_int(num_slots), c_float(scale),
+    slots = (c_void_p * num_slots)(*[c_void_p(int(x)) for x in slots_dev[:num_slots]])  # host array of device pointers
+    _check(lib().tfd_adam_apply(_p(w), _p(m), _p(v), _p(shadow), slots, c_int(num_slots), c_float(scale),
                                 c_longlong(n), arr, c_int(len(pieces)), c_float(lr), c_float(beta1), c_float(beta2),
                                 c_float(eps), _p(t_counter), _p(wait_counter), _p(version_flag), _p(global_step),
                                 _stream()), "tfd_adam_apply")
     _count()
 
 
-def push_multi(srcs, dsts, ns, arrive, scale: float, block_counter) -> None:
+def push_multi(srcs, dsts, ns, arrive, scale: float, block_counter, local_step=None) -> None:
     n = len(srcs)
     S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
     D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
     NS = (c_longlong * n)(*[int(x) for x in ns])
     A = (c_void_p * max(1, len(arrive)))(*[c_void_p(int(x)) for x in arrive])
     _check(lib().tfd_push_multi(S, D, NS, c_int(n), A, c_int(len(arrive)), c_float(scale), _p(block_counter),
-                                _stream()), "tfd_push_multi")
+                                _p(local_step), _stream()), "tfd_push_multi")
     _count()
 
 
-def pull_multi(srcs, dsts, ns, versions, want_version: int) -> None:
+def pull_multi(srcs, dsts, ns, versions, want_version: int, want_ptr=None) -> None:
     n = len(srcs)
     S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
     D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
     NS = (c_longlong * n)(*[int(x) for x in ns])
     V = (c_void_p * n)(*[c_void_p(int(x) if x else 0) for x in versions]) if versions is not None else None
-    _check(lib().tfd_pull_multi(S, D, NS, V, c_int(n), c_uint(want_version), _stream()), "tfd_pull_multi")
+    _check(lib().tfd_pull_multi(S, D, NS, V, c_int(n), c_uint(want_version), _p(want_ptr), _stream()),
+           "tfd_pull_multi")
     _count()
 
 

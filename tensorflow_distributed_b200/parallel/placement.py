@@ -5,8 +5,8 @@ via ``tf.train.replica_device_setter`` (``/root/reference/mnist_python_m.py:
 177``).  That puts 98% of the CNN's bytes (``wd1``) on one ps.
 This module keeps whole-variable round-robin for small tensors and splits big
 tensors *inside* the tensor by rows (the GEMM K dimension of the forward pass),
-in units of ``row_align`` rows so every shard boundary is a K-block boundary of
-the pull-fused GEMM.  Each shard owns one flat fp32 arena (master weights, Adam
+in units of ``row_align`` rows (128 = one tcgen05 M tile = two K blocks) so every shard boundary is a tile
+boundary of the pull-fused (forward/dgrad) and push-fused (wgrad) GEMMs.  Each shard owns one flat fp32 arena (master weights, Adam
 m/v alongside) -- one allocation per ps GPU.
 """
 from __future__ import annotations
@@ -38,7 +38,7 @@ def _align(n: int, a: int = ARENA_ALIGN) -> int:
 
 
 class Placement:
-    def __init__(self, spec: ModelSpec, num_shards: int, split_threshold: int = 1 << 18, row_align: int = 64):
+    def __init__(self, spec: ModelSpec, num_shards: int, split_threshold: int = 1 << 18, row_align: int = 128):
         if num_shards < 1:
             raise ValueError("need at least one ps shard")
         self.spec = spec

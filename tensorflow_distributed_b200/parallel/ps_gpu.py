@@ -1,0 +1,259 @@
+"""GPU parameter server: ps shards in HBM, reached by the workers' kernels over NVLink peer memory.
+
+What TF's gRPC runtime does implicitly for the reference (parameter pull X1, gradient push X2/X3,
+sync token X4, global_step X5, init/readiness X6; ``/root/reference/mnist_python_m.py:158-161,177,210-233``)
+becomes explicit device-side traffic on one 8xB200 box:
+
+* a **ps task is a GPU** that owns one shard: fp32 master arena, Adam m/v, a bf16 shadow of the tensor-core
+  operands, one gradient staging slot per worker, and a few control words -- all in ONE cudaIpc allocation that
+  every other rank maps (symmetric heap; ``torch.distributed`` only carries the 64-byte handles at start-up);
+* **pull**: small tensors are copied by one kernel gated on each shard's ``version`` word; the big sharded
+  matrices are never copied -- the forward/dgrad GEMMs TMA-load their B tiles straight from the owner GPUs;
+* **push**: the wgrad GEMM epilogue stores its tiles straight into this worker's slot on the owner GPU; the small
+  gradients follow in one kernel that then adds 1 to every shard's ``arrive`` word (release, system scope);
+* **apply**: each shard's Adam kernel spins until ``arrive >= workers * t``, sums the slots in a fixed order,
+  scales by 1/R, updates w/m/v, republishes the bf16 shadow and stores ``version = t`` (release).
+  ``version``/``arrive`` are the token queue of SyncReplicasOptimizer reduced to two monotonic counters.
+
+Layouts: ``colocated`` (default) -- every GPU is a worker and hosts a shard; ``dedicated`` -- the first S GPUs are
+ps-only and never run a model kernel, like the reference's ps process that sits in ``server.join()``.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..engine_native import (CTRL_ARRIVE, CTRL_GSTEP, CTRL_PUSHBLK, CTRL_T, CTRL_VERSION, NativeEngine, ShardState,
+                             Workspace, needs_shadow, _pad8)
+from ..models.spec import ModelSpec
+from ..ops import native as nat
+from .placement import Placement
+
+WCTRL_STEP, WCTRL_PUSHBLK = 8, 9   # worker-local control words (inside the rank's own ctrl block)
+DIRECT_THRESHOLD = 1 << 18         # tensors at least this big are consumed in place over NVLink, never mirrored
+
+
+@dataclass
+class Topology:
+    world: int
+    ps_ranks: List[int]
+    worker_ranks: List[int]
+    layout: str
+
+    @classmethod
+    def make(cls, world: int, layout: str = "colocated", num_ps: int = 0) -> "Topology":
+        if world < 1:
+            raise ValueError("world size must be >= 1")
+        if layout == "colocated":
+            s = num_ps or world
+            if not 1 <= s <= world:
+                raise ValueError("colocated layout: need 1 <= ps shards <= GPUs")
+            return cls(world, list(range(s)), list(range(world)), layout)
+        if layout == "dedicated":
+            s = num_ps or 1
+            if not 1 <= s < world:
+                raise ValueError("dedicated layout needs at least one ps GPU and one worker GPU")
+            return cls(world, list(range(s)), list(range(s, world)), layout)
+        raise ValueError("unknown layout %r" % layout)
+
+    @property
+    def num_shards(self) -> int:
+        return len(self.ps_ranks)
+
+    @property
+    def num_workers(self) -> int:
+        return len(self.worker_ranks)
+
+    def shard_of(self, rank: int) -> Optional[int]:
+        return self.ps_ranks.index(rank) if rank in self.ps_ranks else None
+
+    def worker_of(self, rank: int) -> Optional[int]:
+        return self.worker_ranks.index(rank) if rank in self.worker_ranks else None
+
+    def describe(self) -> str:
+        return "ps%d+w%d %s" % (self.num_shards, self.num_workers, self.layout)
+
+
+def _al(n: int, a: int = 1024) -> int:
+    return (n + a - 1) // a * a
+
+
+class HeapLayout:
+    """Byte offsets inside one rank's peer-mapped allocation.  Identical arithmetic on every rank."""
+
+    def __init__(self, spec: ModelSpec, placement: Placement, shard: Optional[int], num_workers: int):
+        off = 0
+        self.ctrl = off; off += 1024
+        self.n = self.shadow_n = 0
+        self.w = self.m = self.v = self.shadow = self.slots = off
+        if shard is not None:
+            self.n = placement.shard_sizes[shard]
+            _, _, _, self.shadow_n = ShardState.layout(spec, placement, shard)
+            self.w = off; off += _al(self.n * 4)
+            self.m = off; off += _al(self.n * 4)
+            self.v = off; off += _al(self.n * 4)
+            self.shadow = off; off += _al(self.shadow_n * 2)
+            self.slots = off; off += num_workers * _al(self.n * 4)
+        self.slot_stride = _al(self.n * 4)
+        self.total = max(off, 4096)
+
+    def slot(self, worker: int) -> int:
+        return self.slots + worker * self.slot_stride
+
+
+class GpuClusterEngine(NativeEngine):
+    """One rank (= one B200) of the ps/worker cluster.  Same public API as NativeEngine."""
+
+    name = "native-sm100a-ps"
+
+    def __init__(self, spec: ModelSpec, topo: Topology, rank: int, device, learning_rate: float = 0.01,
+                 seed: int = 0, init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False):
+        if not dist.is_initialized():
+            raise RuntimeError("GpuClusterEngine needs torch.distributed (bootstrap only) to be initialised")
+        nat.lib()
+        self.spec, self.topo, self.rank = spec, topo, rank
+        self.device = torch.device(device)
+        torch.cuda.set_device(self.device)
+        nat.set_device(self.device.index or 0)
+        self.lr, self.seed = learning_rate, seed
+        self.use_graphs, self.conv2_ref = use_graphs, conv2_ref
+        self.ws: Dict[int, Workspace] = {}
+        self.my_shard = topo.shard_of(rank)
+        self.my_worker = topo.worker_of(rank)
+        self.is_ps, self.is_worker = self.my_shard is not None, self.my_worker is not None
+        self.num_workers = topo.num_workers
+        S = topo.num_shards
+        self.placement = Placement(spec, S)
+        self.layouts = [HeapLayout(spec, self.placement, topo.shard_of(r), topo.num_workers) for r in range(topo.world)]
+        # ---- symmetric heap: allocate, exchange the 64-byte cudaIpc handles, map every ps rank's heap ----
+        self.heap_ptr, handle = nat.ipc_alloc(self.layouts[rank].total)
+        handles: List[Optional[bytes]] = [None] * topo.world
+        dist.all_gather_object(handles, handle)
+        self.peer_base: Dict[int, int] = {rank: self.heap_ptr}
+        self._opened: List[int] = []
+        for r in topo.ps_ranks:
+            if r != rank:
+                self.peer_base[r] = nat.ipc_open(handles[r])
+                self._opened.append(self.peer_base[r])
+        L = self.layouts[rank]
+        self.ctrl = nat.tensor_from_ptr(self.heap_ptr + L.ctrl, 64, torch.int32, self.device)
+        # ---- ps role ----
+        self.shard = None
+        self._shard_layouts = [ShardState.layout(spec, self.placement, s) for s in range(S)]
+        if self.is_ps:
+            offs = {"w": L.w, "m": L.m, "v": L.v, "shadow": L.shadow, "ctrl": L.ctrl}
+            self.shard = ShardState(spec, self.placement, self.my_shard, self.device,
+                                    alloc=lambda name, numel, dtype: nat.tensor_from_ptr(
+                                        self.heap_ptr + offs[name], numel, dtype, self.device))
+            self.slot_ptrs = [self.heap_ptr + L.slot(w) for w in range(topo.num_workers)]
+            self.shard.init_variables(seed, init_stddev)
+        # ---- worker role ----
+        self.direct = {v.name for v in spec.variables if needs_shadow(spec, v.name) and v.numel >= DIRECT_THRESHOLD}
+        if self.is_worker:
+            self._build_worker_tables()
+        torch.cuda.synchronize(self.device)
+        dist.barrier()  # X6: everybody waits until every shard has been initialised
+
+    # ---- addressing helpers ----------------------------------------------------------------
+    def _ps_rank(self, shard: int) -> int:
+        return self.topo.ps_ranks[shard]
+
+    def _ctrl_ptr(self, shard: int, word: int) -> int:
+        r = self._ps_rank(shard)
+        return self.peer_base[r] + self.layouts[r].ctrl + 4 * word
+
+    def _w_ptr(self, shard: int, elem_off: int) -> int:
+        r = self._ps_rank(shard)
+        return self.peer_base[r] + self.layouts[r].w + 4 * elem_off
+
+    def _shadow_ptr(self, shard: int, var: str) -> int:
+        r = self._ps_rank(shard)
+        return self.peer_base[r] + self.layouts[r].shadow + 2 * self._shard_layouts[shard][1][var]
+
+    def _slot_ptr(self, shard: int, elem_off: int) -> int:
+        r = self._ps_rank(shard)
+        return self.peer_base[r] + self.layouts[r].slot(self.my_worker) + 4 * elem_off
+
+    def _build_worker_tables(self) -> None:
+        dev = self.device
+        self.mirror_w: Dict[str, torch.Tensor] = {}
+        self.mirror_s: Dict[str, torch.Tensor] = {}
+        self.local_g: Dict[str, torch.Tensor] = {}
+        pull, push = [], []
+        seen_shards = set()
+        for v in self.spec.variables:
+            if v.name in self.direct:
+                continue
+            (p,) = self.placement.pieces[v.name]  # small tensors live whole on one shard
+            rows, cols = p.row_end - p.row_start, p.cols
+            self.mirror_w[v.name] = torch.zeros(rows, cols, dtype=torch.float32, device=dev)
+            self.local_g[v.name] = torch.zeros(rows, cols, dtype=torch.float32, device=dev)
+            ver = self._ctrl_ptr(p.shard, CTRL_VERSION)
+            pull.append((self._w_ptr(p.shard, p.offset), self.mirror_w[v.name].data_ptr(), p.numel, ver))
+            push.append((self.local_g[v.name].data_ptr(), self._slot_ptr(p.shard, p.offset), p.numel))
+            seen_shards.add(p.shard)
+            if needs_shadow(self.spec, v.name):
+                ld = _pad8(cols)
+                self.mirror_s[v.name] = torch.zeros(rows, ld, dtype=torch.bfloat16, device=dev)
+                pull.append((self._shadow_ptr(p.shard, v.name), self.mirror_s[v.name].data_ptr(), rows * ld // 2, ver))
+        for s in range(self.topo.num_shards):  # wait for EVERY shard's version (its slots are then free again)
+            if s not in seen_shards:
+                pull.append((self._w_ptr(s, 0), self.ctrl.data_ptr() + 4 * 32, 0, self._ctrl_ptr(s, CTRL_VERSION)))
+        self._pull, self._push = pull, push
+        self._arrive = [self._ctrl_ptr(s, CTRL_ARRIVE) for s in range(self.topo.num_shards)]
+        # per direct variable: shard pieces in row order
+        self._direct_info = {}
+        for name in self.direct:
+            pcs = sorted(self.placement.pieces[name], key=lambda q: q.row_start)
+            self._direct_info[name] = {
+                "rows": [q.row_start for q in pcs] + [pcs[-1].row_end], "cols": pcs[0].cols, "ld": _pad8(pcs[0].cols),
+                "shadow": [self._shadow_ptr(q.shard, name) for q in pcs],
+                "slot": [self._slot_ptr(q.shard, q.offset) for q in pcs],
+                "ver": [self._ctrl_ptr(q.shard, CTRL_VERSION) for q in pcs]}
+
+    # ---- parameter / gradient views used by the kernel sequences -----------------------------
+    def P(self, name: str) -> torch.Tensor:
+        return self.mirror_w[name]
+
+    def S(self, name: str) -> torch.Tensor:
+        return self.mirror_s[name]
+
+    def G(self, name: str) -> torch.Tensor:
+        return self.local_g[name]
+
+    def step_ptr(self):
+        return self.ctrl[WCTRL_STEP:]
+
+    def gemm_fwd(self, wname, A, M, out, *, mode, bn, splits=1, split_stride=0, bias=None, ld_out=None):
+        if wname not in self.direct:
+            return super().gemm_fwd(wname, A, M, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride,
+                                    bias=bias, ld_out=ld_out)
+        d = self._direct_info[wname]
+        nat.gemm_bf16_seg(A, 0, d["shadow"], 1, M, d["cols"], d["rows"][-1], out, mode=mode, lda=A.stride(0),
+                          ldb=d["ld"], ld_out=ld_out if ld_out is not None else out.stride(0), seg_mode=nat.SEG_B_K,
+                          seg_rows=d["rows"], wait_flags=d["ver"], wait_value_ptr=self.step_ptr(), bn=bn,
+                          splits=splits, split_stride=split_stride, bias=bias)
+
+    def gemm_dgrad(self, wname, dY, M, out, *, mode, bn, splits=1, split_stride=0, relu_mask=None, ld_out=None):
+        if wname not in self.direct:
+            return super().gemm_dgrad(wname, dY, M, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride,
+                                      relu_mask=relu_mask, ld_out=ld_out)
+        d = self._direct_info[wname]
+        nat.gemm_bf16_seg(dY, 0, d["shadow"], 0, M, d["rows"][-1], d["cols"], out, mode=mode, lda=dY.stride(0),
+                          ldb=d["ld"], ld_out=ld_out if ld_out is not None else out.stride(0), seg_mode=nat.SEG_B_N,
+                          seg_rows=d["rows"], wait_flags=d["ver"], wait_value_ptr=self.step_ptr(), bn=bn,
+                          splits=splits, split_stride=split_stride, relu_mask=relu_mask,
+                          ld_mask=relu_mask.stride(0) if relu_mask is not None else 0)
+
+    def gemm_wgrad(self, wname, X, dY, Bsz, *, bn):
+        if wname not in self.direct:
+            return super().gemm_wgrad(wname, X, dY, Bsz, bn=bn)
+        d = self._direct_info[wname]
+        nseg = len(d["slot"])
+        nat.gemm_bf16_seg(X, 1, [dY.data_ptr()] + [0] * (nseg - 1), 1, d["rows"][-1], d["cols"], Bsz, None,
+                          mode=nat.EPI_STORE_F32, lda=X.stride(0), ldb=dY.stride(0), ld_out=d["cols"],
+                          seg_mode=nat.SEG_OUT_M, seg_rows=d["rows"], out_ptrs=d["slot"], bn=bn)

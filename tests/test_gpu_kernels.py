@@ -46,6 +46,12 @@ def test_gemm_fwd_kmajor_a_mnmajor_b(nat, M, N, K, bn, splits):
     nat.gemm_bf16(A, 0, W, 1, M, N, K, out, mode=mode, bn=bn, splits=splits)
     torch.cuda.synchronize()
     assert rel_err(out, ref) < 2e-3
+    if splits > 1:  # split-K without atomics: partial planes, summed by the consumer
+        planes = torch.zeros(splits, M, N, device=DEV)
+        nat.gemm_bf16(A, 0, W, 1, M, N, K, planes, mode=nat.EPI_STORE_F32, bn=bn, splits=splits, split_stride=M * N,
+                      ld_out=N)
+        torch.cuda.synchronize()
+        assert rel_err(planes.sum(0), ref) < 2e-3
     # the CUDA-core reference kernel agrees too
     out2 = torch.zeros(M, N, device=DEV)
     nat.gemm_ref(A, W, M, N, K, out2)
@@ -209,7 +215,8 @@ def test_pool2_bwd(nat):
     pool_bf = bf(pooled.detach())
     dy = torch.empty(B, 14, 14, 64, device=DEV, dtype=torch.bfloat16)
     db = torch.zeros(64, device=DEV)
-    nat.pool2_bwd(dpool, pool_bf, am, dy, db, B)
+    parts = torch.stack([0.5 * dpool, 0.25 * dpool, 0.25 * dpool])
+    nat.pool2_bwd(parts, pool_bf, am, dy, db, B, nsplit=3, split_stride=dpool.numel())
     torch.cuda.synchronize()
     g = dpool * (pooled.detach() > 0)
     ref = torch.zeros(B, 7, 7, 64, 4, device=DEV).scatter_(4, am.long().unsqueeze(-1), g.unsqueeze(-1))
@@ -234,7 +241,9 @@ def test_head_cnn_mode_matches_oracle(nat, keep_prob):
     lr_ = torch.empty(B, device=DEV)
     hit = torch.empty(B, device=DEV, dtype=torch.uint8)
     mask = torch.ones(B, H, device=DEV, dtype=torch.uint8)
-    nat.head_rows(pre, None, bias, ow, ob, y, B, H, H, keep_prob, 123, 5, True, hid, dhid, dl, lr_, hit, mask)
+    pre2 = torch.stack([0.25 * pre, 0.75 * pre])  # two split-K partial planes
+    nat.head_rows(pre2, None, bias, ow, ob, y, B, H, H, keep_prob, 123, 5, True, hid, dhid, dl, lr_, hit, mask,
+                  pre_nsplit=2, pre_split_stride=B * H)
     dow = torch.empty(H, 10, device=DEV)
     dhb = torch.empty(H, device=DEV)
     dob = torch.empty(10, device=DEV)
@@ -320,7 +329,7 @@ def test_adam_apply_matches_tf_form_and_publishes_shadow(nat):
     shadow = torch.zeros(40 * 64 + 104, device=DEV, dtype=torch.bfloat16)
     pieces = [Piece(0, 40 * 64, 64, 64, 0), Piece(40 * 64, 100, 100, 104, 40 * 64)]
     slots = [torch.randn(n, device=DEV) for _ in range(3)]
-    ptrs = torch.tensor([s.data_ptr() for s in slots], dtype=torch.int64, device=DEV)
+    ptrs = [s.data_ptr() for s in slots]
     ctrl = torch.zeros(8, dtype=torch.int32, device=DEV)  # [0]=t [1]=scratch [2]=version [3]=global_step
     ref = {"w": w0.clone().cpu()}
     opt = oracle.TFAdam(0.01)
@@ -347,3 +356,34 @@ def test_push_pull_single_gpu(nat):
     for s, d, b in zip(src, dst, back):
         assert torch.allclose(d, 0.5 * s) and torch.equal(d, b)
     assert ctrl[0].item() == 1 and ctrl[1].item() == 1 and ctrl[2].item() == 0
+
+
+def test_gemm_segmented_operands_single_gpu(nat):
+    """The sharded-operand paths of the fused pull/push GEMM, with the shards as separate local allocations."""
+    torch.manual_seed(13)
+    B_, Kin, H = 128, 3136, 1024
+    bounds = [0, 1152, 2176, 3136]  # multiples of 128
+    x = bf(torch.randn(B_, Kin, device=DEV))
+    W = bf(torch.randn(Kin, H, device=DEV))
+    dy = bf(torch.randn(B_, H, device=DEV))
+    pieces = [W[bounds[i]:bounds[i + 1]].clone() for i in range(3)]
+    flags = torch.tensor([5, 5, 7], dtype=torch.int32, device=DEV)
+    fl = [flags[i:].data_ptr() for i in range(3)]
+    # forward: K rows sharded, version-gated
+    planes = torch.zeros(4, B_, H, device=DEV)
+    nat.gemm_bf16_seg(x, 0, [p.data_ptr() for p in pieces], 1, B_, H, Kin, planes, mode=nat.EPI_STORE_F32, lda=Kin,
+                      ldb=H, ld_out=H, seg_mode=nat.SEG_B_K, seg_rows=bounds, wait_flags=fl, wait_value=5, bn=64,
+                      splits=4, split_stride=B_ * H)
+    # dgrad: N rows sharded
+    dplanes = torch.zeros(2, B_, Kin, device=DEV)
+    nat.gemm_bf16_seg(dy, 0, [p.data_ptr() for p in pieces], 0, B_, Kin, H, dplanes, mode=nat.EPI_STORE_F32, lda=H,
+                      ldb=H, ld_out=Kin, seg_mode=nat.SEG_B_N, seg_rows=bounds, wait_flags=fl, wait_value=5, bn=64,
+                      splits=2, split_stride=B_ * Kin)
+    # wgrad: output rows sharded (fused push into per-shard slots)
+    slots = [torch.zeros(bounds[i + 1] - bounds[i], H, device=DEV) for i in range(3)]
+    nat.gemm_bf16_seg(x, 1, [dy.data_ptr(), 0, 0], 1, Kin, H, B_, None, mode=nat.EPI_STORE_F32, lda=Kin, ldb=H,
+                      ld_out=H, seg_mode=nat.SEG_OUT_M, seg_rows=bounds, out_ptrs=[t.data_ptr() for t in slots], bn=128)
+    torch.cuda.synchronize()
+    assert rel_err(torch.cat(slots, 0), x.float().t() @ dy.float()) < 2e-3
+    assert rel_err(planes.sum(0), x.float() @ W.float()) < 2e-3
+    assert rel_err(dplanes.sum(0), dy.float() @ W.float().t()) < 2e-3

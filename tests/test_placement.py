@@ -24,10 +24,10 @@ def test_sharded_placement_splits_wd1_on_k_blocks():
         assert len(rows) == S
         assert rows[0][1] == 0 and rows[-1][2] == 3136
         for (s, r0, r1) in rows:
-            assert r0 % 64 == 0
+            assert r0 % 128 == 0
         if S > 1:
             sizes = [r1 - r0 for _, r0, r1 in rows]
-            assert max(sizes) - min(sizes) <= 64
+            assert max(sizes) - min(sizes) <= 128
         for p in pl.shard_pieces(0):
             assert p.offset % 64 == 0
         assert "weights/wd1" in pl.table()
