@@ -44,8 +44,8 @@ void tfd_set_error(const char* fmt, ...);
 namespace tfd {
 
 // Every spin in this library is bounded: a protocol bug must end in a trap (process exits with
-// an error), never in a hung GPU box.  ~4 s at the globaltimer resolution.
-constexpr unsigned long long kSpinTimeoutNs = 4000000000ull;
+// an error), never in a hung GPU box.  20 s at the globaltimer resolution (ranks may be seconds apart at start-up).
+constexpr unsigned long long kSpinTimeoutNs = 20000000000ull;
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;

@@ -1,0 +1,110 @@
+"""Multi-GPU ps/worker check, run under torchrun (one rank per GPU):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        scripts/cluster_check.py --layout colocated
+
+Every rank trains a few synchronous steps through GpuClusterEngine; rank 0 then checks the pushed gradients
+against the CPU oracle, the Adam update against the average of the pushed gradients, and the counters."""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from tensorflow_distributed_b200.models.spec import make_spec  # noqa: E402
+from tensorflow_distributed_b200.ops import oracle  # noqa: E402
+from tensorflow_distributed_b200.parallel.ps_gpu import GpuClusterEngine, Topology  # noqa: E402
+
+
+def rel(a, b):
+    return (a.float() - b.float()).abs().max().item() / (b.float().abs().max().item() + 1e-20)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--layout", default="colocated")
+    ap.add_argument("--ps", type=int, default=0)
+    ap.add_argument("--model", default="cnn")
+    ap.add_argument("--hidden", type=int, default=512)
+    ap.add_argument("--layers", type=int, default=2)
+    ap.add_argument("--steps", type=int, default=12)
+    a = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    device = torch.device("cuda:%d" % local)
+    dist.init_process_group("nccl", device_id=device)
+    spec = make_spec(a.model, a.hidden, a.layers)
+    topo = Topology.make(world, a.layout, a.ps)
+    eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05)
+    B = 128
+    keep = 1.0
+    w = topo.worker_of(rank)
+    rng = np.random.RandomState(100 + (w if w is not None else 99))
+    xs = [rng.rand(B, 784).astype(np.float32) for _ in range(a.steps)]
+    ys = [np.eye(10, dtype=np.float32)[rng.randint(0, 10, size=B)] for _ in range(a.steps)]
+    p0 = eng.get_params()
+    dist.barrier()
+    # ---- step 1 (eager) ----
+    l1 = eng.train_step(xs[0], ys[0], keep, fetch_loss=True)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ok = True
+    msgs = []
+    if rank == 0:
+        p0r = {k: (v.to(torch.bfloat16).float() if k in eng.direct or k == "weights/wc2" or k.startswith("weights/h")
+                   else v) for k, v in p0.items()}
+        slots = [eng.get_slot_grads(i) for i in range(topo.num_workers)]
+        for i in range(topo.num_workers):
+            r2 = np.random.RandomState(100 + i)
+            x = torch.from_numpy([r2.rand(B, 784).astype(np.float32) for _ in range(a.steps)][0])
+            y = torch.from_numpy(np.eye(10, dtype=np.float32)[r2.randint(0, 10, size=B)])
+            xin = x.to(torch.bfloat16).float() if a.model == "mlp" else x
+            _, og, _ = oracle.loss_and_grads(a.model, xin, y, p0r)
+            for k in og:
+                e = rel(slots[i][k], og[k])
+                if e > 0.1:
+                    ok = False
+                    msgs.append("worker %d grad %s rel err %.3f" % (i, k, e))
+        avg = {k: sum(s[k] for s in slots) / topo.num_workers for k in slots[0]}
+        ref = {k: v.clone() for k, v in p0.items()}
+        oracle.TFAdam(0.01).apply(ref, avg)
+        p1 = eng.get_params()
+        for k in ref:
+            if not torch.allclose(p1[k], ref[k], atol=2e-5, rtol=1e-4):
+                ok = False
+                msgs.append("adam mismatch %s max diff %.3e" % (k, (p1[k] - ref[k]).abs().max().item()))
+        if eng.global_step != 1:
+            ok = False
+            msgs.append("global_step %d != 1" % eng.global_step)
+    dist.barrier()
+    # ---- more steps (second is eager warm-up of the graph path, then captured graphs) ----
+    losses = [l1]
+    for s in range(1, a.steps):
+        losses.append(eng.train_step(xs[s % 4], ys[s % 4], keep, fetch_loss=True))
+    torch.cuda.synchronize()
+    dist.barrier()
+    gs = eng.global_step
+    acc = eng.eval_accuracy(xs[0], ys[0]) if eng.is_worker else 0.0
+    if rank == 0:
+        if gs != a.steps:
+            ok = False
+            msgs.append("global_step %d != %d" % (gs, a.steps))
+    if eng.is_worker and not (losses[-1] < losses[0]):
+        ok = False
+        msgs.append("rank %d loss did not decrease: %.4f -> %.4f" % (rank, losses[0], losses[-1]))
+    flag = torch.tensor([0 if ok else 1], device=device)
+    dist.all_reduce(flag)
+    print("rank %d %s %s losses %.4f -> %.4f acc %.3f gs %d %s" % (rank, topo.describe(), "OK" if ok else "FAIL",
+                                                                 losses[0], losses[-1], acc, gs, "; ".join(msgs)), flush=True)
+    eng.shutdown()
+    dist.destroy_process_group()
+    sys.exit(1 if flag.item() else 0)
+
+
+if __name__ == "__main__":
+    main()

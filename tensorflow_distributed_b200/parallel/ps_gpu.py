@@ -257,3 +257,116 @@ class GpuClusterEngine(NativeEngine):
         nat.gemm_bf16_seg(X, 1, [dY.data_ptr()] + [0] * (nseg - 1), 1, d["rows"][-1], d["cols"], Bsz, None,
                           mode=nat.EPI_STORE_F32, lda=X.stride(0), ldb=dY.stride(0), ld_out=d["cols"],
                           seg_mode=nat.SEG_OUT_M, seg_rows=d["rows"], out_ptrs=d["slot"], bn=bn)
+
+    # ---- step pieces -----------------------------------------------------------------------
+    def _pre_step(self, ws, training: bool) -> None:
+        """Pull (X1): small tensors are copied once the owning shard's version has caught up with this
+        worker's step counter; the same kernel thereby waits for every shard (slots are free to overwrite)."""
+        p = self._pull
+        nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
+                       want_ptr=self.step_ptr())
+
+    def _post_backward(self, ws) -> None:
+        """Push (X2): small gradients into this worker's slots, then arrive += 1 on every shard."""
+        p = self._push
+        nat.push_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], self._arrive, 1.0,
+                       self.ctrl[WCTRL_PUSHBLK:], local_step=self.ctrl[WCTRL_STEP:])
+
+    def _apply(self) -> None:
+        """Shard-side reduce + 1/R + Adam + shadow publish, gated on the arrivals of this step."""
+        if not self.is_ps:
+            return
+        s = self.shard
+        nat.adam_apply(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, 1.0 / self.num_workers, s.n,
+                       s.pieces, self.lr, s.ctrl[CTRL_T:], s.ctrl[CTRL_ARRIVE:], s.ctrl[CTRL_VERSION:],
+                       s.ctrl[CTRL_GSTEP:])
+
+    def _sequence(self, ws, mode: str, keep_prob: float, mask_out=None) -> None:
+        if self.is_worker:
+            return super()._sequence(ws, mode, keep_prob, mask_out)
+        if mode == "train":  # dedicated ps: nothing but the apply, like the reference's passive ps (m:160-161)
+            self._apply()
+
+    # ---- public API ------------------------------------------------------------------------
+    def workspace(self, B: int) -> Workspace:
+        if B not in self.ws:
+            self.ws[B] = Workspace(self.spec, B if self.is_worker else 1, self.device)
+            self.ws[B].B = B if self.is_worker else 1
+        return self.ws[B]
+
+    def load_batch(self, ws, x, y) -> None:
+        if self.is_worker:
+            super().load_batch(ws, x, y)
+
+    @property
+    def global_step(self) -> int:
+        t = nat.tensor_from_ptr(self._ctrl_ptr(self.placement.global_step_shard, CTRL_GSTEP), 1, torch.int32, self.device)
+        return int(t.item())
+
+    def describe(self) -> str:
+        return self.topo.describe() + " sync"
+
+    def _read_arena(self, which: str) -> Dict[str, torch.Tensor]:
+        """Gather a full name->tensor dict by reading every shard's arena through the peer mapping."""
+        torch.cuda.synchronize(self.device)
+        out = {}
+        for v in self.spec.variables:
+            parts = []
+            for p in sorted(self.placement.pieces[v.name], key=lambda q: q.row_start):
+                r = self._ps_rank(p.shard)
+                base = self.peer_base[r] + getattr(self.layouts[r], which) + 4 * p.offset
+                parts.append(nat.tensor_from_ptr(base, p.numel, torch.float32, self.device).cpu()
+                             .view(p.row_end - p.row_start, p.cols))
+            out[v.name] = torch.cat(parts, 0).reshape(v.shape).clone()
+        return out
+
+    def get_params(self) -> Dict[str, torch.Tensor]:
+        return self._read_arena("w")
+
+    def get_adam_state(self) -> dict:
+        r = self._ps_rank(0)
+        t = int(nat.tensor_from_ptr(self._ctrl_ptr(0, CTRL_T), 1, torch.int32, self.device).item())
+        return {"t": t, "beta1_power": 0.9 ** t, "beta2_power": 0.999 ** t, "m": self._read_arena("m"),
+                "v": self._read_arena("v")}
+
+    def get_grads(self):
+        raise NotImplementedError("gradients live in the ps staging slots; use get_slot_grads()")
+
+    def get_slot_grads(self, worker: int) -> Dict[str, torch.Tensor]:
+        """What worker `worker` pushed last (read back from the shards' staging slots): tests."""
+        torch.cuda.synchronize(self.device)
+        out = {}
+        for v in self.spec.variables:
+            parts = []
+            for p in sorted(self.placement.pieces[v.name], key=lambda q: q.row_start):
+                r = self._ps_rank(p.shard)
+                base = self.peer_base[r] + self.layouts[r].slot(worker) + 4 * p.offset
+                parts.append(nat.tensor_from_ptr(base, p.numel, torch.float32, self.device).cpu()
+                             .view(p.row_end - p.row_start, p.cols))
+            out[v.name] = torch.cat(parts, 0).reshape(v.shape).clone()
+        return out
+
+    def set_params(self, params: Dict[str, torch.Tensor]) -> None:
+        """Chief-side restore: every ps rank copies its own pieces (call on all ranks with the same dict)."""
+        if self.is_ps:
+            s = self.shard
+            for v in self.spec.variables:
+                p = s.piece_of(v.name)
+                if p is not None:
+                    full = params[v.name].to(torch.float32).reshape(-1, p.cols)
+                    s.view(s.w, v.name).copy_(full[p.row_start:p.row_end].to(self.device))
+            s.publish_shadow()
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+
+    def shutdown(self) -> None:
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+        for p in self._opened:
+            nat.ipc_close(p)
+        self._opened = []
+
+    @classmethod
+    def from_bench_args(cls, spec, a, rank: int, world: int, device) -> "GpuClusterEngine":
+        topo = Topology.make(world, a.layout, a.ps)
+        return cls(spec, topo, rank, device, learning_rate=0.01, seed=0, init_stddev=a.init_stddev)
