@@ -363,3 +363,78 @@ extern "C" int tfd_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   return tfd_gemm_bf16_seg(A, lda, a_mn, bp, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
                            ld_mask, split_stride, TFD_SEG_NONE, 1, nullptr, nullptr, wf, wait_value, nullptr, stream);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Split-K GEMM for callers that cannot allocate.
+//
+// The split-K path above needs scratch: one fp32 partial plane per split, summed afterwards.  Normally the
+// caller allocates those planes.  Some callers cannot: a host that has handed every byte of HBM to its own pool
+// (or runs under a fixed memory budget) has nothing left to cudaMalloc from, and a latency-critical serving loop
+// must not enter the CUDA allocator at all, because cudaMalloc/cudaFree synchronise the whole device under the
+// other streams' feet.  For them the planes live in the file-scope array below: it is part of the library image,
+// so every GPU that loads the library carries these 8 MiB from load time until the process exits, whether or not
+// this entry point is ever called.
+//
+// The array's name is only a host-side stand-in for the device object -- handing it to a kernel would make the
+// kernel use host (or unmapped) memory -- so the first call on each device asks the runtime for the real device
+// address with cudaGetSymbolAddress, with that device current, and keeps it.  That first call therefore does
+// one-time set-up work (address lookup, kernel attribute) and should be made before any stream capture begins.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr long long kNoAllocScratchFloats = 2ll << 20;  // 2 Mi floats = 8 MiB: splits * M * N must fit
+static __device__ __align__(256) float g_noalloc_planes[kNoAllocScratchFloats];
+
+constexpr int kMaxDevices = 64;
+float* g_noalloc_planes_dev[kMaxDevices] = {nullptr};  // device address of the array, per device ordinal
+
+__global__ void __launch_bounds__(256)
+sum_planes_kernel(const float* __restrict__ planes, int nplanes, long long plane_stride, int M, int N,
+                  float* __restrict__ out, long long ld_out, const float* __restrict__ bias, int relu) {
+  const long long total = (long long)M * N;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / N), c = (int)(i % N);
+    float s = bias ? bias[c] : 0.f;
+    for (int z = 0; z < nplanes; ++z) s += planes[z * plane_stride + i];  // fixed order: deterministic
+    out[(long long)r * ld_out + c] = relu ? fmaxf(s, 0.f) : s;
+  }
+}
+
+}  // namespace
+
+extern "C" int tfd_gemm_bf16_splitk_noalloc(const void* A, long long lda, int a_mn, const void* B, long long ldb,
+                                            int b_mn, int M, int N, int K, int bn, int splits, float* out,
+                                            long long ld_out, const float* bias, int relu, void* stream) {
+  TFD_REQUIRE(M > 0 && N > 0 && K > 0, "splitk_noalloc: empty problem %dx%dx%d", M, N, K);
+  TFD_REQUIRE(splits >= 1, "splitk_noalloc: splits must be >= 1, got %d", splits);
+  const int kblocks = (K + BK - 1) / BK;
+  if (splits > kblocks) splits = kblocks;
+  const long long need = (long long)splits * M * N;
+  TFD_REQUIRE(need <= kNoAllocScratchFloats,
+              "splitk_noalloc: splits*M*N = %lld floats exceeds the built-in scratch of %lld floats (8 MiB); "
+              "use fewer splits or tfd_gemm_bf16 with caller-provided planes",
+              need, kNoAllocScratchFloats);
+  int dev = 0;
+  TFD_CUDA_CHECK(cudaGetDevice(&dev));
+  TFD_REQUIRE(dev >= 0 && dev < kMaxDevices, "splitk_noalloc: device ordinal %d out of range", dev);
+  if (g_noalloc_planes_dev[dev] == nullptr) {
+    // set-up, once per device, with that device current: the device address of the file-scope array
+    float* p = nullptr;
+    TFD_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_planes));
+    TFD_REQUIRE(p != nullptr, "splitk_noalloc: cudaGetSymbolAddress returned a null device address");
+    g_noalloc_planes_dev[dev] = p;
+  }
+  float* planes = g_noalloc_planes_dev[dev];
+  // Every plane element the reduction reads is written by this call's GEMM first, so nothing in the array has to
+  // start at zero and the previous call's contents are simply overwritten.
+  const long long plane_stride = (long long)M * N;
+  int rc = tfd_gemm_bf16(A, lda, a_mn, B, ldb, b_mn, M, N, K, bn, splits, TFD_EPI_STORE_F32, 1.0f, planes, N, nullptr,
+                         nullptr, 0, plane_stride, nullptr, 0, stream);
+  if (rc) return rc;
+  long long blocks = (plane_stride + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  sum_planes_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(planes, splits, plane_stride, M, N, out,
+                                                                                    ld_out, bias, relu);
+  TFD_LAUNCH_CHECK();
+  return 0;
+}

@@ -52,6 +52,21 @@ int tfd_gemm_bf16_seg(const void* A, long long lda, int a_mn, const void* const*
                       int nseg, const int* seg_rows, void* const* out_ptrs, const unsigned* const* wait_flags,
                       unsigned wait_value, const unsigned* wait_value_ptr, void* stream);
 
+/* Split-K GEMM that allocates nothing: out[M,N] fp32 = A*B (+bias, optional ReLU), same operand conventions as
+ * tfd_gemm_bf16.  No counterpart in the reference (it has no native code and no allocator contract at all).
+ * For callers that cannot call cudaMalloc -- hosts whose own pool already owns all device memory or that run
+ * under a fixed memory budget, and latency-critical loops that must not enter the CUDA allocator because
+ * cudaMalloc/cudaFree synchronise the device.  The split-K partial planes live in an 8 MiB static __device__
+ * array inside the library (every GPU that loads the library holds it until the process exits), so
+ * splits*M*N must be <= 2*1024*1024 floats; larger requests are rejected with an error message, nothing is run.
+ * The first call on each device looks the array's device address up (cudaGetSymbolAddress) and sets a kernel
+ * attribute: make that first call before any stream capture.  All calls share the one array and it keeps the
+ * last call's partial sums: calls that overlap on the GPU (different streams, or two host threads) race on it --
+ * serialise them.  Nothing in the array has to start at zero (each call writes every element it later reads). */
+int tfd_gemm_bf16_splitk_noalloc(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M,
+                                 int N, int K, int bn, int splits, float* out, long long ld_out, const float* bias,
+                                 int relu, void* stream);
+
 /* CUDA-core fp32 reference GEMM (validation only): D[M,N] = A[M,K](bf16,row) * B[K,N](bf16,row). */
 int tfd_gemm_ref(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, float* out,
                  long long ld_out, void* stream);
