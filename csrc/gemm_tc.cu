@@ -197,6 +197,45 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc_fence_after();
     const bool row_ok = row < p.M;
     const bool vec_ok = ((p.ld_out & 3) == 0);
+    if (p.mode == TFD_EPI_STORE_F32 && vec_ok && n0 + BN <= p.N) {
+      // Coalesced fp32 store: TMEM -> registers -> shared (the pipeline stages are idle by now) -> global, so a
+      // warp instruction writes whole 512 B row segments instead of 32 scattered 16 B pieces.  That matters most
+      // when `out` is a staging slot on another GPU: NVLink wants long contiguous writes.
+      constexpr int kPitch = BN + 4;  // floats; (BN/4 + 1) float4 per row is odd -> conflict-free both ways
+      float* stg = reinterpret_cast<float*>(smem) + (size_t)q * 32 * kPitch;
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 16) {
+        float v[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+          float4 o4 = make_float4(v[i] * p.alpha, v[i + 1] * p.alpha, v[i + 2] * p.alpha, v[i + 3] * p.alpha);
+          if (p.bias) {
+            o4.x += __ldg(p.bias + n0 + c + i); o4.y += __ldg(p.bias + n0 + c + i + 1);
+            o4.z += __ldg(p.bias + n0 + c + i + 2); o4.w += __ldg(p.bias + n0 + c + i + 3);
+          }
+          *reinterpret_cast<float4*>(stg + lane * kPitch + c + i) = o4;
+        }
+      }
+      __syncwarp();
+      float* obase = out_f32 + (long long)blockIdx.z * p.split_stride + n0;
+      constexpr int kLanesPerRow = BN / 4;                       // float4 per row
+      constexpr int kRowsPerInst = kLanesPerRow >= 32 ? 1 : 32 / kLanesPerRow;
+      constexpr int kInstPerRow = kLanesPerRow >= 32 ? kLanesPerRow / 32 : 1;
+#pragma unroll 4
+      for (int r0 = 0; r0 < 32; r0 += kRowsPerInst) {
+        const int r = r0 + (kLanesPerRow >= 32 ? 0 : lane / kLanesPerRow);
+        const int grow = m0 + q * 32 + r;
+#pragma unroll
+        for (int k = 0; k < kInstPerRow; ++k) {
+          const int col = ((kLanesPerRow >= 32 ? lane : lane % kLanesPerRow) + 32 * k) * 4;
+          if (grow < p.M) {
+            const float4 o4 = *reinterpret_cast<const float4*>(stg + r * kPitch + col);
+            *reinterpret_cast<float4*>(obase + (long long)(out_row - lane + r) * p.ld_out + col) = o4;
+          }
+        }
+      }
+    } else
 #pragma unroll 1
     for (int c = 0; c < BN; c += 16) {
       float v[16];

@@ -31,6 +31,10 @@ struct AdamArgs {
   const unsigned* wait_counter; // arrivals (local memory, incremented by workers over NVLink)
   unsigned* version_flag;
   unsigned* global_step;
+  // async (apply-on-arrival): serve exactly one ticket of the shard's arrival ring
+  unsigned* queue;              // ring of qlen words: worker id + 1 once that worker's slot is complete, else 0
+  int qlen;
+  const unsigned* shutdown;     // non-zero: leave without applying (the ps is being released)
 };
 
 __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __grid_constant__ PieceTable pt) {
@@ -40,6 +44,30 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   if (a.wait_counter) {
     if (threadIdx.x == 0) spin_until_ge(a.wait_counter, (unsigned)a.num_slots * t, "adam: gradient arrivals");
     __syncthreads();
+  }
+  const float* serve_slot = nullptr;
+  if (a.queue) {
+    // apply-on-arrival in ticket order: ticket (t-1) is the next one this shard serves.  Every block reads the
+    // same ring entry; the last block clears it after all blocks are done.
+    __shared__ unsigned s_who;
+    if (threadIdx.x == 0) {
+      const unsigned* q = a.queue + ((t - 1) % (unsigned)a.qlen);
+      unsigned who = ld_acquire_sys_u32(q);
+      unsigned long long t0 = globaltimer_ns();
+      unsigned it = 0;
+      while (who == 0 && !(a.shutdown && ld_acquire_sys_u32(a.shutdown) != 0)) {
+        __nanosleep(128);
+        who = ld_acquire_sys_u32(q);
+        if ((++it & 0xff) == 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) {
+          printf("tfd: async apply waited 20 s for ticket %u\n", t - 1);
+          __trap();
+        }
+      }
+      s_who = who;
+    }
+    __syncthreads();
+    if (s_who == 0) return;  // shutdown
+    serve_slot = a.slots[s_who - 1];
   }
   // 1 - beta^t through expm1 keeps full relative accuracy for small t (where beta^t is close to 1)
   const float om_b1t = -expm1f((float)t * logf(a.beta1)), om_b2t = -expm1f((float)t * logf(a.beta2));
@@ -54,9 +82,9 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
       w4[h] = *reinterpret_cast<const float4*>(a.w + i + 4 * h);
       m4[h] = *reinterpret_cast<const float4*>(a.m + i + 4 * h);
       v4[h] = *reinterpret_cast<const float4*>(a.v + i + 4 * h);
-      g4[h] = *reinterpret_cast<const float4*>(a.slots[0] + i + 4 * h);
+      g4[h] = *reinterpret_cast<const float4*>((serve_slot ? serve_slot : a.slots[0]) + i + 4 * h);
     }
-    for (int r = 1; r < a.num_slots; ++r) {
+    for (int r = 1; r < (serve_slot ? 1 : a.num_slots); ++r) {
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const float4 x = *reinterpret_cast<const float4*>(a.slots[r] + i + 4 * h);
@@ -117,6 +145,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
     if (done == gridDim.x - 1) {
       a.t_counter[1] = 0;
       a.t_counter[0] = t;
+      if (a.queue) a.queue[(t - 1) % (unsigned)a.qlen] = 0;
       if (a.global_step) *a.global_step = *a.global_step + 1;
       __threadfence_system();
       if (a.version_flag) st_release_sys_u32(a.version_flag, t);
@@ -132,8 +161,12 @@ struct PushSeg {
 constexpr int kMaxSegs = 32;
 struct PushTable {
   PushSeg seg[kMaxSegs];
-  unsigned* arrive[kMaxSegs];
+  unsigned* arrive[kMaxSegs];   // sync: per-shard arrival counter.  async: per-shard ticket dispenser
+  unsigned* queue[kMaxSegs];    // async: per-shard arrival ring
   int nseg, narrive;
+  int qlen;                     // > 0 selects the async (ticket) protocol
+  unsigned worker;              // this worker's index
+  unsigned* my_ticket;          // async: local array [narrive]; receives ticket+1 = the version that serves it
 };
 
 // grid (blocks_per_seg, nseg)
@@ -155,7 +188,16 @@ __global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushT
     if (atomicAdd(block_counter, 1u) == total - 1) {
       *block_counter = 0;
       __threadfence_system();
-      for (int k = 0; k < t.narrive; ++k) atom_add_release_sys_u32(t.arrive[k], 1u);
+      if (t.qlen > 0) {
+        // apply-on-arrival: take a ticket on every shard, then publish "worker w's slot is ready" in that ring cell
+        for (int k = 0; k < t.narrive; ++k) {
+          const unsigned tk = atom_add_release_sys_u32(t.arrive[k], 1u);
+          st_release_sys_u32(t.queue[k] + (tk % (unsigned)t.qlen), t.worker + 1u);
+          t.my_ticket[k] = tk + 1u;
+        }
+      } else {
+        for (int k = 0; k < t.narrive; ++k) atom_add_release_sys_u32(t.arrive[k], 1u);
+      }
       if (local_step) *local_step = *local_step + 1;
     }
   }
@@ -166,6 +208,7 @@ struct PullSeg {
   float* dst;
   long long n;
   const unsigned* version;
+  const unsigned* want_seg;     // optional: wait for *version >= *want_seg instead of the common value
 };
 struct PullTable {
   PullSeg seg[kMaxSegs];
@@ -177,7 +220,7 @@ __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullT
   const PullSeg s = t.seg[blockIdx.y];
   const unsigned want = want_base + (want_ptr ? *want_ptr : 0u);
   if (s.version) {
-    if (threadIdx.x == 0) spin_until_ge(s.version, want, "pull: parameter version");
+    if (threadIdx.x == 0) spin_until_ge(s.version, s.want_seg ? *s.want_seg : want, "pull: parameter version");
     __syncthreads();
   }
   const long long n4 = s.n >> 2;
@@ -191,10 +234,11 @@ __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullT
 
 #define ST(s) static_cast<cudaStream_t>(s)
 
-extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
-                              float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
-                              float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
-                              unsigned* version_flag, unsigned* global_step, void* stream) {
+static int adam_launch(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
+                       float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
+                       float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
+                       unsigned* version_flag, unsigned* global_step, unsigned* queue, int qlen,
+                       const unsigned* shutdown, void* stream) {
   TFD_REQUIRE(n % 8 == 0, "adam: arena length %lld not a multiple of 8", n);
   TFD_REQUIRE(num_pieces <= kMaxPieces, "adam: too many pieces (%d)", num_pieces);
   TFD_REQUIRE(num_slots >= 1, "adam: need at least one gradient slot");
@@ -207,6 +251,7 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
   for (int i = 0; i < TFD_MAX_SLOTS; ++i) a.slots[i] = i < num_slots ? slots[i] : nullptr;
   a.num_slots = num_slots; a.scale = scale; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
   a.t_counter = t_counter; a.wait_counter = wait_counter; a.version_flag = version_flag; a.global_step = global_step;
+  a.queue = queue; a.qlen = qlen; a.shutdown = shutdown;
   long long blocks = (n / 8 + 255) / 256;
   if (blocks > 148 * 3) blocks = 148 * 3;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
   adam_apply_kernel<<<(unsigned)blocks, 256, 0, ST(stream)>>>(a, pt);
@@ -214,14 +259,35 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
   return 0;
 }
 
+extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
+                              float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
+                              float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
+                              unsigned* version_flag, unsigned* global_step, void* stream) {
+  return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
+                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, stream);
+}
+
+extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
+                              long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1, float beta2,
+                              float eps, unsigned* t_counter, unsigned* queue, int qlen, const unsigned* shutdown,
+                              unsigned* version_flag, unsigned* global_step, void* stream) {
+  TFD_REQUIRE(queue != nullptr && qlen >= num_slots, "adam_serve: ring of %d cells cannot hold %d workers", qlen, num_slots);
+  return adam_launch(w, m, v, shadow, slots, num_slots, 1.0f, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
+                     nullptr, version_flag, global_step, queue, qlen, shutdown, stream);
+}
+
 /* Multi-segment push: segs[i] = {src, dst, n}; after every segment is written the last block adds 1 to each
  * arrive counter.  (tfd_push_grads is the single-segment convenience form.) */
-extern "C" int tfd_push_multi(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
-                              unsigned* const* arrive, int narrive, float scale, unsigned* block_counter,
-                              unsigned* local_step, void* stream) {
+static int push_launch(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
+                       unsigned* const* arrive, int narrive, float scale, unsigned* block_counter,
+                       unsigned* local_step, unsigned* const* queues, int qlen, unsigned worker, unsigned* my_ticket,
+                       void* stream) {
   TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSegs && narrive <= kMaxSegs, "push: bad segment count %d/%d", nseg, narrive);
   PushTable t;
+  memset(&t, 0, sizeof(t));
   t.nseg = nseg; t.narrive = narrive;
+  t.qlen = qlen; t.worker = worker; t.my_ticket = my_ticket;
+  for (int i = 0; i < narrive && queues; ++i) t.queue[i] = queues[i];
   long long maxn = 0;
   for (int i = 0; i < nseg; ++i) {
     t.seg[i] = PushSeg{static_cast<const float*>(srcs[i]), static_cast<float*>(dsts[i]), ns[i]};
@@ -237,6 +303,21 @@ extern "C" int tfd_push_multi(const void* const* srcs, void* const* dsts, const 
   return 0;
 }
 
+extern "C" int tfd_push_multi(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
+                              unsigned* const* arrive, int narrive, float scale, unsigned* block_counter,
+                              unsigned* local_step, void* stream) {
+  return push_launch(srcs, dsts, ns, nseg, arrive, narrive, scale, block_counter, local_step, nullptr, 0, 0, nullptr, stream);
+}
+
+extern "C" int tfd_push_multi_async(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
+                                    unsigned* const* tickets, unsigned* const* queues, int nshards, int qlen,
+                                    unsigned worker, unsigned* my_ticket, unsigned* block_counter, unsigned* local_step,
+                                    void* stream) {
+  TFD_REQUIRE(qlen > 0 && my_ticket != nullptr && queues != nullptr, "push_async: ring / ticket array missing");
+  return push_launch(srcs, dsts, ns, nseg, tickets, nshards, 1.0f, block_counter, local_step, queues, qlen, worker,
+                     my_ticket, stream);
+}
+
 extern "C" int tfd_push_grads(const float* src, float* dst, long long n, float scale, unsigned* arrive_counter,
                               unsigned* block_counter, void* stream) {
   const void* s[1] = {src};
@@ -246,16 +327,17 @@ extern "C" int tfd_push_grads(const float* src, float* dst, long long n, float s
   return tfd_push_multi(s, d, ns, 1, a, arrive_counter ? 1 : 0, scale, block_counter, nullptr, stream);
 }
 
-extern "C" int tfd_pull_multi(const void* const* srcs, void* const* dsts, const long long* ns,
-                              const unsigned* const* versions, int nseg, unsigned want_version,
-                              const unsigned* want_ptr, void* stream) {
+static int pull_launch(const void* const* srcs, void* const* dsts, const long long* ns,
+                       const unsigned* const* versions, const unsigned* const* want_segs, int nseg,
+                       unsigned want_version, const unsigned* want_ptr, void* stream) {
   TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSegs, "pull: bad segment count %d", nseg);
   PullTable t;
   memset(&t, 0, sizeof(t));
   t.nseg = nseg;
   long long maxn = 0;
   for (int i = 0; i < nseg; ++i) {
-    t.seg[i] = PullSeg{static_cast<const float*>(srcs[i]), static_cast<float*>(dsts[i]), ns[i], versions ? versions[i] : nullptr};
+    t.seg[i] = PullSeg{static_cast<const float*>(srcs[i]), static_cast<float*>(dsts[i]), ns[i], versions ? versions[i] : nullptr,
+                        want_segs ? want_segs[i] : nullptr};
     if (ns[i] > maxn) maxn = ns[i];
   }
   long long bx = (maxn / 4 + 255) / 256;
@@ -264,6 +346,18 @@ extern "C" int tfd_pull_multi(const void* const* srcs, void* const* dsts, const 
   pull_kernel<<<dim3((unsigned)bx, nseg), 256, 0, ST(stream)>>>(t, want_version, want_ptr);
   TFD_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int tfd_pull_multi(const void* const* srcs, void* const* dsts, const long long* ns,
+                              const unsigned* const* versions, int nseg, unsigned want_version,
+                              const unsigned* want_ptr, void* stream) {
+  return pull_launch(srcs, dsts, ns, versions, nullptr, nseg, want_version, want_ptr, stream);
+}
+
+extern "C" int tfd_pull_multi_async(const void* const* srcs, void* const* dsts, const long long* ns,
+                                    const unsigned* const* versions, const unsigned* const* want_segs, int nseg,
+                                    void* stream) {
+  return pull_launch(srcs, dsts, ns, versions, want_segs, nseg, 0, nullptr, stream);
 }
 
 extern "C" int tfd_pull_params(const float* src, float* dst, long long n, const unsigned* version_flag, unsigned version,

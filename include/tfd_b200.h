@@ -179,6 +179,24 @@ int tfd_push_multi(const void* const* srcs, void* const* dsts, const long long* 
 int tfd_pull_multi(const void* const* srcs, void* const* dsts, const long long* ns, const unsigned* const* versions,
                    int nseg, unsigned want_version, const unsigned* want_ptr, void* stream);
 
+/* ---- asynchronous replicas: apply on arrival, in per-shard ticket order (m:72-75 with sync_replicas=False) ----
+ * Worker: after its slot on a shard is complete it takes a ticket (atomic add on the shard's dispenser word) and
+ * writes worker+1 into ring cell ticket % qlen (release); my_ticket[k] (local) receives ticket+1, the shard version
+ * at which that gradient has been applied -- the worker waits for it before overwriting its slot again
+ * (tfd_pull_multi_async: segment i waits for *versions[i] >= *want_segs[i]).
+ * Shard: tfd_adam_serve applies exactly ONE gradient: the slot named by ring cell (t mod qlen), scale 1, then clears
+ * the cell, bumps t / global_step and releases version = t+1.  Every arriving gradient is applied exactly once, in
+ * ticket order, and no worker ever waits for another worker.  *shutdown != 0 makes a waiting serve kernel leave. */
+int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots, long long n,
+                   const tfd_piece_t* pieces, int num_pieces, float lr, float beta1, float beta2, float eps,
+                   unsigned* t_counter, unsigned* queue, int qlen, const unsigned* shutdown, unsigned* version_flag,
+                   unsigned* global_step, void* stream);
+int tfd_push_multi_async(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
+                         unsigned* const* tickets, unsigned* const* queues, int nshards, int qlen, unsigned worker,
+                         unsigned* my_ticket, unsigned* block_counter, unsigned* local_step, void* stream);
+int tfd_pull_multi_async(const void* const* srcs, void* const* dsts, const long long* ns,
+                         const unsigned* const* versions, const unsigned* const* want_segs, int nseg, void* stream);
+
 /* ---- peer memory (symmetric heap over cudaIpc) ---- */
 int tfd_set_device(int device);
 int tfd_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out64);    /* cudaMalloc + cudaIpcGetMemHandle */

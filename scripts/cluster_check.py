@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--hidden", type=int, default=512)
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--steps", type=int, default=12)
+    ap.add_argument("--async_mode", action="store_true")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -40,7 +41,8 @@ def main():
     dist.init_process_group("nccl", device_id=device)
     spec = make_spec(a.model, a.hidden, a.layers)
     topo = Topology.make(world, a.layout, a.ps)
-    eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05)
+    eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05,
+                           async_mode=a.async_mode)
     B = 128
     keep = 1.0
     w = topo.worker_of(rank)
@@ -55,7 +57,7 @@ def main():
     dist.barrier()
     ok = True
     msgs = []
-    if rank == 0:
+    if rank == 0 and not a.async_mode:
         p0r = {k: (v.to(torch.bfloat16).float() if k in eng.direct or k == "weights/wc2" or k.startswith("weights/h")
                    else v) for k, v in p0.items()}
         slots = [eng.get_slot_grads(i) for i in range(topo.num_workers)]
@@ -91,15 +93,17 @@ def main():
     gs = eng.global_step
     acc = eng.eval_accuracy(xs[0], ys[0]) if eng.is_worker else 0.0
     if rank == 0:
-        if gs != a.steps:
+        # sync: one apply per global step.  async: every pushed gradient applied exactly once (no lost update)
+        want = a.steps * topo.num_workers if a.async_mode else a.steps
+        if gs != want:
             ok = False
-            msgs.append("global_step %d != %d" % (gs, a.steps))
+            msgs.append("global_step %d != %d" % (gs, want))
     if eng.is_worker and not (losses[-1] < losses[0]):
         ok = False
         msgs.append("rank %d loss did not decrease: %.4f -> %.4f" % (rank, losses[0], losses[-1]))
     flag = torch.tensor([0 if ok else 1], device=device)
     dist.all_reduce(flag)
-    print("rank %d %s %s losses %.4f -> %.4f acc %.3f gs %d %s" % (rank, topo.describe(), "OK" if ok else "FAIL",
+    print("rank %d %s %s losses %.4f -> %.4f acc %.3f gs %d %s" % (rank, eng.describe(), "OK" if ok else "FAIL",
                                                                  losses[0], losses[-1], acc, gs, "; ".join(msgs)), flush=True)
     eng.shutdown()
     dist.destroy_process_group()

@@ -268,20 +268,36 @@ class NativeEngine:
                       step_ptr=self.step_ptr() if training else None, pre_nsplit=ws.fc1_splits,
                       pre_split_stride=B * 1024)
 
+    def _side_streams(self):
+        if not hasattr(self, "_sides"):
+            self._sides = [torch.cuda.Stream(device=self.device) for _ in range(2)]
+        return self._sides
+
     def _cnn_backward(self, ws: Workspace) -> None:
+        """Backward as a DAG: the weight-gradient kernels are leaves (nothing downstream reads them before the
+        push/apply), so they run on side streams -- graph branches after capture -- next to the critical path
+        head -> fc1 dgrad -> pool2 bwd -> conv2 dgrad -> conv1 wgrad."""
         B = ws.B
-        nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, self.G("weights/out"),
-                      self.G("biases/bd1"), self.G("biases/out"), ws.scalars)
-        # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
-        self.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
+        main = torch.cuda.current_stream()
+        s1, s2 = self._side_streams()
+        s1.wait_stream(main)
+        with torch.cuda.stream(s1):
+            nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, self.G("weights/out"),
+                          self.G("biases/bd1"), self.G("biases/out"), ws.scalars)
+            # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
+            self.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
         # fc1 dgrad: dpool2[B,3136] = dhid wd1^T    (wd1 read K-major in place)
         self.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
                         split_stride=B * 3136, ld_out=3136)
         nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"), B, nsplit=ws.dg_splits,
                       split_stride=B * 3136)
-        nat.conv2_wgrad(ws.pool1, ws.dy2, self.G("weights/wc2"), B, ref=self.conv2_ref)
+        s2.wait_stream(main)
+        with torch.cuda.stream(s2):
+            nat.conv2_wgrad(ws.pool1, ws.dy2, self.G("weights/wc2"), B, ref=self.conv2_ref)
         nat.conv2_dgrad(ws.dy2, self.S("weights/wc2"), ws.dpool1, B, ref=self.conv2_ref)
         nat.conv1_wgrad(ws.x, ws.dpool1, ws.pool1, ws.am1, self.G("weights/wc1"), self.G("biases/bc1"), B)
+        main.wait_stream(s1)
+        main.wait_stream(s2)
 
     def _mlp_forward(self, ws: Workspace, training: bool) -> None:
         B, dims = ws.B, [784] + list(self.spec.hidden)

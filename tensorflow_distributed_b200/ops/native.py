@@ -247,6 +247,41 @@ def pull_multi(srcs, dsts, ns, versions, want_version: int, want_ptr=None) -> No
     _count()
 
 
+def adam_serve(w, m, v, shadow, slots, num_slots: int, n: int, pieces, lr: float, t_counter, queue, qlen: int,
+               shutdown, version_flag, global_step, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8) -> None:
+    arr = (Piece * max(1, len(pieces)))(*pieces)
+    sl = (c_void_p * num_slots)(*[c_void_p(int(x)) for x in slots[:num_slots]])
+    _check(lib().tfd_adam_serve(_p(w), _p(m), _p(v), _p(shadow), sl, c_int(num_slots), c_longlong(n), arr,
+                                c_int(len(pieces)), c_float(lr), c_float(beta1), c_float(beta2), c_float(eps),
+                                _p(t_counter), _p(queue), c_int(qlen), _p(shutdown), _p(version_flag), _p(global_step),
+                                _stream()), "tfd_adam_serve")
+    _count()
+
+
+def push_multi_async(srcs, dsts, ns, tickets, queues, qlen: int, worker: int, my_ticket, block_counter,
+                     local_step=None) -> None:
+    n, k = len(srcs), len(tickets)
+    S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
+    D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
+    NS = (c_longlong * n)(*[int(x) for x in ns])
+    T = (c_void_p * k)(*[c_void_p(int(x)) for x in tickets])
+    Q = (c_void_p * k)(*[c_void_p(int(x)) for x in queues])
+    _check(lib().tfd_push_multi_async(S, D, NS, c_int(n), T, Q, c_int(k), c_int(qlen), c_uint(worker), _p(my_ticket),
+                                      _p(block_counter), _p(local_step), _stream()), "tfd_push_multi_async")
+    _count()
+
+
+def pull_multi_async(srcs, dsts, ns, versions, want_segs) -> None:
+    n = len(srcs)
+    S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
+    D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
+    NS = (c_longlong * n)(*[int(x) for x in ns])
+    V = (c_void_p * n)(*[c_void_p(int(x)) for x in versions])
+    W = (c_void_p * n)(*[c_void_p(int(x)) for x in want_segs])
+    _check(lib().tfd_pull_multi_async(S, D, NS, V, W, c_int(n), _stream()), "tfd_pull_multi_async")
+    _count()
+
+
 # ---- symmetric heap ----
 def ipc_alloc(nbytes: int):
     ptr = c_void_p()

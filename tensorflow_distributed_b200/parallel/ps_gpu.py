@@ -34,6 +34,10 @@ from ..ops import native as nat
 from .placement import Placement
 
 WCTRL_STEP, WCTRL_PUSHBLK = 8, 9   # worker-local control words (inside the rank's own ctrl block)
+CTRL_TICKET, CTRL_SHUTDOWN = 6, 7  # async: ticket dispenser / release word of a shard
+CTRL_RING, RING_LEN = 16, 32       # async: arrival ring (worker id + 1 per served-in-order ticket)
+CTRL_DONE = 56                     # async: shard 0 holds one 'worker finished' word per worker (56..63)
+WCTRL_MYTICKET = 48                # async: worker-local, one word per shard: version that serves my last push
 DIRECT_THRESHOLD = 1 << 18         # tensors at least this big are consumed in place over NVLink, never mirrored
 
 
@@ -111,7 +115,15 @@ class GpuClusterEngine(NativeEngine):
     name = "native-sm100a-ps"
 
     def __init__(self, spec: ModelSpec, topo: Topology, rank: int, device, learning_rate: float = 0.01,
-                 seed: int = 0, init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False):
+                 seed: int = 0, init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False,
+                 async_mode: bool = False):
+        if async_mode and topo.layout != "dedicated":
+            # A colocated rank runs its worker kernels and its shard's apply in ONE in-order stream.  With
+            # apply-on-arrival a worker blocked on "my ticket has been served" would sit in front of the very apply
+            # kernel another rank is waiting for (A waits on B's shard, B on A's): only ps-only GPUs can serve
+            # tickets unconditionally -- which is also the reference's topology (separate ps processes).
+            raise ValueError("async replicas need dedicated ps GPUs (layout='dedicated')")
+        self.async_mode = async_mode
         if not dist.is_initialized():
             raise RuntimeError("GpuClusterEngine needs torch.distributed (bootstrap only) to be initialised")
         nat.lib()
@@ -193,16 +205,16 @@ class GpuClusterEngine(NativeEngine):
             self.mirror_w[v.name] = torch.zeros(rows, cols, dtype=torch.float32, device=dev)
             self.local_g[v.name] = torch.zeros(rows, cols, dtype=torch.float32, device=dev)
             ver = self._ctrl_ptr(p.shard, CTRL_VERSION)
-            pull.append((self._w_ptr(p.shard, p.offset), self.mirror_w[v.name].data_ptr(), p.numel, ver))
+            pull.append((self._w_ptr(p.shard, p.offset), self.mirror_w[v.name].data_ptr(), p.numel, ver, p.shard))
             push.append((self.local_g[v.name].data_ptr(), self._slot_ptr(p.shard, p.offset), p.numel))
             seen_shards.add(p.shard)
             if needs_shadow(self.spec, v.name):
                 ld = _pad8(cols)
                 self.mirror_s[v.name] = torch.zeros(rows, ld, dtype=torch.bfloat16, device=dev)
-                pull.append((self._shadow_ptr(p.shard, v.name), self.mirror_s[v.name].data_ptr(), rows * ld // 2, ver))
+                pull.append((self._shadow_ptr(p.shard, v.name), self.mirror_s[v.name].data_ptr(), rows * ld // 2, ver, p.shard))
         for s in range(self.topo.num_shards):  # wait for EVERY shard's version (its slots are then free again)
             if s not in seen_shards:
-                pull.append((self._w_ptr(s, 0), self.ctrl.data_ptr() + 4 * 32, 0, self._ctrl_ptr(s, CTRL_VERSION)))
+                pull.append((self._w_ptr(s, 0), self.ctrl.data_ptr() + 4 * 60, 0, self._ctrl_ptr(s, CTRL_VERSION), s))
         self._pull, self._push = pull, push
         self._arrive = [self._ctrl_ptr(s, CTRL_ARRIVE) for s in range(self.topo.num_shards)]
         # per direct variable: shard pieces in row order
@@ -213,7 +225,7 @@ class GpuClusterEngine(NativeEngine):
                 "rows": [q.row_start for q in pcs] + [pcs[-1].row_end], "cols": pcs[0].cols, "ld": _pad8(pcs[0].cols),
                 "shadow": [self._shadow_ptr(q.shard, name) for q in pcs],
                 "slot": [self._slot_ptr(q.shard, q.offset) for q in pcs],
-                "ver": [self._ctrl_ptr(q.shard, CTRL_VERSION) for q in pcs]}
+                "ver": None if self.async_mode else [self._ctrl_ptr(q.shard, CTRL_VERSION) for q in pcs]}
 
     # ---- parameter / gradient views used by the kernel sequences -----------------------------
     def P(self, name: str) -> torch.Tensor:
@@ -263,12 +275,23 @@ class GpuClusterEngine(NativeEngine):
         """Pull (X1): small tensors are copied once the owning shard's version has caught up with this
         worker's step counter; the same kernel thereby waits for every shard (slots are free to overwrite)."""
         p = self._pull
+        if self.async_mode:  # wait (per shard) until my previous gradient has been applied: read-your-writes
+            nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
+                                 [self.ctrl.data_ptr() + 4 * (WCTRL_MYTICKET + s[4]) for s in p])
+            return
         nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
                        want_ptr=self.step_ptr())
 
     def _post_backward(self, ws) -> None:
         """Push (X2): small gradients into this worker's slots, then arrive += 1 on every shard."""
         p = self._push
+        if self.async_mode:
+            S = self.topo.num_shards
+            nat.push_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p],
+                                 [self._ctrl_ptr(s, CTRL_TICKET) for s in range(S)],
+                                 [self._ctrl_ptr(s, CTRL_RING) for s in range(S)], RING_LEN, self.my_worker,
+                                 self.ctrl[WCTRL_MYTICKET:], self.ctrl[WCTRL_PUSHBLK:], local_step=self.ctrl[WCTRL_STEP:])
+            return
         nat.push_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], self._arrive, 1.0,
                        self.ctrl[WCTRL_PUSHBLK:], local_step=self.ctrl[WCTRL_STEP:])
 
@@ -277,6 +300,11 @@ class GpuClusterEngine(NativeEngine):
         if not self.is_ps:
             return
         s = self.shard
+        if self.async_mode:  # one arriving gradient, in ticket order, scale 1 (apply-on-arrival)
+            nat.adam_serve(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, s.n, s.pieces, self.lr,
+                           s.ctrl[CTRL_T:], s.ctrl[CTRL_RING:], RING_LEN, s.ctrl[CTRL_SHUTDOWN:], s.ctrl[CTRL_VERSION:],
+                           s.ctrl[CTRL_GSTEP:])
+            return
         nat.adam_apply(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, 1.0 / self.num_workers, s.n,
                        s.pieces, self.lr, s.ctrl[CTRL_T:], s.ctrl[CTRL_ARRIVE:], s.ctrl[CTRL_VERSION:],
                        s.ctrl[CTRL_GSTEP:])
@@ -285,7 +313,8 @@ class GpuClusterEngine(NativeEngine):
         if self.is_worker:
             return super()._sequence(ws, mode, keep_prob, mask_out)
         if mode == "train":  # dedicated ps: nothing but the apply, like the reference's passive ps (m:160-161)
-            self._apply()
+            for _ in range(self.num_workers if self.async_mode else 1):  # async: one serve per worker push
+                self._apply()
 
     # ---- public API ------------------------------------------------------------------------
     def workspace(self, B: int) -> Workspace:
@@ -304,7 +333,7 @@ class GpuClusterEngine(NativeEngine):
         return int(t.item())
 
     def describe(self) -> str:
-        return self.topo.describe() + " sync"
+        return self.topo.describe() + (" async" if self.async_mode else " sync")
 
     def _read_arena(self, which: str) -> Dict[str, torch.Tensor]:
         """Gather a full name->tensor dict by reading every shard's arena through the peer mapping."""
@@ -369,4 +398,154 @@ class GpuClusterEngine(NativeEngine):
     @classmethod
     def from_bench_args(cls, spec, a, rank: int, world: int, device) -> "GpuClusterEngine":
         topo = Topology.make(world, a.layout, a.ps)
-        return cls(spec, topo, rank, device, learning_rate=0.01, seed=0, init_stddev=a.init_stddev)
+        return cls(spec, topo, rank, device, learning_rate=0.01, seed=0, init_stddev=a.init_stddev,
+                   async_mode=getattr(a, "async_mode", False))
+
+    # ---- restore / release helpers used by the cluster program -------------------------------
+    def set_adam_state(self, sd: dict) -> None:
+        if self.is_ps:
+            s = self.shard
+            for v in self.spec.variables:
+                p = s.piece_of(v.name)
+                if p is not None:
+                    for arena, key in ((s.m, "m"), (s.v, "v")):
+                        full = sd[key][v.name].to(torch.float32).reshape(-1, p.cols)
+                        s.view(arena, v.name).copy_(full[p.row_start:p.row_end].to(self.device))
+            s.ctrl[CTRL_T] = int(sd["t"])
+            s.ctrl[CTRL_VERSION] = 0
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+
+    def set_global_step(self, step: int) -> None:
+        if self.is_ps:
+            self.shard.ctrl[CTRL_GSTEP] = int(step)
+        torch.cuda.synchronize(self.device)
+
+    def request_shutdown(self) -> None:
+        """Release ps GPUs that are waiting for a ticket (async): the clean replacement for killing the ps process."""
+        for s in range(self.topo.num_shards):
+            nat.tensor_from_ptr(self._ctrl_ptr(s, CTRL_SHUTDOWN), 1, torch.int32, self.device).fill_(1)
+        torch.cuda.synchronize(self.device)
+
+    def mark_done(self) -> None:
+        """Async: tell the chief this worker will push no more gradients (its own word in shard 0's ctrl block)."""
+        nat.tensor_from_ptr(self._ctrl_ptr(0, CTRL_DONE + self.my_worker), 1, torch.int32, self.device).fill_(1)
+        torch.cuda.synchronize(self.device)
+
+    def all_workers_done(self) -> bool:
+        t = nat.tensor_from_ptr(self._ctrl_ptr(0, CTRL_DONE), self.num_workers, torch.int32, self.device)
+        return bool(int(t.sum().item()) == self.num_workers)
+
+    def shutdown_requested(self) -> bool:
+        return bool(self.is_ps and int(self.shard.ctrl[CTRL_SHUTDOWN].item()) != 0)
+
+
+def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
+    """The cluster program (mnist_python_{m,w1,w2}.py) when ps_hosts / worker_hosts name GPUs of one box
+    (``gpu:<ordinal>``): one OS process per task, ps tasks on their own GPUs (``/root/reference/mnist_python_m.py:
+    145-320``).  ps and worker tasks must name different GPUs here: two processes cannot share one GPU while their
+    kernels wait on each other; the colocated layout exists through the one-process-per-GPU launcher (bench.py)."""
+    import time
+
+    from .. import cluster as cl
+    from ..models.spec import make_spec
+    from ..supervisor import Supervisor
+    from .. import checkpoint
+
+    addr = cluster.task_address(flags.job_name, flags.task_index)
+    gpus = [cluster.task_address(j, i).gpu_ordinal for j in ("ps", "worker") for i in range(cluster.num_tasks(j))]
+    if len(set(gpus)) != len(gpus):
+        raise ValueError("gpu cluster: every ps and worker task needs its own GPU (got %s)" % gpus)
+    device = torch.device("cuda:%d" % addr.gpu_ordinal)
+    torch.cuda.set_device(device)
+    rank, world = cluster.rank_of(flags.job_name, flags.task_index), cluster.world_size
+    host, port = cluster.master_endpoint()
+    import datetime
+    dist.init_process_group("nccl", init_method="tcp://%s:%d" % (host, port), rank=rank, world_size=world,
+                            device_id=device, timeout=datetime.timedelta(seconds=flags.step_timeout_secs))
+    topo = Topology(world, list(range(cluster.num_ps)), list(range(cluster.num_ps, world)), "dedicated")
+    spec = make_spec(flags.model, flags.hidden_units, flags.mlp_layers)
+    R = cl.effective_replicas_to_aggregate(flags, cluster.num_workers)
+    if flags.sync_replicas and R != cluster.num_workers:
+        log("note: the GPU path aggregates all %d workers per step (replicas_to_aggregate=%d is honoured on the "
+            "CPU/gloo path only)" % (cluster.num_workers, R))
+    is_worker = flags.job_name == "worker"
+    is_chief = is_worker and cl.is_chief(flags)
+    if is_worker:
+        log("Worker %d: %s" % (flags.task_index, "Initializing session..." if is_chief
+                               else "Waiting for session to be initialized..."))
+    eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
+                           init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas)
+    if flags.log_device_placement and (is_chief or flags.job_name == "ps"):
+        log(eng.placement.table())
+    sv = Supervisor(is_chief, spec, flags.train_dir, recovery_wait_secs=1.0, log=log)
+    start_step = 0
+    path = checkpoint.latest_checkpoint(flags.train_dir) if flags.train_dir else None
+    if path is not None:  # every task reads the same file; each ps restores the rows it owns
+        blob = checkpoint.load(path, spec)
+        eng.set_params(blob["variables"])
+        if "adam" in blob:
+            eng.set_adam_state(blob["adam"])
+        eng.set_global_step(blob["global_step"])
+        start_step = blob["global_step"]
+        dist.barrier()
+    if is_worker:
+        log("Worker %d: Session initialization complete." % flags.task_index)
+    steps_left = max(0, flags.train_steps - start_step)
+    B = flags.batch_size
+    if flags.job_name == "ps":
+        # server.join() (m:160-161): the ps only ever runs its shard's apply kernel until it is released
+        if flags.sync_replicas:
+            ws = eng.workspace(B)
+            for _ in range(steps_left):
+                eng.train_step_resident(ws, flags.keep_prob)
+            eng.synchronize()
+        else:
+            ws = eng.workspace(B)
+            while not eng.shutdown_requested():
+                eng._apply()
+                eng.synchronize()
+        dist.barrier()
+        out = {"role": "ps", "global_step": eng.global_step}
+        eng.shutdown()
+        return out
+    time_begin = time.time()
+    log("Training begins @ %f" % time_begin)
+    local_step, step = 0, start_step
+    while step < flags.train_steps:
+        batch_xs, batch_ys = mnist.train.next_batch(B)
+        eng.train_step(batch_xs, batch_ys, flags.keep_prob)
+        local_step += 1
+        step = (start_step + local_step) if flags.sync_replicas else eng.global_step  # X5
+        log("%f: Worker %d: training step %d done (global step: %d)" % (time.time(), flags.task_index, local_step, step))
+    eng.synchronize()
+    time_end = time.time()
+    log("Training ends @ %f" % time_end)
+    log("Training elapsed time: %f s" % (time_end - time_begin))
+    accuracy_arr = []
+    for _ in range(flags.validation_batches):
+        val_x, val_y = mnist.validation.next_batch(flags.validation_batch_size)
+        acc = eng.eval_accuracy(val_x, val_y)
+        log("After %d training step(s)" % flags.train_steps)
+        log("Accuracy : %f" % acc)
+        accuracy_arr.append(acc)
+    mean_accuracy = sum(accuracy_arr) / len(accuracy_arr)
+    log("Mean Accuracy : %f" % mean_accuracy)
+    saved = None
+    if is_chief and flags.train_dir:
+        saved = sv.save(eng.global_step, eng.get_params(), eng.get_adam_state())
+    if not flags.sync_replicas:
+        # no NCCL while ps GPUs may still be spinning in a serve kernel: finish through peer-memory words
+        eng.mark_done()
+        if is_chief:
+            t0 = time.time()
+            while not eng.all_workers_done():
+                if time.time() - t0 > flags.step_timeout_secs:
+                    raise TimeoutError("chief: workers did not finish within %.0f s" % flags.step_timeout_secs)
+                time.sleep(0.01)
+            eng.request_shutdown()
+    dist.barrier()
+    out = {"role": "worker", "task_index": flags.task_index, "local_steps": local_step, "global_step": eng.global_step,
+           "mean_accuracy": mean_accuracy, "checkpoint": saved}
+    eng.shutdown()
+    return out

@@ -26,3 +26,9 @@ needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_c
 def test_two_gpu_sync_ps(layout, model):
     out = _torchrun(2, ["--layout", layout, "--model", model], 29611)
     assert "OK" in out and "FAIL" not in out
+
+
+@needs2
+def test_two_gpu_async_apply_on_arrival_counts_every_update():
+    out = _torchrun(2, ["--layout", "dedicated", "--async_mode"], 29613)
+    assert "OK" in out and "FAIL" not in out and "async" in out
