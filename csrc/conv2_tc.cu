@@ -2,11 +2,10 @@
 // implicit GEMMs.  Replaces tf.nn.conv2d + bias_add + relu + max_pool of /root/reference/mnist_python_m.py:
 // 93-101,114-116 and the conv gradients TF's autodiff generates at m:222.
 //
-// im2col never touches memory: for filter tap (kh,kw) the A tile of 128 output pixels is ONE 4-D TMA box
-// {C, 16 w, 2 h, 4 n} of the NHWC activation, shifted by (kh-2, kw-2); TMA zero-fills everything outside the
-// image, which is exactly SAME padding.  The box is 16 wide on a 14-wide map, so 2 of 16 accumulator rows per
-// image row are padding (never stored); in exchange a 2x2 pooling window lives inside one warp's 32 TMEM lanes
-// (lane = hh*16 + ww) and the pool is two shuffles.  The whole bf16 filter (100 KB) stays resident in shared
+// im2col never touches memory: the A tiles are 4-D TMA boxes of the NHWC activation shifted by the filter tap;
+// TMA zero-fills everything outside the image, which is exactly SAME padding.  Boxes are 16 wide on a 14-wide
+// map, so 2 of 16 accumulator rows per image row are padding (never stored); in exchange a 2x2 pooling window
+// lives inside one warp's 32 TMEM lanes (lane = hh*16 + ww) and the pool is two shuffles.  The whole bf16 filter (100 KB) stays resident in shared
 // memory; CTAs are persistent over pixel tiles with double-buffered TMEM accumulators.
 #include "../include/tfd_b200.h"
 #include "tfd_common.cuh"
@@ -28,14 +27,21 @@ __device__ __forceinline__ void load_filter(uint8_t* filt, const CUtensorMap* tm
 // ------------------------------------------------------------------------------------------------
 // forward / dgrad share one kernel shape.  kFwd: A = in [B,14,14,32] (64 B rows, SW64), N = 64, fused
 // bias+ReLU+pool epilogue.  !kFwd: A = dy [B,14,14,64] (128 B rows, SW128), N = 32, fp32 store epilogue.
+//
+// Tile = 8 rows x 16 columns of ONE image (two tiles per image; rows >= 14 and columns >= 14 are padding).
+// Per tile only FIVE TMA boxes are loaded, one per filter column kw: {C, 16 w, 12 h, 1 n} starting at
+// (w = kw-2, h = 8*tile-2) -- 8 output rows plus the 4-row halo.  The A operand of tap (kh,kw) is then just a
+// descriptor into that box at row offset kh*16 (a multiple of the swizzle atom), so the five row taps of a
+// column reuse one box: 5x less L2->SM traffic than one box per tap, which is what bounded this kernel.
 // ------------------------------------------------------------------------------------------------
 template <bool kFwd>
 struct ConvCfg {
-  static constexpr int kABytes = kFwd ? 8192 : 16384;
-  static constexpr int kStages = kFwd ? 8 : 6;
+  static constexpr int kRowBytes = kFwd ? 64 : 128;
+  static constexpr int kBoxBytes = 12 * 16 * kRowBytes;  // 12 KB / 24 KB
+  static constexpr int kStages = kFwd ? 8 : 5;           // ring of kw boxes
   static constexpr int kN = kFwd ? 64 : 32;
-  static constexpr int kKSteps = kFwd ? 2 : 4;  // UMMA K=16 steps per tap
-  static constexpr int kSmem = kFilterBytes + kStages * kABytes + 1024 + 512;
+  static constexpr int kKSteps = kFwd ? 2 : 4;           // UMMA K=16 steps per tap
+  static constexpr int kSmem = kFilterBytes + kStages * kBoxBytes + 1024 + 512;
 };
 
 template <bool kFwd>
@@ -48,7 +54,7 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* filt = smem;
   uint8_t* abuf = smem + kFilterBytes;
-  uint64_t* a_full = reinterpret_cast<uint64_t*>(abuf + C::kStages * C::kABytes);
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(abuf + C::kStages * C::kBoxBytes);
   uint64_t* a_empty = a_full + C::kStages;
   uint64_t* filt_full = a_empty + C::kStages;
   uint64_t* acc_full = filt_full + 1;   // [2]
@@ -73,19 +79,18 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
   if (warp == 0) {
     if (lane == 0) {
-      load_filter(filt, &tmW, filt_full);
+      // the first input boxes go out before the 100 KB filter so the first MMAs are not queued behind it
       int stage = 0;
       uint32_t phase = 0;
+      bool filter_sent = false;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int nb = tile / 7, hp = tile % 7;
-        for (int tap = 0; tap < 25; ++tap) {
-          const int kh = tap / 5, kw = tap % 5;
+        const int n = tile >> 1, ht = tile & 1;
+        for (int kw = 0; kw < 5; ++kw) {
           mbar_wait(&a_empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&a_full[stage], C::kABytes);
-          const int w0 = kFwd ? kw - 2 : 2 - kw;
-          const int h0 = kFwd ? 2 * hp + kh - 2 : 2 * hp + 2 - kh;
-          tma_load_4d(abuf + stage * C::kABytes, &tmA, &a_full[stage], 0, w0, h0, nb * 4);
+          mbar_arrive_expect_tx(&a_full[stage], C::kBoxBytes);
+          tma_load_4d(abuf + stage * C::kBoxBytes, &tmA, &a_full[stage], 0, kFwd ? kw - 2 : 2 - kw, 8 * ht - 2, n);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          if (!filter_sent) { load_filter(filt, &tmW, filt_full); filter_sent = true; }
         }
       }
     }
@@ -101,22 +106,27 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tacc = tmem_base + buf * C::kN;
-        for (int tap = 0; tap < 25; ++tap) {
+        for (int kw = 0; kw < 5; ++kw) {
           mbar_wait(&a_full[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(abuf + stage * C::kABytes);
-          const uint32_t sw = smem_u32(filt + tap * 4096);
+          const uint32_t sbox = smem_u32(abuf + stage * C::kBoxBytes);
 #pragma unroll
-          for (int ks = 0; ks < C::kKSteps; ++ks) {
-            uint64_t da, db;
-            if (kFwd) {
-              da = make_smem_desc(sa + ks * 32, 16, 512, kSwz64);         // [128 px][32 ci]  K-major, 64 B rows
-              db = make_smem_desc(sw + ks * 2048, 4096, 1024, kSwz128);   // [32 ci][64 co]   MN-major (co contiguous)
-            } else {
-              da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);       // [128 px][64 co]  K-major, 128 B rows
-              db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);       // [32 ci][64 co]   K-major  (co = K)
+          for (int kh = 0; kh < 5; ++kh) {
+            // forward: output row hh reads box row hh+kh.  dgrad: dy row hh+2-kh -> box row hh+4-kh.
+            const uint32_t sa = sbox + (kFwd ? kh : 4 - kh) * 16 * C::kRowBytes;
+            const uint32_t sw = smem_u32(filt + (kh * 5 + kw) * 4096);
+#pragma unroll
+            for (int ks = 0; ks < C::kKSteps; ++ks) {
+              uint64_t da, db;
+              if (kFwd) {
+                da = make_smem_desc(sa + ks * 32, 16, 512, kSwz64);         // [128 px][32 ci]  K-major, 64 B rows
+                db = make_smem_desc(sw + ks * 2048, 4096, 1024, kSwz128);   // [32 ci][64 co]   MN-major (co contiguous)
+              } else {
+                da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);       // [128 px][64 co]  K-major, 128 B rows
+                db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);       // [32 ci][64 co]   K-major  (co = K)
+              }
+              umma_bf16(tacc, da, db, idesc, (kw > 0 || kh > 0 || ks > 0) ? 1u : 0u);
             }
-            umma_bf16(tacc, da, db, idesc, (tap > 0 || ks > 0) ? 1u : 0u);
           }
           umma_commit(&a_empty[stage]);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -125,18 +135,19 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else {
-    const int q = warp & 3;  // image inside the tile; also the TMEM lane quadrant
+    const int q = warp & 3;  // TMEM lane quadrant = two image rows of the tile
     const int hh = lane >> 4, ww = lane & 15;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int buf = it & 1;
-      const int nb = tile / 7, hp = tile % 7;
-      const int n = nb * 4 + q;
+      const int n = tile >> 1, ht = tile & 1;
+      const int h = 8 * ht + 2 * q + hh;  // conv output row of this lane
       mbar_wait(&acc_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t tacc = tmem_base + buf * C::kN + ((uint32_t)(q * 32) << 16);
       if (kFwd) {
         const int self = hh * 2 + (ww & 1);
+        const int ph = 4 * ht + q;  // pooled row
 #pragma unroll 1
         for (int j = 0; j < 4; ++j) {
           float v[16];
@@ -158,16 +169,16 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           }
 #pragma unroll
           for (int i = 0; i < 8; ++i) packed[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
-          if (j == self && ww < 14 && n < B) {
-            const long long o = ((((long long)n * 7 + hp) * 7) + (ww >> 1)) * 64 + j * 16;
+          if (j == self && ww < 14 && ph < 7 && n < B) {
+            const long long o = ((((long long)n * 7 + ph) * 7) + (ww >> 1)) * 64 + j * 16;
             *reinterpret_cast<uint4*>(pool_out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
             *reinterpret_cast<uint4*>(pool_out + o + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
             *reinterpret_cast<uint4*>(amax + o) = make_uint4(am[0], am[1], am[2], am[3]);
           }
         }
       } else {
-        const bool ok = (ww < 14) && (n < B);
-        float* o = dx + ((((long long)n * 14 + 2 * hp + hh) * 14) + ww) * 32;
+        const bool ok = (ww < 14) && (h < 14) && (n < B);
+        float* o = dx + ((((long long)n * 14 + h) * 14) + ww) * 32;
 #pragma unroll 1
         for (int j = 0; j < 2; ++j) {
           float v[16];
@@ -309,7 +320,7 @@ int num_sms() {
 extern "C" int tfd_conv2_fwd(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
                              void* stream) {
   CUtensorMap tmA, tmW;
-  int rc = tfd_make_tmap_nhwc_bf16(&tmA, in, B, 14, 14, 32, 4, 2, 16, 64);
+  int rc = tfd_make_tmap_nhwc_bf16(&tmA, in, B, 14, 14, 32, 1, 12, 16, 64);
   if (rc) return rc;
   rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
   if (rc) return rc;
@@ -319,7 +330,7 @@ extern "C" int tfd_conv2_fwd(const void* in, const void* w, const float* b, void
     TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
     attr = true;
   }
-  const int tiles = ((B + 3) / 4) * 7;
+  const int tiles = B * 2;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   conv2_tc_kernel<true><<<grid, kThreads, C::kSmem, static_cast<cudaStream_t>(stream)>>>(
       tmA, tmW, b, static_cast<bf16*>(pool_out), argmax, nullptr, B, tiles);
@@ -329,7 +340,7 @@ extern "C" int tfd_conv2_fwd(const void* in, const void* w, const float* b, void
 
 extern "C" int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, void* stream) {
   CUtensorMap tmA, tmW;
-  int rc = tfd_make_tmap_nhwc_bf16(&tmA, dy, B, 14, 14, 64, 4, 2, 16, 128);
+  int rc = tfd_make_tmap_nhwc_bf16(&tmA, dy, B, 14, 14, 64, 1, 12, 16, 128);
   if (rc) return rc;
   rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
   if (rc) return rc;
@@ -339,7 +350,7 @@ extern "C" int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, 
     TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
     attr = true;
   }
-  const int tiles = ((B + 3) / 4) * 7;
+  const int tiles = B * 2;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   conv2_tc_kernel<false><<<grid, kThreads, C::kSmem, static_cast<cudaStream_t>(stream)>>>(
       tmA, tmW, nullptr, nullptr, nullptr, dx, B, tiles);
