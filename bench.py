@@ -80,6 +80,8 @@ def parse():
     ap.add_argument("--layout", default="colocated", choices=["colocated", "dedicated"])
     ap.add_argument("--ps", type=int, default=0, help="ps shards (0: one per GPU when colocated, 1 when dedicated)")
     ap.add_argument("--async", dest="async_mode", action="store_true")
+    ap.add_argument("--pull", default="auto", choices=["auto", "fused", "prefetch"],
+                    help="big-matrix pull: fused into the GEMMs (TMA from the ps GPU) or prefetched under the conv layers")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--init-stddev", type=float, default=1.0)
     return ap.parse_args()

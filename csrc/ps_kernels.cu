@@ -183,24 +183,31 @@ __global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushT
     s.dst[i] = s.src[i] * scale;
   __threadfence_system();
   __syncthreads();
+  // The last block to finish signals every shard.  One thread per shard, so the NVLink round trips of the
+  // release operations overlap instead of queueing behind each other (8 shards: ~2 us instead of ~20 us).
+  __shared__ unsigned s_last;
   if (threadIdx.x == 0) {
     const unsigned total = gridDim.x * gridDim.y;
-    if (atomicAdd(block_counter, 1u) == total - 1) {
+    s_last = (atomicAdd(block_counter, 1u) == total - 1) ? 1u : 0u;
+    if (s_last) {
       *block_counter = 0;
       __threadfence_system();
-      if (t.qlen > 0) {
-        // apply-on-arrival: take a ticket on every shard, then publish "worker w's slot is ready" in that ring cell
-        for (int k = 0; k < t.narrive; ++k) {
-          const unsigned tk = atom_add_release_sys_u32(t.arrive[k], 1u);
-          st_release_sys_u32(t.queue[k] + (tk % (unsigned)t.qlen), t.worker + 1u);
-          t.my_ticket[k] = tk + 1u;
-        }
-      } else {
-        for (int k = 0; k < t.narrive; ++k) atom_add_release_sys_u32(t.arrive[k], 1u);
-      }
-      if (local_step) *local_step = *local_step + 1;
     }
   }
+  __syncthreads();
+  if (!s_last) return;
+  const int k = threadIdx.x;
+  if (k < t.narrive) {
+    if (t.qlen > 0) {
+      // apply-on-arrival: take a ticket on the shard, then publish "worker w's slot is ready" in that ring cell
+      const unsigned tk = atom_add_release_sys_u32(t.arrive[k], 1u);
+      st_release_sys_u32(t.queue[k] + (tk % (unsigned)t.qlen), t.worker + 1u);
+      t.my_ticket[k] = tk + 1u;
+    } else {
+      red_add_release_sys_u32(t.arrive[k], 1u);
+    }
+  }
+  if (k == 0 && local_step) *local_step = *local_step + 1;
 }
 
 struct PullSeg {

@@ -225,6 +225,9 @@ __device__ __forceinline__ uint32_t atom_add_release_sys_u32(uint32_t* p, uint32
   asm volatile("atom.add.release.sys.global.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
   return old;
 }
+__device__ __forceinline__ void red_add_release_sys_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 // bounded wait until *p >= target (flags are monotonic counters)
 __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t target, const char* what) {
   if (ld_acquire_sys_u32(p) >= target) return;

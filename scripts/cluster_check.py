@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--steps", type=int, default=12)
     ap.add_argument("--async_mode", action="store_true")
+    ap.add_argument("--pull", default="auto")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -42,7 +43,7 @@ def main():
     spec = make_spec(a.model, a.hidden, a.layers)
     topo = Topology.make(world, a.layout, a.ps)
     eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05,
-                           async_mode=a.async_mode)
+                           async_mode=a.async_mode, pull_mode=a.pull)
     B = 128
     keep = 1.0
     w = topo.worker_of(rank)

@@ -223,7 +223,7 @@ class NativeEngine:
                  bias=None, ld_out: Optional[int] = None) -> None:
         """out[M,N] = A[M,K] W[K,N]  (A K-major, W MN-major as stored)."""
         W = self.S(wname)
-        K, N = W.shape[0], self.P(wname).shape[1]
+        K, N = W.shape[0], self.spec.by_name()[wname].cols
         nat.gemm_bf16(A, 0, W, 1, M, N, K, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride, bias=bias,
                       ld_out=ld_out)
 
@@ -231,7 +231,7 @@ class NativeEngine:
                    relu_mask=None, ld_out: Optional[int] = None) -> None:
         """out[M,K] = dY[M,N] W^T  (W [K,N] read in place as the K-major B operand [N'=K, K'=N])."""
         W = self.S(wname)
-        K, N = W.shape[0], self.P(wname).shape[1]
+        K, N = W.shape[0], self.spec.by_name()[wname].cols
         nat.gemm_bf16(dY, 0, W, 0, M, K, N, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride,
                       relu_mask=relu_mask, ld_out=ld_out)
 

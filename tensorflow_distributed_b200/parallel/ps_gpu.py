@@ -116,7 +116,8 @@ class GpuClusterEngine(NativeEngine):
 
     def __init__(self, spec: ModelSpec, topo: Topology, rank: int, device, learning_rate: float = 0.01,
                  seed: int = 0, init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False,
-                 async_mode: bool = False):
+                 async_mode: bool = False, pull_mode: str = "auto", prefetch_max_numel: int = 8 << 20):
+        self.pull_mode, self.prefetch_max_numel = pull_mode, prefetch_max_numel
         if async_mode and topo.layout != "dedicated":
             # A colocated rank runs its worker kernels and its shard's apply in ONE in-order stream.  With
             # apply-on-arrival a worker blocked on "my ticket has been served" would sit in front of the very apply
@@ -164,7 +165,15 @@ class GpuClusterEngine(NativeEngine):
             self.slot_ptrs = [self.heap_ptr + L.slot(w) for w in range(topo.num_workers)]
             self.shard.init_variables(seed, init_stddev)
         # ---- worker role ----
+        # Big tensor-core operands are never pushed through a local gradient copy (push-fused wgrad).  For the pull
+        # there are two strategies: "fused" -- forward and dgrad GEMMs TMA-load B from the owner GPUs (bandwidth-bound
+        # layers: 97% of the NVLink roofline on 8192x8192); "prefetch" -- a few-MB matrix such as the CNN's wd1 is
+        # copied once per step on a side stream *under* the conv layers and both GEMMs read the local copy, which
+        # takes two latency-bound NVLink reads off the critical path.  Measured on 2 GPUs the fused
+        # pull is the faster one even for wd1 (156 vs 166 us/step), so "auto" = fused; "prefetch" stays selectable.
         self.direct = {v.name for v in spec.variables if needs_shadow(spec, v.name) and v.numel >= DIRECT_THRESHOLD}
+        self.prefetched = {n for n in self.direct
+                           if pull_mode == "prefetch" and spec.by_name()[n].numel <= prefetch_max_numel}
         if self.is_worker:
             self._build_worker_tables()
         torch.cuda.synchronize(self.device)
@@ -219,8 +228,17 @@ class GpuClusterEngine(NativeEngine):
         self._arrive = [self._ctrl_ptr(s, CTRL_ARRIVE) for s in range(self.topo.num_shards)]
         # per direct variable: shard pieces in row order
         self._direct_info = {}
+        self._prefetch = []
         for name in self.direct:
             pcs = sorted(self.placement.pieces[name], key=lambda q: q.row_start)
+            if name in self.prefetched:
+                ld = _pad8(pcs[0].cols)
+                self.mirror_s[name] = torch.zeros(pcs[-1].row_end, ld, dtype=torch.bfloat16, device=dev)
+                for q in pcs:
+                    self._prefetch.append((self._shadow_ptr(q.shard, name),
+                                           self.mirror_s[name].data_ptr() + 2 * q.row_start * ld,
+                                           (q.row_end - q.row_start) * ld // 2, self._ctrl_ptr(q.shard, CTRL_VERSION),
+                                           q.shard))
             self._direct_info[name] = {
                 "rows": [q.row_start for q in pcs] + [pcs[-1].row_end], "cols": pcs[0].cols, "ld": _pad8(pcs[0].cols),
                 "shadow": [self._shadow_ptr(q.shard, name) for q in pcs],
@@ -241,7 +259,9 @@ class GpuClusterEngine(NativeEngine):
         return self.ctrl[WCTRL_STEP:]
 
     def gemm_fwd(self, wname, A, M, out, *, mode, bn, splits=1, split_stride=0, bias=None, ld_out=None):
-        if wname not in self.direct:
+        if wname in self.prefetched:
+            self._join_prefetch()
+        if wname not in self.direct or wname in self.prefetched:
             return super().gemm_fwd(wname, A, M, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride,
                                     bias=bias, ld_out=ld_out)
         d = self._direct_info[wname]
@@ -251,7 +271,9 @@ class GpuClusterEngine(NativeEngine):
                           splits=splits, split_stride=split_stride, bias=bias)
 
     def gemm_dgrad(self, wname, dY, M, out, *, mode, bn, splits=1, split_stride=0, relu_mask=None, ld_out=None):
-        if wname not in self.direct:
+        if wname in self.prefetched:
+            self._join_prefetch()
+        if wname not in self.direct or wname in self.prefetched:
             return super().gemm_dgrad(wname, dY, M, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride,
                                       relu_mask=relu_mask, ld_out=ld_out)
         d = self._direct_info[wname]
@@ -274,6 +296,8 @@ class GpuClusterEngine(NativeEngine):
     def _pre_step(self, ws, training: bool) -> None:
         """Pull (X1): small tensors are copied once the owning shard's version has caught up with this
         worker's step counter; the same kernel thereby waits for every shard (slots are free to overwrite)."""
+        if self._prefetch:
+            self._launch_prefetch()
         p = self._pull
         if self.async_mode:  # wait (per shard) until my previous gradient has been applied: read-your-writes
             nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
@@ -281,6 +305,28 @@ class GpuClusterEngine(NativeEngine):
             return
         nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
                        want_ptr=self.step_ptr())
+
+    def _launch_prefetch(self) -> None:
+        """Copy the prefetched matrices' bf16 shadow from the owner GPUs on a side stream (joined by the first GEMM
+        that reads them), gated on the same parameter version as everything else."""
+        main = torch.cuda.current_stream()
+        if not hasattr(self, "_pf_stream"):
+            self._pf_stream = torch.cuda.Stream(device=self.device)
+        self._pf_stream.wait_stream(main)
+        p = self._prefetch
+        with torch.cuda.stream(self._pf_stream):
+            if self.async_mode:
+                nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
+                                     [self.ctrl.data_ptr() + 4 * (WCTRL_MYTICKET + s[4]) for s in p])
+            else:
+                nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
+                               want_ptr=self.step_ptr())
+        self._pf_pending = True
+
+    def _join_prefetch(self) -> None:
+        if getattr(self, "_pf_pending", False):
+            torch.cuda.current_stream().wait_stream(self._pf_stream)
+            self._pf_pending = False
 
     def _post_backward(self, ws) -> None:
         """Push (X2): small gradients into this worker's slots, then arrive += 1 on every shard."""
@@ -399,7 +445,7 @@ class GpuClusterEngine(NativeEngine):
     def from_bench_args(cls, spec, a, rank: int, world: int, device) -> "GpuClusterEngine":
         topo = Topology.make(world, a.layout, a.ps)
         return cls(spec, topo, rank, device, learning_rate=0.01, seed=0, init_stddev=a.init_stddev,
-                   async_mode=getattr(a, "async_mode", False))
+                   async_mode=getattr(a, "async_mode", False), pull_mode=getattr(a, "pull", "auto"))
 
     # ---- restore / release helpers used by the cluster program -------------------------------
     def set_adam_state(self, sd: dict) -> None:

@@ -22,9 +22,11 @@ needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_c
 
 
 @needs2
-@pytest.mark.parametrize("layout,model", [("colocated", "cnn"), ("dedicated", "cnn"), ("colocated", "mlp")])
-def test_two_gpu_sync_ps(layout, model):
-    out = _torchrun(2, ["--layout", layout, "--model", model], 29611)
+@pytest.mark.parametrize("layout,model,pull", [("colocated", "cnn", "fused"), ("colocated", "cnn", "prefetch"),
+                                               ("dedicated", "cnn", "auto"), ("colocated", "mlp", "fused"),
+                                               ("colocated", "mlp", "prefetch")])
+def test_two_gpu_sync_ps(layout, model, pull):
+    out = _torchrun(2, ["--layout", layout, "--model", model, "--pull", pull], 29611)
     assert "OK" in out and "FAIL" not in out
 
 
