@@ -118,13 +118,29 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
   for (int t = 0; t < 25; ++t) acc[t] = 0.f;
   float accb = 0.f;
   const int pbeg = blockIdx.y * 98;
-  for (int pix = pbeg + grp; pix < pbeg + 98; pix += 8) {
+  // 98 pixels / 8 groups = at most 13 per thread: issue all their global loads first (the loop below would
+  // otherwise sit on one dependent load chain per pixel), then do the shared-memory / FMA work
+  float gq[13];
+  int aq[13];
+#pragma unroll
+  for (int it = 0; it < 13; ++it) {
+    const int pix = pbeg + grp + it * 8;
+    gq[it] = 0.f;
+    aq[it] = 0;
+    if (pix < pbeg + 98) {
+      const long long idx = ((long long)n * 196 + pix) * 32 + c;
+      const float g = dpool[idx];
+      gq[it] = (__bfloat162float(pool[idx]) > 0.f) ? g : 0.f;
+      aq[it] = amax[idx];
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < 13; ++it) {
+    const int pix = pbeg + grp + it * 8;
+    if (pix >= pbeg + 98) break;
     const int ph = pix / 14, pw = pix % 14;
-    const long long idx = (((long long)n * 14 + ph) * 14 + pw) * 32 + c;
-    float g = dpool[idx];
-    if (!(__bfloat162float(pool[idx]) > 0.f)) g = 0.f;
-    const int a = amax[idx];
-    const int h = 2 * ph + (a >> 1), wq = 2 * pw + (a & 1);
+    const float g = gq[it];
+    const int h = 2 * ph + (aq[it] >> 1), wq = 2 * pw + (aq[it] & 1);
     accb += g;
 #pragma unroll
     for (int kh = 0; kh < 5; ++kh)
@@ -208,9 +224,13 @@ head_rows_kernel(const float* __restrict__ pre, int pre_nsplit, long long pre_sp
   for (int k = tid; k < H; k += 256) {
     float a;
     if (pre) {
+      float pv[8];
+#pragma unroll
+      for (int sp = 0; sp < 8; ++sp) pv[sp] = sp < pre_nsplit ? pre[sp * pre_split_stride + (long long)r * H + k] : 0.f;
       a = hid_bias[k];
-#pragma unroll 8
-      for (int sp = 0; sp < pre_nsplit; ++sp) a += pre[sp * pre_split_stride + (long long)r * H + k];
+#pragma unroll
+      for (int sp = 0; sp < 8; ++sp) a += pv[sp];
+      for (int sp = 8; sp < pre_nsplit; ++sp) a += pre[sp * pre_split_stride + (long long)r * H + k];
       a = fmaxf(a, 0.f);
       if (keep_prob < 1.f) {
         const unsigned long long e = (unsigned long long)r * H + k;

@@ -72,67 +72,75 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   // 1 - beta^t through expm1 keeps full relative accuracy for small t (where beta^t is close to 1)
   const float om_b1t = -expm1f((float)t * logf(a.beta1)), om_b2t = -expm1f((float)t * logf(a.beta2));
   const float lr_t = a.lr * sqrtf(om_b2t) / om_b1t;
-  // 8 elements per thread per iteration; every load is issued before the first use (memory-level parallelism)
-  const long long n8 = a.n >> 3;
-  for (long long i8 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i8 < n8; i8 += (long long)gridDim.x * blockDim.x) {
-    const long long i = i8 << 3;
+  // Two float4 groups per thread per iteration, one block-stride apart (every warp instruction touches 512
+  // contiguous bytes); all eight streaming loads are issued before the first use (memory-level parallelism).
+  const long long n4 = a.n >> 2;
+  const long long stride4 = (long long)gridDim.x * blockDim.x;
+  const float* g0 = serve_slot ? serve_slot : a.slots[0];
+  const int nslots = serve_slot ? 1 : a.num_slots;
+  int cur = 0;  // cached piece index for the shadow lookup
+  for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += 2 * stride4) {
+    long long idx[2] = {i4 << 2, (i4 + stride4) << 2};
+    const bool ok1 = (i4 + stride4) < n4;
+    if (!ok1) idx[1] = idx[0];
     float4 w4[2], m4[2], v4[2], g4[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      w4[h] = *reinterpret_cast<const float4*>(a.w + i + 4 * h);
-      m4[h] = *reinterpret_cast<const float4*>(a.m + i + 4 * h);
-      v4[h] = *reinterpret_cast<const float4*>(a.v + i + 4 * h);
-      g4[h] = *reinterpret_cast<const float4*>((serve_slot ? serve_slot : a.slots[0]) + i + 4 * h);
+      w4[h] = __ldcs(reinterpret_cast<const float4*>(a.w + idx[h]));
+      m4[h] = __ldcs(reinterpret_cast<const float4*>(a.m + idx[h]));
+      v4[h] = __ldcs(reinterpret_cast<const float4*>(a.v + idx[h]));
+      g4[h] = __ldcs(reinterpret_cast<const float4*>(g0 + idx[h]));
     }
-    for (int r = 1; r < (serve_slot ? 1 : a.num_slots); ++r) {
+    for (int r = 1; r < nslots; ++r) {
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        const float4 x = *reinterpret_cast<const float4*>(a.slots[r] + i + 4 * h);
+        const float4 x = __ldcs(reinterpret_cast<const float4*>(a.slots[r] + idx[h]));
         g4[h].x += x.x; g4[h].y += x.y; g4[h].z += x.z; g4[h].w += x.w;
       }
     }
-    float wv[8], mv[8], vv[8], gv[8];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      wv[4 * h] = w4[h].x; wv[4 * h + 1] = w4[h].y; wv[4 * h + 2] = w4[h].z; wv[4 * h + 3] = w4[h].w;
-      mv[4 * h] = m4[h].x; mv[4 * h + 1] = m4[h].y; mv[4 * h + 2] = m4[h].z; mv[4 * h + 3] = m4[h].w;
-      vv[4 * h] = v4[h].x; vv[4 * h + 1] = v4[h].y; vv[4 * h + 2] = v4[h].z; vv[4 * h + 3] = v4[h].w;
-      gv[4 * h] = g4[h].x * a.scale; gv[4 * h + 1] = g4[h].y * a.scale;
-      gv[4 * h + 2] = g4[h].z * a.scale; gv[4 * h + 3] = g4[h].w * a.scale;
-    }
+      if (h == 1 && !ok1) break;
+      float wv[4] = {w4[h].x, w4[h].y, w4[h].z, w4[h].w}, mv[4] = {m4[h].x, m4[h].y, m4[h].z, m4[h].w};
+      float vv[4] = {v4[h].x, v4[h].y, v4[h].z, v4[h].w};
+      const float gv[4] = {g4[h].x * a.scale, g4[h].y * a.scale, g4[h].z * a.scale, g4[h].w * a.scale};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      mv[j] = a.beta1 * mv[j] + (1.f - a.beta1) * gv[j];
-      vv[j] = a.beta2 * vv[j] + (1.f - a.beta2) * gv[j] * gv[j];
-      wv[j] -= lr_t * mv[j] / (sqrtf(vv[j]) + a.eps);  // TF form: epsilon outside the bias correction
-    }
+      for (int j = 0; j < 4; ++j) {
+        mv[j] = a.beta1 * mv[j] + (1.f - a.beta1) * gv[j];
+        vv[j] = a.beta2 * vv[j] + (1.f - a.beta2) * gv[j] * gv[j];
+        // TF form: epsilon outside the bias correction.  MUFU-based sqrt and divide (2 ulp): the IEEE versions made
+        // this streaming kernel issue-bound (158 instructions per element).
+        wv[j] -= __fdividef(lr_t * mv[j], vv[j] * rsqrtf(fmaxf(vv[j], 1e-38f)) + a.eps);
+      }
+      const long long i = idx[h];
+      __stcs(reinterpret_cast<float4*>(a.w + i), make_float4(wv[0], wv[1], wv[2], wv[3]));
+      __stcs(reinterpret_cast<float4*>(a.m + i), make_float4(mv[0], mv[1], mv[2], mv[3]));
+      __stcs(reinterpret_cast<float4*>(a.v + i), make_float4(vv[0], vv[1], vv[2], vv[3]));
+      if (a.shadow) {
+        // pieces are 64-element aligned in the arena, so one float4 lies in one piece; a thread's indices grow
+        // monotonically, so the piece found last time is almost always still the right one
+        if (!(i >= pt.p[cur].arena_off && i < pt.p[cur].arena_off + pt.p[cur].numel)) {
+          for (int q = 0; q < pt.n; ++q)
+            if (i >= pt.p[q].arena_off && i < pt.p[q].arena_off + pt.p[q].numel) { cur = q; break; }
+        }
+        {
+          const tfd_piece_t& pc = pt.p[cur];
+          if (i >= pc.arena_off && i < pc.arena_off + pc.numel) {
+            if (pc.ld_shadow > 0) {
+              const long long e0 = i - pc.arena_off;
+              if (pc.ld_shadow == pc.cols) {
+                *reinterpret_cast<uint2*>(a.shadow + pc.shadow_off + e0) =
+                    make_uint2(pack_bf16x2(wv[0], wv[1]), pack_bf16x2(wv[2], wv[3]));
+              } else {
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      *reinterpret_cast<float4*>(a.w + i + 4 * h) = make_float4(wv[4 * h], wv[4 * h + 1], wv[4 * h + 2], wv[4 * h + 3]);
-      *reinterpret_cast<float4*>(a.m + i + 4 * h) = make_float4(mv[4 * h], mv[4 * h + 1], mv[4 * h + 2], mv[4 * h + 3]);
-      *reinterpret_cast<float4*>(a.v + i + 4 * h) = make_float4(vv[4 * h], vv[4 * h + 1], vv[4 * h + 2], vv[4 * h + 3]);
-    }
-    if (a.shadow) {
-      // pieces are 64-element aligned in the arena, so the 8 elements lie in one piece
-      for (int q = 0; q < pt.n; ++q) {
-        const tfd_piece_t& pc = pt.p[q];
-        if (i >= pc.arena_off && i < pc.arena_off + pc.numel) {
-          if (pc.ld_shadow > 0) {
-            const long long e0 = i - pc.arena_off;
-            if (pc.ld_shadow == pc.cols) {
-              bf16* d = a.shadow + pc.shadow_off + e0;
-              *reinterpret_cast<uint4*>(d) = make_uint4(pack_bf16x2(wv[0], wv[1]), pack_bf16x2(wv[2], wv[3]),
-                                                        pack_bf16x2(wv[4], wv[5]), pack_bf16x2(wv[6], wv[7]));
-            } else {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const long long e = e0 + j;
-                if (e < pc.numel)
-                  a.shadow[pc.shadow_off + (e / pc.cols) * pc.ld_shadow + (e % pc.cols)] = __float2bfloat16(wv[j]);
+                for (int j = 0; j < 4; ++j) {
+                  const long long e = e0 + j;
+                  if (e < pc.numel)
+                    a.shadow[pc.shadow_off + (e / pc.cols) * pc.ld_shadow + (e % pc.cols)] = __float2bfloat16(wv[j]);
+                }
               }
             }
           }
-          break;
         }
       }
     }
@@ -246,7 +254,7 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
                        float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                        unsigned* version_flag, unsigned* global_step, unsigned* queue, int qlen,
                        const unsigned* shutdown, void* stream) {
-  TFD_REQUIRE(n % 8 == 0, "adam: arena length %lld not a multiple of 8", n);
+  TFD_REQUIRE(n % 4 == 0, "adam: arena length %lld not a multiple of 4", n);
   TFD_REQUIRE(num_pieces <= kMaxPieces, "adam: too many pieces (%d)", num_pieces);
   TFD_REQUIRE(num_slots >= 1, "adam: need at least one gradient slot");
   PieceTable pt;

@@ -95,7 +95,8 @@ class ClusterSpec:
         """Rendezvous endpoint: ps task 0's host:port (the only address every task knows)."""
         a = self.task_address("ps", 0)
         if a.is_gpu:
-            return "127.0.0.1", 29500 + (a.gpu_ordinal or 0)
+            import os
+            return "127.0.0.1", int(os.environ.get("TFD_MASTER_PORT", 29500 + (a.gpu_ordinal or 0)))
         return a.host_port
 
 

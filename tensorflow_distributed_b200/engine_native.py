@@ -256,8 +256,13 @@ class NativeEngine:
 
     def _cnn_forward(self, ws: Workspace, training: bool, keep_prob: float, mask_out=None) -> None:
         B = ws.B
-        if training:  # accumulators of the atomic epilogues (all tiny)
-            nat.zero_multi([self.G("weights/wc1"), self.G("biases/bc1"), self.G("weights/wc2"), self.G("biases/bc2")])
+        if training:  # accumulators of the atomic epilogues (all tiny): cleared off the critical path
+            main = torch.cuda.current_stream()
+            s2 = self._side_streams()[1]
+            s2.wait_stream(main)
+            with torch.cuda.stream(s2):
+                nat.zero_multi([self.G("weights/wc1"), self.G("biases/bc1"), self.G("weights/wc2"),
+                                self.G("biases/bc2")])
         nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, B)
         nat.conv2_fwd(ws.pool1, self.S("weights/wc2"), self.P("biases/bc2"), ws.pool2, ws.am2, B, ref=self.conv2_ref)
         self.gemm_fwd("weights/wd1", ws.pool2.view(B, 3136), B, ws.fc1acc, mode=nat.EPI_STORE_F32, bn=64,
@@ -289,6 +294,7 @@ class NativeEngine:
         # fc1 dgrad: dpool2[B,3136] = dhid wd1^T    (wd1 read K-major in place)
         self.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
                         split_stride=B * 3136, ld_out=3136)
+        main.wait_stream(s2)  # the zeroed accumulators
         nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"), B, nsplit=ws.dg_splits,
                       split_stride=B * 3136)
         s2.wait_stream(main)
@@ -421,3 +427,68 @@ class NativeEngine:
         self._sequence(ws, "grads", keep_prob, mask)
         loss, _ = self._fetch_scalars(ws)
         return loss, self.get_grads(), mask
+
+    def train_loop(self, batches, keep_prob: float = 0.75, fetch_loss: bool = True) -> List[float]:
+        """Public streaming API: run one training step per (x, y) host batch, end to end.
+
+        Every step's inputs go pinned-host -> device (H2D on a copy stream, double-buffered so the copy of step i+1
+        runs under the compute of step i) and every step's loss comes back device -> pinned host (D2H, read by the
+        host two steps late so it never stalls the device).  Returns the per-step losses."""
+        batches = iter(batches)
+        first = next(batches, None)
+        if first is None:
+            return []
+        B = len(first[0])
+        if not getattr(self, "is_worker", True):  # ps-only GPU of a dedicated layout: one shard apply per step
+            ws, n = self.workspace(B), 1
+            self._run(ws, "train", keep_prob)
+            for _ in batches:
+                self._run(ws, "train", keep_prob)
+                n += 1
+            return [0.0] * n
+        ws = self.workspace(B)
+        dev = self.device
+        if not hasattr(ws, "_slots"):
+            ws._slots = [(torch.zeros(B, 784, device=dev), torch.zeros(B, 10, device=dev),
+                          torch.zeros(B, 784).pin_memory(), torch.zeros(B, 10).pin_memory()) for _ in range(2)]
+            ws._copy_stream = torch.cuda.Stream(device=dev)
+            ws._copied = [torch.cuda.Event() for _ in range(2)]
+            ws._consumed = [torch.cuda.Event() for _ in range(2)]
+            ws._loss_ring = torch.zeros(4, 2).pin_memory()
+            ws._loss_ev = [torch.cuda.Event() for _ in range(4)]
+        main = torch.cuda.current_stream()
+        losses: List[float] = []
+        pending: List[int] = []
+        i, item = 0, first
+        for k in range(2):
+            ws._consumed[k].record(main)
+        while item is not None:
+            x, y = item
+            xd, yd, xh, yh = ws._slots[i & 1]
+            # host -> pinned staging (the slot is free once its previous H2D has been issued and consumed)
+            ws._consumed[i & 1].synchronize()
+            xh.copy_(torch.as_tensor(np.ascontiguousarray(x) if isinstance(x, np.ndarray) else x).reshape(B, 784))
+            yh.copy_(torch.as_tensor(np.ascontiguousarray(y) if isinstance(y, np.ndarray) else y).reshape(B, 10))
+            with torch.cuda.stream(ws._copy_stream):
+                xd.copy_(xh, non_blocking=True)
+                yd.copy_(yh, non_blocking=True)
+                ws._copied[i & 1].record(ws._copy_stream)
+            main.wait_event(ws._copied[i & 1])
+            ws.x.copy_(xd, non_blocking=True)
+            ws.y.copy_(yd, non_blocking=True)
+            ws._consumed[i & 1].record(main)
+            self._run(ws, "train", keep_prob)
+            if fetch_loss:
+                if len(pending) == 4:  # ring full: the oldest loss has long been written
+                    j = pending.pop(0)
+                    ws._loss_ev[j & 3].synchronize()
+                    losses.append(float(ws._loss_ring[j & 3, 0]))
+                ws._loss_ring[i & 3].copy_(ws.scalars, non_blocking=True)
+                ws._loss_ev[i & 3].record(main)
+                pending.append(i)
+            i += 1
+            item = next(batches, None)
+        for j in pending:
+            ws._loss_ev[j & 3].synchronize()
+            losses.append(float(ws._loss_ring[j & 3, 0]))
+        return losses

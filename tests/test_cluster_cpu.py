@@ -104,3 +104,28 @@ def test_cnn_default_tokens_two_ps_shards(free_port):
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
     assert "Mean Accuracy :" in outs[2] and "Mean Accuracy :" in outs[3]
+
+
+@pytest.mark.timeout(300)
+def test_backup_workers_tolerate_a_straggler(free_port):
+    """R-of-N (m:62-65): 3 workers, aggregate the fastest 2; worker 2 is stalled by fault injection.
+    Training still reaches the global step; the straggler's stale gradients are dropped, it rejoins via tokens."""
+    port = free_port
+    hosts = ["--ps_hosts=127.0.0.1:%d" % port,
+             "--worker_hosts=127.0.0.1:%d,127.0.0.1:%d,127.0.0.1:%d" % (port + 1, port + 2, port + 3)]
+    common = hosts + ["--backend=cpu", "--step_timeout_secs=120", "--model=mlp", "--hidden_units=16", "--init_stddev=0.1",
+                      "--train_steps=4", "--replicas_to_aggregate=2", "--batch_size=32", "--validation_batch_size=100",
+                      "--validation_batches=1", "--inject_fault=stall:2:1.5"]
+    cmds = [("mnist_python_m.py", []), ("mnist_python_w1.py", []), ("mnist_python_w2.py", []),
+            ("mnist_python_w2.py", ["--task_index=2"])]
+    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, s)] + common + e, stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True, env=dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2"),
+                              cwd=ROOT) for s, e in cmds]
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+    fast = outs[1].count(": training step") + outs[2].count(": training step")
+    slow = outs[3].count(": training step")
+    assert fast >= 2 * 3 and slow < outs[1].count(": training step")  # the stalled worker did fewer steps
+    for o in outs[1:]:
+        assert "Mean Accuracy :" in o

@@ -34,3 +34,53 @@ def test_two_gpu_sync_ps(layout, model, pull):
 def test_two_gpu_async_apply_on_arrival_counts_every_update():
     out = _torchrun(2, ["--layout", "dedicated", "--async_mode"], 29613)
     assert "OK" in out and "FAIL" not in out and "async" in out
+
+
+needs3 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 3, reason="needs 3 GPUs")
+
+
+def _run_scripts(extra, tmp_path, port):
+    """ps on gpu:0, chief on gpu:1, worker 1 on gpu:2 -- three OS processes started like m / w1 / w2."""
+    common = ["--ps_hosts=gpu:0", "--worker_hosts=gpu:1,gpu:2", "--train_steps=6", "--init_stddev=0.05",
+              "--validation_batch_size=500", "--validation_batches=2", "--step_timeout_secs=120"] + extra
+    env = dict(os.environ, PYTHONPATH=ROOT, TFD_MASTER_PORT=str(port))
+    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, s)] + common, stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True, env=env, cwd=ROOT)
+             for s in ("mnist_python_m.py", "mnist_python_w1.py", "mnist_python_w2.py")]
+    outs = []
+    for p in procs:
+        try:
+            outs.append(p.communicate(timeout=280)[0])
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o[-3000:]
+    return outs
+
+
+@needs3
+def test_gpu_cluster_scripts_sync_and_resume(tmp_path):
+    ps, w1, w2 = _run_scripts(["--train_dir=%s" % tmp_path], tmp_path, 29700)
+    assert "job name = ps" in ps
+    for o, t in ((w1, 0), (w2, 1)):
+        assert "Worker %d: Session initialization complete." % t in o
+        assert o.count(": training step") == 6 and "(global step: 6)" in o
+        assert "Mean Accuracy :" in o and "Training elapsed time:" in o
+    from tensorflow_distributed_b200 import checkpoint
+    from tensorflow_distributed_b200.models.spec import cnn_spec
+    blob = checkpoint.load(checkpoint.latest_checkpoint(str(tmp_path)), cnn_spec())
+    assert blob["global_step"] == 6 and blob["adam"]["t"] == 6
+    assert tuple(blob["variables"]["weights/wd1"].shape) == (3136, 1024)
+    # resume: the checkpoint already satisfies train_steps, so no further step is taken
+    ps, w1, w2 = _run_scripts(["--train_dir=%s" % tmp_path], tmp_path, 29710)
+    assert w1.count(": training step") == 0 and "Mean Accuracy :" in w1
+
+
+@needs3
+def test_gpu_cluster_scripts_async(tmp_path):
+    ps, w1, w2 = _run_scripts(["--sync_replicas=False"], tmp_path, 29720)
+    n = w1.count(": training step") + w2.count(": training step")
+    assert n >= 6  # global_step counts worker updates (m:301)
+    assert "Mean Accuracy :" in w1 and "Mean Accuracy :" in w2
