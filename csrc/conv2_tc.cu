@@ -76,6 +76,8 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  grid_dep_wait();
+  grid_dep_launch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -241,6 +243,8 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  grid_dep_wait();
+  grid_dep_launch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -332,9 +336,8 @@ extern "C" int tfd_conv2_fwd(const void* in, const void* w, const float* b, void
   }
   const int tiles = B * 2;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv2_tc_kernel<true><<<grid, kThreads, C::kSmem, static_cast<cudaStream_t>(stream)>>>(
-      tmA, tmW, b, static_cast<bf16*>(pool_out), argmax, nullptr, B, tiles);
-  TFD_LAUNCH_CHECK();
+  TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<true>, dim3(grid), dim3(kThreads), C::kSmem, static_cast<cudaStream_t>(stream),
+                            tmA, tmW, b, static_cast<bf16*>(pool_out), argmax, (float*)nullptr, B, tiles));
   return 0;
 }
 
@@ -352,9 +355,8 @@ extern "C" int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, 
   }
   const int tiles = B * 2;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv2_tc_kernel<false><<<grid, kThreads, C::kSmem, static_cast<cudaStream_t>(stream)>>>(
-      tmA, tmW, nullptr, nullptr, nullptr, dx, B, tiles);
-  TFD_LAUNCH_CHECK();
+  TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<false>, dim3(grid), dim3(kThreads), C::kSmem, static_cast<cudaStream_t>(stream),
+                            tmA, tmW, (const float*)nullptr, (bf16*)nullptr, (unsigned char*)nullptr, dx, B, tiles));
   return 0;
 }
 
@@ -373,7 +375,7 @@ extern "C" int tfd_conv2_wgrad(const void* in, const void* dy, float* dw, int B,
   int chunks = num_sms() / 7;
   if (chunks > tiles) chunks = tiles;
   if (chunks < 1) chunks = 1;
-  conv2_wgrad_tc_kernel<<<dim3(chunks, 7), kThreads, kWgSmem, static_cast<cudaStream_t>(stream)>>>(tmIn, tmDy, dw, tiles);
-  TFD_LAUNCH_CHECK();
+  TFD_CUDA_CHECK(tfd_launch(conv2_wgrad_tc_kernel, dim3(chunks, 7), dim3(kThreads), kWgSmem, static_cast<cudaStream_t>(stream),
+                            tmIn, tmDy, dw, tiles));
   return 0;
 }

@@ -30,6 +30,8 @@ __device__ __forceinline__ float u01(uint32_t x) { return ((float)x + 0.5f) * 2.
 
 __global__ void random_normal_kernel(float* __restrict__ out, long long n, unsigned long long seed, float stddev,
                                      long long off4) {
+  grid_dep_wait();
+  grid_dep_launch();
   const long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // 4 values per thread
   if (i4 * 4 >= n) return;
   const long long c4 = i4 + off4;  // counter = global index of the 4-element group (shard-independent stream)
@@ -46,6 +48,8 @@ __global__ void random_normal_kernel(float* __restrict__ out, long long n, unsig
 
 __global__ void cast_bf16_kernel(const float* __restrict__ src, long long ld_src, bf16* __restrict__ dst,
                                  long long ld_dst, int rows, int cols) {
+  grid_dep_wait();
+  grid_dep_launch();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)rows * ld_dst) return;
   const int r = (int)(i / ld_dst), c = (int)(i % ld_dst);
@@ -59,6 +63,8 @@ __global__ void cast_bf16_kernel(const float* __restrict__ src, long long ld_src
 __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                         const float* __restrict__ b, bf16* __restrict__ out,
                                                         unsigned char* __restrict__ amax) {
+  grid_dep_wait();
+  grid_dep_launch();
   __shared__ float patch[18][32];  // input rows 14*half-2 .. +17, cols -2 .. 29
   const int n = blockIdx.x, half = blockIdx.y;
   for (int i = threadIdx.x; i < 18 * 32; i += blockDim.x) {
@@ -104,6 +110,8 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
 __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
                                                           const bf16* __restrict__ pool, const unsigned char* __restrict__ amax,
                                                           float* __restrict__ dw, float* __restrict__ db) {
+  grid_dep_wait();
+  grid_dep_launch();
   __shared__ float img[32][33];
   __shared__ float red[8][26][32];
   const int n = blockIdx.x;
@@ -166,6 +174,8 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
 __global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict__ dpool, int nsplit, long long split_stride,
                                                         const bf16* __restrict__ pool, const unsigned char* __restrict__ amax,
                                                         bf16* __restrict__ dy, float* __restrict__ db, long long npix) {
+  grid_dep_wait();
+  grid_dep_launch();
   __shared__ float red[256];
   const int c = threadIdx.x & 63, pl = threadIdx.x >> 6;
   float gsum = 0.f;
@@ -215,6 +225,8 @@ head_rows_kernel(const float* __restrict__ pre, int pre_nsplit, long long pre_sp
                  int B, int H, long long ld_h, float keep_prob, unsigned long long seed, unsigned long long step_base,
                  const unsigned* __restrict__ step_ptr, int training, bf16* __restrict__ hid_out, bf16* __restrict__ dhid, float* __restrict__ dlogits,
                  float* __restrict__ loss_row, unsigned char* __restrict__ hit, unsigned char* __restrict__ keep_out) {
+  grid_dep_wait();
+  grid_dep_launch();
   extern __shared__ float sh[];  // H hidden values, then 8*10 partials, then 10 dlogits
   float* part = sh + H;
   float* dl = part + 80;
@@ -322,6 +334,8 @@ head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, lo
                  const float* __restrict__ dlogits, const float* __restrict__ loss_row,
                  const unsigned char* __restrict__ hit, int B, int H, float* __restrict__ d_out_w,
                  float* __restrict__ d_hid_bias, float* __restrict__ d_out_b, float* __restrict__ scalars) {
+  grid_dep_wait();
+  grid_dep_launch();
   extern __shared__ float dls[];  // [B][10], then [8][11][32] partials
   float* part = dls + B * 10;
   const int tid = threadIdx.x, lane = tid & 31, wv = tid >> 5;
@@ -380,6 +394,8 @@ head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, lo
 }
 
 __global__ void colsum_bf16_kernel(const bf16* __restrict__ x, long long ld, int rows, int cols, float* __restrict__ out) {
+  grid_dep_wait();
+  grid_dep_launch();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= cols) return;
   float s = 0.f;
@@ -481,6 +497,8 @@ struct ZeroTable {
   int cnt;
 };
 __global__ void zero_multi_kernel(const __grid_constant__ ZeroTable t) {
+  grid_dep_wait();
+  grid_dep_launch();
   float* p = t.p[blockIdx.y];
   const long long n = t.n[blockIdx.y], n4 = n >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x)
@@ -497,7 +515,7 @@ extern "C" int tfd_random_normal(float* out, long long n, unsigned long long see
                                  void* stream) {
   TFD_REQUIRE(elem_offset % 4 == 0, "random_normal: element offset %lld not a multiple of 4", elem_offset);
   const long long n4 = (n + 3) / 4;
-  random_normal_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, ST(stream)>>>(out, n, seed, stddev, elem_offset / 4);
+  TFD_CUDA_CHECK(tfd_launch(random_normal_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, ST(stream), out, n, seed, stddev, elem_offset / 4));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -505,21 +523,21 @@ extern "C" int tfd_random_normal(float* out, long long n, unsigned long long see
 extern "C" int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long long ld_dst, int rows, int cols,
                              void* stream) {
   const long long total = (long long)rows * ld_dst;
-  cast_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ST(stream)>>>(src, ld_src, (bf16*)dst, ld_dst, rows, cols);
+  TFD_CUDA_CHECK(tfd_launch(cast_bf16_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, ST(stream), src, ld_src, (bf16*)dst, ld_dst, rows, cols));
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int tfd_conv1_fwd(const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
                              void* stream) {
-  conv1_fwd_kernel<<<dim3(B, 2), 224, 0, ST(stream)>>>(x, w, b, (bf16*)pool_out, argmax);
+  TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel, dim3(B, 2), dim3(224), 0, ST(stream), x, w, b, (bf16*)pool_out, argmax));
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int tfd_conv1_wgrad(const float* x, const float* dpool, const void* pool_out, const unsigned char* argmax,
                                float* dw, float* db, int B, void* stream) {
-  conv1_wgrad_kernel<<<dim3(B, 2), 256, 0, ST(stream)>>>(x, dpool, (const bf16*)pool_out, argmax, dw, db);
+  TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel, dim3(B, 2), dim3(256), 0, ST(stream), x, dpool, (const bf16*)pool_out, argmax, dw, db));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -527,8 +545,8 @@ extern "C" int tfd_conv1_wgrad(const float* x, const float* dpool, const void* p
 extern "C" int tfd_pool2_bwd(const float* dpool, int nsplit, long long split_stride, const void* pool_out,
                              const unsigned char* argmax, void* dy, float* db, int B, void* stream) {
   const long long npix = (long long)B * 49;
-  pool2_bwd_kernel<<<(unsigned)((npix + 15) / 16), 256, 0, ST(stream)>>>(dpool, nsplit < 1 ? 1 : nsplit, split_stride,
-                                                                       (const bf16*)pool_out, argmax, (bf16*)dy, db, npix);
+  TFD_CUDA_CHECK(tfd_launch(pool2_bwd_kernel, dim3((unsigned)((npix + 15) / 16)), dim3(256), 0, ST(stream), dpool, nsplit < 1 ? 1 : nsplit, split_stride,
+                                                                       (const bf16*)pool_out, argmax, (bf16*)dy, db, npix));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -548,10 +566,10 @@ extern "C" int tfd_head_rows(const float* pre_f32, int pre_nsplit, long long pre
     TFD_CUDA_CHECK(cudaFuncSetAttribute(head_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  head_rows_kernel<<<B, 256, smem, ST(stream)>>>(pre_f32, pre_nsplit < 1 ? 1 : pre_nsplit, pre_split_stride,
+  TFD_CUDA_CHECK(tfd_launch(head_rows_kernel, dim3(B), dim3(256), smem, ST(stream), pre_f32, pre_nsplit < 1 ? 1 : pre_nsplit, pre_split_stride,
                                                  (const bf16*)hid_bf16, hid_bias, out_w, out_b, labels, B, H, ld_h,
                                                  keep_prob, seed, step, step_ptr, training, (bf16*)hid_out, (bf16*)dhid, dlogits,
-                                                 loss_row, hit, keep_mask_out);
+                                                 loss_row, hit, keep_mask_out));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -567,14 +585,14 @@ extern "C" int tfd_head_cols(const void* hid, const void* dhid, long long ld_h, 
     configured = smem;
   }
   const int blocks = hid ? (H + 31) / 32 : 1;
-  head_cols_kernel<<<blocks, 256, smem, ST(stream)>>>((const bf16*)hid, (const bf16*)dhid, ld_h, dlogits, loss_row, hit, B,
-                                                      H, d_out_w, d_hid_bias, d_out_b, scalars);
+  TFD_CUDA_CHECK(tfd_launch(head_cols_kernel, dim3(blocks), dim3(256), smem, ST(stream), (const bf16*)hid, (const bf16*)dhid, ld_h, dlogits, loss_row, hit, B,
+                                                      H, d_out_w, d_hid_bias, d_out_b, scalars));
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int tfd_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out, void* stream) {
-  colsum_bf16_kernel<<<(cols + 255) / 256, 256, 0, ST(stream)>>>((const bf16*)x, ld, rows, cols, out);
+  TFD_CUDA_CHECK(tfd_launch(colsum_bf16_kernel, dim3((cols + 255) / 256), dim3(256), 0, ST(stream), (const bf16*)x, ld, rows, cols, out));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -625,7 +643,7 @@ extern "C" int tfd_zero_multi(float* const* ptrs, const long long* ns, int count
   long long bx = (maxn / 4 + 255) / 256;
   if (bx < 1) bx = 1;
   if (bx > 296) bx = 296;
-  zero_multi_kernel<<<dim3((unsigned)bx, count), 256, 0, ST(stream)>>>(t);
+  TFD_CUDA_CHECK(tfd_launch(zero_multi_kernel, dim3((unsigned)bx, count), dim3(256), 0, ST(stream), t));
   TFD_LAUNCH_CHECK();
   return 0;
 }

@@ -110,6 +110,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  grid_dep_wait();    // prologue above overlapped the previous kernel's tail; from here on we touch global memory
+  grid_dep_launch();
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -310,8 +312,7 @@ int launch(const CUtensorMap& tmA, const TmapArray& tmBs, const GemmParams& p, c
     attr_set = true;
   }
   dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, p.splits);
-  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmBs, p, sg);
-  TFD_LAUNCH_CHECK();
+  TFD_CUDA_CHECK(tfd_launch(kern, grid, dim3(kThreads), C::kSmemBytes, stream, tmA, tmBs, p, sg));
   return 0;
 }
 
@@ -430,6 +431,7 @@ float* g_noalloc_planes_dev[kMaxDevices] = {nullptr};  // device address of the 
 __global__ void __launch_bounds__(256)
 sum_planes_kernel(const float* __restrict__ planes, int nplanes, long long plane_stride, int M, int N,
                   float* __restrict__ out, long long ld_out, const float* __restrict__ bias, int relu) {
+  grid_dep_wait();
   const long long total = (long long)M * N;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int r = (int)(i / N), c = (int)(i % N);

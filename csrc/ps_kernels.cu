@@ -38,6 +38,8 @@ struct AdamArgs {
 };
 
 __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __grid_constant__ PieceTable pt) {
+  grid_dep_wait();
+  grid_dep_launch();
   // Every thread derives the step index and lr_t itself (one broadcast load + a few SFU ops): no block barrier
   // and no serial prologue in front of the streaming loop.  Only one thread per block waits for the arrivals.
   const unsigned t = a.t_counter[0] + 1;  // this update's 1-based index
@@ -180,6 +182,8 @@ struct PushTable {
 // grid (blocks_per_seg, nseg)
 __global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushTable t, float scale, unsigned* block_counter,
                                                    unsigned* local_step) {
+  grid_dep_wait();
+  grid_dep_launch();
   const PushSeg s = t.seg[blockIdx.y];
   const long long n4 = s.n >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
@@ -232,6 +236,8 @@ struct PullTable {
 
 __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullTable t, unsigned want_base,
                                                    const unsigned* want_ptr) {
+  grid_dep_wait();
+  grid_dep_launch();
   const PullSeg s = t.seg[blockIdx.y];
   const unsigned want = want_base + (want_ptr ? *want_ptr : 0u);
   if (s.version) {
@@ -269,7 +275,7 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
   a.queue = queue; a.qlen = qlen; a.shutdown = shutdown;
   long long blocks = (n / 8 + 255) / 256;
   if (blocks > 148 * 3) blocks = 148 * 3;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
-  adam_apply_kernel<<<(unsigned)blocks, 256, 0, ST(stream)>>>(a, pt);
+  TFD_CUDA_CHECK(tfd_launch(adam_apply_kernel, dim3((unsigned)blocks), dim3(256), 0, ST(stream), a, pt));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -313,7 +319,7 @@ static int push_launch(const void* const* srcs, void* const* dsts, const long lo
   long long bx = (maxn / 4 + 255) / 256;
   if (bx < 1) bx = 1;
   if (bx > 148) bx = 148;
-  push_kernel<<<dim3((unsigned)bx, nseg), 256, 0, ST(stream)>>>(t, scale, block_counter, local_step);
+  TFD_CUDA_CHECK(tfd_launch(push_kernel, dim3((unsigned)bx, nseg), dim3(256), 0, ST(stream), t, scale, block_counter, local_step));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -358,7 +364,7 @@ static int pull_launch(const void* const* srcs, void* const* dsts, const long lo
   long long bx = (maxn / 4 + 255) / 256;
   if (bx < 1) bx = 1;
   if (bx > 64) bx = 64;
-  pull_kernel<<<dim3((unsigned)bx, nseg), 256, 0, ST(stream)>>>(t, want_version, want_ptr);
+  TFD_CUDA_CHECK(tfd_launch(pull_kernel, dim3((unsigned)bx, nseg), dim3(256), 0, ST(stream), t, want_version, want_ptr));
   TFD_LAUNCH_CHECK();
   return 0;
 }

@@ -71,6 +71,14 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---- programmatic dependent launch (PDL) ----
+// Every kernel of the training step is launched with programmaticStreamSerialization: the next kernel's CTAs may be
+// scheduled (and run their prologue: barrier init, TMEM alloc, tensor-map prefetch) while this kernel drains.
+// grid_dep_wait() returns once ALL earlier kernels in the stream have completed and flushed; no kernel touches
+// global memory before it.  grid_dep_launch() is this kernel's "my successor may be scheduled" signal.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- mbarrier ----
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -244,6 +252,28 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t target
 
 }  // namespace tfd
 #endif  // __CUDACC__
+
+// ---------------------------------------------------------------------------------------------
+// host: kernel launch with the PDL attribute (tfd_set_pdl(0) turns it into a plain serialized launch)
+// ---------------------------------------------------------------------------------------------
+int tfd_pdl_enabled();
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t tfd_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = tfd_pdl_enabled();
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // host: tensor-map construction (driver entry point fetched at run time; no -lcuda needed)

@@ -16,6 +16,8 @@ extern "C" {
 
 const char* tfd_last_error(void);
 int tfd_version(void);
+/* Programmatic dependent launch for the step kernels (default off: measured no gain; also env TFD_PDL=1). */
+int tfd_set_pdl(int on);
 int tfd_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin);
 
 /* ---- GEMM epilogues (tfd_gemm_bf16 `mode`) ---- */
