@@ -103,6 +103,8 @@ def parse():
     ap.add_argument("--async", dest="async_mode", action="store_true")
     ap.add_argument("--pull", default="auto", choices=["auto", "fused", "prefetch"],
                     help="big-matrix pull: fused into the GEMMs (TMA from the ps GPU) or prefetched under the conv layers")
+    ap.add_argument("--grad-dtype", dest="grad_dtype", default="fp32", choices=["fp32", "bf16"],
+                    help="storage type of the pushed gradients in the ps staging slots (multi-GPU)")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--init-stddev", type=float, default=1.0)
     return ap.parse_args()

@@ -237,6 +237,39 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       }
+    } else if (p.mode == TFD_EPI_STORE_BF16 && (p.ld_out & 7) == 0 && n0 + BN <= p.N) {
+      // Coalesced bf16 store (bf16 gradient push): same staging idea, rows of BN*2 bytes.
+      constexpr int kPitchB = BN * 2 + 16;  // bytes; odd multiple of 16 -> conflict-free
+      uint8_t* stg = smem + (size_t)q * 32 * kPitchB;
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 16) {
+        float v[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+        if (p.bias) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = v[i] * p.alpha + __ldg(p.bias + n0 + c + i);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] *= p.alpha;
+        }
+        uint4* d = reinterpret_cast<uint4*>(stg + lane * kPitchB + c * 2);
+        d[0] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+        d[1] = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]),
+                          pack_bf16x2(v[14], v[15]));
+      }
+      __syncwarp();
+      __nv_bfloat16* ob = (sg.mode == TFD_SEG_OUT_M ? reinterpret_cast<__nv_bfloat16*>(out_f32) : p.out_bf16) + n0;
+      constexpr int kLanesPerRow = BN / 8;  // 16-byte pieces per row
+      constexpr int kRowsPerInst = 32 / kLanesPerRow;
+#pragma unroll 4
+      for (int r0 = 0; r0 < 32; r0 += kRowsPerInst) {
+        const int r = r0 + lane / kLanesPerRow;
+        const int piece = lane % kLanesPerRow;
+        if (m0 + q * 32 + r < p.M) {
+          const uint4 o4 = *reinterpret_cast<const uint4*>(stg + r * kPitchB + piece * 16);
+          *reinterpret_cast<uint4*>(ob + (long long)(out_row - lane + r) * p.ld_out + piece * 8) = o4;
+        }
+      }
     } else
 #pragma unroll 1
     for (int c = 0; c < BN; c += 16) {
@@ -279,7 +312,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int i = 0; i < ncols; ++i) red_add_f32(o + i, v[i]);
         }
       } else {  // bf16 outputs
-        __nv_bfloat16* o = p.out_bf16 + (long long)row * p.ld_out + col0;
+        __nv_bfloat16* o = (sg.mode == TFD_SEG_OUT_M ? reinterpret_cast<__nv_bfloat16*>(out_f32) : p.out_bf16) +
+                           (long long)out_row * p.ld_out + col0;
         if (ncols == 16 && (p.ld_out & 7) == 0) {
           uint4 w0 = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
                                 pack_bf16x2(v[6], v[7]));
@@ -333,8 +367,9 @@ extern "C" int tfd_gemm_bf16_seg(const void* A, long long lda, int a_mn, const v
   TFD_REQUIRE(seg_mode == TFD_SEG_NONE || seg_rows != nullptr, "gemm: segmented call without boundaries");
   TFD_REQUIRE(seg_mode != TFD_SEG_B_K || b_mn == 1, "gemm: TFD_SEG_B_K needs B stored [K,N]");
   TFD_REQUIRE(seg_mode != TFD_SEG_B_N || b_mn == 0, "gemm: TFD_SEG_B_N needs B stored [N,K]");
-  TFD_REQUIRE(seg_mode != TFD_SEG_OUT_M || (mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32),
-              "gemm: TFD_SEG_OUT_M needs an fp32 epilogue");
+  TFD_REQUIRE(seg_mode != TFD_SEG_OUT_M || mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32 ||
+                  mode == TFD_EPI_STORE_BF16,
+              "gemm: TFD_SEG_OUT_M needs a plain store epilogue (fp32, fp32 atomic or bf16)");
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
   p.kblocks = (K + BK - 1) / BK;

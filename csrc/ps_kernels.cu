@@ -35,7 +35,16 @@ struct AdamArgs {
   unsigned* queue;              // ring of qlen words: worker id + 1 once that worker's slot is complete, else 0
   int qlen;
   const unsigned* shutdown;     // non-zero: leave without applying (the ps is being released)
+  int slots_bf16;               // gradient slots hold bf16 (halves the push bytes); accumulation stays fp32
 };
+
+// four gradient values at element index i of a staging slot (fp32 or bf16 storage)
+__device__ __forceinline__ float4 load_grad4(const float* slot, long long i, int is_bf16) {
+  if (!is_bf16) return __ldcs(reinterpret_cast<const float4*>(slot + i));
+  const uint2 r = __ldcs(reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(slot) + i));
+  return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                     __uint_as_float(r.y & 0xffff0000u));
+}
 
 __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __grid_constant__ PieceTable pt) {
   grid_dep_wait();
@@ -91,12 +100,12 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
       w4[h] = __ldcs(reinterpret_cast<const float4*>(a.w + idx[h]));
       m4[h] = __ldcs(reinterpret_cast<const float4*>(a.m + idx[h]));
       v4[h] = __ldcs(reinterpret_cast<const float4*>(a.v + idx[h]));
-      g4[h] = __ldcs(reinterpret_cast<const float4*>(g0 + idx[h]));
+      g4[h] = load_grad4(g0, idx[h], a.slots_bf16);
     }
     for (int r = 1; r < nslots; ++r) {
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        const float4 x = __ldcs(reinterpret_cast<const float4*>(a.slots[r] + idx[h]));
+        const float4 x = load_grad4(a.slots[r], idx[h], a.slots_bf16);
         g4[h].x += x.x; g4[h].y += x.y; g4[h].z += x.z; g4[h].w += x.w;
       }
     }
@@ -177,6 +186,7 @@ struct PushTable {
   int qlen;                     // > 0 selects the async (ticket) protocol
   unsigned worker;              // this worker's index
   unsigned* my_ticket;          // async: local array [narrive]; receives ticket+1 = the version that serves it
+  int dst_bf16;                 // destination slots hold bf16
 };
 
 // grid (blocks_per_seg, nseg)
@@ -186,13 +196,17 @@ __global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushT
   grid_dep_launch();
   const PushSeg s = t.seg[blockIdx.y];
   const long long n4 = s.n >> 2;
+  bf16* dst16 = reinterpret_cast<bf16*>(s.dst);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     float4 x = *reinterpret_cast<const float4*>(s.src + (i << 2));
     x.x *= scale; x.y *= scale; x.z *= scale; x.w *= scale;
-    *reinterpret_cast<float4*>(s.dst + (i << 2)) = x;
+    if (t.dst_bf16) *reinterpret_cast<uint2*>(dst16 + (i << 2)) = make_uint2(pack_bf16x2(x.x, x.y), pack_bf16x2(x.z, x.w));
+    else *reinterpret_cast<float4*>(s.dst + (i << 2)) = x;
   }
-  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < s.n; i += (long long)gridDim.x * blockDim.x)
-    s.dst[i] = s.src[i] * scale;
+  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < s.n; i += (long long)gridDim.x * blockDim.x) {
+    if (t.dst_bf16) dst16[i] = __float2bfloat16(s.src[i] * scale);
+    else s.dst[i] = s.src[i] * scale;
+  }
   __threadfence_system();
   __syncthreads();
   // The last block to finish signals every shard.  One thread per shard, so the NVLink round trips of the
@@ -255,11 +269,18 @@ __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullT
 
 #define ST(s) static_cast<cudaStream_t>(s)
 
+// storage type of the gradient slots for the adam/push entry points (set once per shard by the runtime)
+static int g_next_slots_bf16 = 0;
+extern "C" int tfd_set_slot_dtype(int is_bf16) {
+  g_next_slots_bf16 = is_bf16 ? 1 : 0;
+  return 0;
+}
+
 static int adam_launch(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
                        float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
                        float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                        unsigned* version_flag, unsigned* global_step, unsigned* queue, int qlen,
-                       const unsigned* shutdown, void* stream) {
+                       const unsigned* shutdown, int slots_bf16, void* stream) {
   TFD_REQUIRE(n % 4 == 0, "adam: arena length %lld not a multiple of 4", n);
   TFD_REQUIRE(num_pieces <= kMaxPieces, "adam: too many pieces (%d)", num_pieces);
   TFD_REQUIRE(num_slots >= 1, "adam: need at least one gradient slot");
@@ -272,7 +293,7 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
   for (int i = 0; i < TFD_MAX_SLOTS; ++i) a.slots[i] = i < num_slots ? slots[i] : nullptr;
   a.num_slots = num_slots; a.scale = scale; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
   a.t_counter = t_counter; a.wait_counter = wait_counter; a.version_flag = version_flag; a.global_step = global_step;
-  a.queue = queue; a.qlen = qlen; a.shutdown = shutdown;
+  a.queue = queue; a.qlen = qlen; a.shutdown = shutdown; a.slots_bf16 = slots_bf16;
   long long blocks = (n / 8 + 255) / 256;
   if (blocks > 148 * 3) blocks = 148 * 3;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
   TFD_CUDA_CHECK(tfd_launch(adam_apply_kernel, dim3((unsigned)blocks), dim3(256), 0, ST(stream), a, pt));
@@ -285,7 +306,7 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
                               float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, stream);
+                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, stream);
 }
 
 extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
@@ -294,7 +315,7 @@ extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const 
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   TFD_REQUIRE(queue != nullptr && qlen >= num_slots, "adam_serve: ring of %d cells cannot hold %d workers", qlen, num_slots);
   return adam_launch(w, m, v, shadow, slots, num_slots, 1.0f, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     nullptr, version_flag, global_step, queue, qlen, shutdown, stream);
+                     nullptr, version_flag, global_step, queue, qlen, shutdown, g_next_slots_bf16, stream);
 }
 
 /* Multi-segment push: segs[i] = {src, dst, n}; after every segment is written the last block adds 1 to each
@@ -307,12 +328,12 @@ static int push_launch(const void* const* srcs, void* const* dsts, const long lo
   PushTable t;
   memset(&t, 0, sizeof(t));
   t.nseg = nseg; t.narrive = narrive;
-  t.qlen = qlen; t.worker = worker; t.my_ticket = my_ticket;
+  t.qlen = qlen; t.worker = worker; t.my_ticket = my_ticket; t.dst_bf16 = g_next_slots_bf16;
   for (int i = 0; i < narrive && queues; ++i) t.queue[i] = queues[i];
   long long maxn = 0;
   for (int i = 0; i < nseg; ++i) {
     t.seg[i] = PushSeg{static_cast<const float*>(srcs[i]), static_cast<float*>(dsts[i]), ns[i]};
-    TFD_REQUIRE(((uintptr_t)srcs[i] & 15) == 0 && ((uintptr_t)dsts[i] & 15) == 0, "push: segment %d not 16B aligned", i);
+    TFD_REQUIRE(((uintptr_t)srcs[i] & 15) == 0 && ((uintptr_t)dsts[i] & 7) == 0, "push: segment %d misaligned", i);
     if (ns[i] > maxn) maxn = ns[i];
   }
   for (int i = 0; i < narrive; ++i) t.arrive[i] = arrive[i];

@@ -162,6 +162,11 @@ int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const float* cons
                    float eps, unsigned* t_counter, const unsigned* wait_counter, unsigned* version_flag,
                    unsigned* global_step, void* stream);
 
+/* Storage type of the gradient staging slots used by tfd_adam_apply / tfd_adam_serve / tfd_push_multi[_async] from
+ * now on in this process: 0 = fp32 (default), 1 = bf16 (halves the bytes a push moves over NVLink; the shard still
+ * accumulates and applies in fp32).  The push-fused wgrad GEMM writes bf16 slots with TFD_EPI_STORE_BF16. */
+int tfd_set_slot_dtype(int is_bf16);
+
 /* Gradient push: copy (and scale) a worker's local fp32 gradient arena segment into its staging slot on the
  * owning shard (dst may be a peer pointer), then signal arrival: atomicAdd(arrive_counter, 1) at system scope
  * after a release fence, executed once by the last block. */

@@ -22,7 +22,8 @@ from tensorflow_distributed_b200.parallel.ps_gpu import GpuClusterEngine, Topolo
 
 
 def rel(a, b):
-    return (a.float() - b.float()).abs().max().item() / (b.float().abs().max().item() + 1e-20)
+    """Relative Frobenius error (robust against a single bf16-rounded outlier in a large tensor)."""
+    return (a.float() - b.float()).norm().item() / (b.float().norm().item() + 1e-20)
 
 
 def main():
@@ -35,6 +36,7 @@ def main():
     ap.add_argument("--steps", type=int, default=12)
     ap.add_argument("--async_mode", action="store_true")
     ap.add_argument("--pull", default="auto")
+    ap.add_argument("--grad_dtype", default="fp32")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -43,13 +45,14 @@ def main():
     spec = make_spec(a.model, a.hidden, a.layers)
     topo = Topology.make(world, a.layout, a.ps)
     eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05,
-                           async_mode=a.async_mode, pull_mode=a.pull)
+                           async_mode=a.async_mode, pull_mode=a.pull, grad_dtype=a.grad_dtype)
     B = 128
     keep = 1.0
     w = topo.worker_of(rank)
-    rng = np.random.RandomState(100 + (w if w is not None else 99))
-    xs = [rng.rand(B, 784).astype(np.float32) for _ in range(a.steps)]
-    ys = [np.eye(10, dtype=np.float32)[rng.randint(0, 10, size=B)] for _ in range(a.steps)]
+    from tensorflow_distributed_b200 import data
+    stream = data.read_data_sets("", synthetic=True, seed=100 + (w if w is not None else 99)).train
+    batches = [stream.next_batch(B) for _ in range(a.steps)]  # learnable synthetic digits, one stream per worker
+    xs, ys = [b[0] for b in batches], [b[1] for b in batches]
     p0 = eng.get_params()
     dist.barrier()
     # ---- step 1 (eager) ----
@@ -63,14 +66,13 @@ def main():
                    else v) for k, v in p0.items()}
         slots = [eng.get_slot_grads(i) for i in range(topo.num_workers)]
         for i in range(topo.num_workers):
-            r2 = np.random.RandomState(100 + i)
-            x = torch.from_numpy([r2.rand(B, 784).astype(np.float32) for _ in range(a.steps)][0])
-            y = torch.from_numpy(np.eye(10, dtype=np.float32)[r2.randint(0, 10, size=B)])
+            bx, by = data.read_data_sets("", synthetic=True, seed=100 + i).train.next_batch(B)
+            x, y = torch.from_numpy(bx), torch.from_numpy(by)
             xin = x.to(torch.bfloat16).float() if a.model == "mlp" else x
             _, og, _ = oracle.loss_and_grads(a.model, xin, y, p0r)
             for k in og:
                 e = rel(slots[i][k], og[k])
-                if e > 0.1:
+                if e > 0.08:
                     ok = False
                     msgs.append("worker %d grad %s rel err %.3f" % (i, k, e))
         avg = {k: sum(s[k] for s in slots) / topo.num_workers for k in slots[0]}
@@ -78,7 +80,7 @@ def main():
         oracle.TFAdam(0.01).apply(ref, avg)
         p1 = eng.get_params()
         for k in ref:
-            if not torch.allclose(p1[k], ref[k], atol=2e-5, rtol=1e-4):
+            if not torch.allclose(p1[k], ref[k], atol=2e-5 if a.grad_dtype == "fp32" else 2e-4, rtol=1e-4):
                 ok = False
                 msgs.append("adam mismatch %s max diff %.3e" % (k, (p1[k] - ref[k]).abs().max().item()))
         if eng.global_step != 1:
@@ -88,7 +90,7 @@ def main():
     # ---- more steps (second is eager warm-up of the graph path, then captured graphs) ----
     losses = [l1]
     for s in range(1, a.steps):
-        losses.append(eng.train_step(xs[s % 4], ys[s % 4], keep, fetch_loss=True))
+        losses.append(eng.train_step(xs[s], ys[s], keep, fetch_loss=True))
     torch.cuda.synchronize()
     dist.barrier()
     gs = eng.global_step

@@ -152,6 +152,7 @@ class NativeEngine:
         self.device = torch.device(device or ("cuda:%d" % torch.cuda.current_device()))
         torch.cuda.set_device(self.device)
         nat.set_device(self.device.index or 0)
+        nat.set_slot_dtype(False)
         self.lr, self.seed = learning_rate, seed
         self.use_graphs, self.conv2_ref = use_graphs, conv2_ref
         self.placement = Placement(spec, 1)
@@ -323,13 +324,21 @@ class NativeEngine:
         H = dims[L]
         nat.head_cols(ws.act[L], ws.dact[L], _pad8(H), ws.dlogits, ws.loss_row, ws.hit, B, H, self.G("weights/out"),
                       self.G("biases/b%d" % L), self.G("biases/out"), ws.scalars)
+        # wgrad_l only needs dact[l] and act[l-1]; it runs on a side stream (a graph branch) while the main stream
+        # continues with dgrad_l.  On a multi-GPU run that also overlaps the two NVLink directions: wgrad pushes
+        # (egress) while dgrad pulls (ingress).
+        main = torch.cuda.current_stream()
+        s1 = self._side_streams()[0]
         for l in range(L, 0, -1):
             H, K = dims[l], dims[l - 1]
-            self.gemm_wgrad("weights/h%d" % l, ws.act[l - 1], ws.dact[l], B, bn=128 if H >= 128 else 64)
+            s1.wait_stream(main)
+            with torch.cuda.stream(s1):
+                self.gemm_wgrad("weights/h%d" % l, ws.act[l - 1], ws.dact[l], B, bn=128 if H >= 128 else 64)
             if l > 1:
                 self.gemm_dgrad("weights/h%d" % l, ws.dact[l], B, ws.dact[l - 1], mode=nat.EPI_RELUMASK_BF16, bn=64,
                                 relu_mask=ws.act[l - 1])
                 nat.colsum_bf16(ws.dact[l - 1], _pad8(K), B, K, self.G("biases/b%d" % (l - 1)))
+        main.wait_stream(s1)
 
     def _apply(self) -> None:
         s = self.shard

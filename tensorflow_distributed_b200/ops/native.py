@@ -80,6 +80,10 @@ def set_device(dev: int) -> None:
     _check(lib().tfd_set_device(c_int(dev)), "tfd_set_device")
 
 
+def set_slot_dtype(is_bf16: bool) -> None:
+    _check(lib().tfd_set_slot_dtype(c_int(int(is_bf16))), "tfd_set_slot_dtype")
+
+
 def device_info(dev: int = 0) -> dict:
     sm, maj, mnr, sm_opt = c_int(), c_int(), c_int(), c_size_t()
     _check(lib().tfd_device_info(c_int(dev), ctypes.byref(sm), ctypes.byref(maj), ctypes.byref(mnr),

@@ -89,7 +89,9 @@ def _al(n: int, a: int = 1024) -> int:
 class HeapLayout:
     """Byte offsets inside one rank's peer-mapped allocation.  Identical arithmetic on every rank."""
 
-    def __init__(self, spec: ModelSpec, placement: Placement, shard: Optional[int], num_workers: int):
+    def __init__(self, spec: ModelSpec, placement: Placement, shard: Optional[int], num_workers: int,
+                 grad_bytes: int = 4):
+        self.grad_bytes = grad_bytes
         off = 0
         self.ctrl = off; off += 1024
         self.n = self.shadow_n = 0
@@ -101,8 +103,8 @@ class HeapLayout:
             self.m = off; off += _al(self.n * 4)
             self.v = off; off += _al(self.n * 4)
             self.shadow = off; off += _al(self.shadow_n * 2)
-            self.slots = off; off += num_workers * _al(self.n * 4)
-        self.slot_stride = _al(self.n * 4)
+            self.slots = off; off += num_workers * _al(self.n * grad_bytes)
+        self.slot_stride = _al(self.n * grad_bytes)
         self.total = max(off, 4096)
 
     def slot(self, worker: int) -> int:
@@ -116,7 +118,11 @@ class GpuClusterEngine(NativeEngine):
 
     def __init__(self, spec: ModelSpec, topo: Topology, rank: int, device, learning_rate: float = 0.01,
                  seed: int = 0, init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False,
-                 async_mode: bool = False, pull_mode: str = "auto", prefetch_max_numel: int = 8 << 20):
+                 async_mode: bool = False, pull_mode: str = "auto", prefetch_max_numel: int = 8 << 20,
+                 grad_dtype: str = "fp32"):
+        if grad_dtype not in ("fp32", "bf16"):
+            raise ValueError("grad_dtype must be fp32 or bf16")
+        self.grad_dtype, self.grad_bytes = grad_dtype, (2 if grad_dtype == "bf16" else 4)
         self.pull_mode, self.prefetch_max_numel = pull_mode, prefetch_max_numel
         if async_mode and topo.layout != "dedicated":
             # A colocated rank runs its worker kernels and its shard's apply in ONE in-order stream.  With
@@ -141,7 +147,9 @@ class GpuClusterEngine(NativeEngine):
         self.num_workers = topo.num_workers
         S = topo.num_shards
         self.placement = Placement(spec, S)
-        self.layouts = [HeapLayout(spec, self.placement, topo.shard_of(r), topo.num_workers) for r in range(topo.world)]
+        self.layouts = [HeapLayout(spec, self.placement, topo.shard_of(r), topo.num_workers, self.grad_bytes)
+                        for r in range(topo.world)]
+        nat.set_slot_dtype(self.grad_dtype == "bf16")
         # ---- symmetric heap: allocate, exchange the 64-byte cudaIpc handles, map every ps rank's heap ----
         self.heap_ptr, handle = nat.ipc_alloc(self.layouts[rank].total)
         handles: List[Optional[bytes]] = [None] * topo.world
@@ -197,7 +205,7 @@ class GpuClusterEngine(NativeEngine):
 
     def _slot_ptr(self, shard: int, elem_off: int) -> int:
         r = self._ps_rank(shard)
-        return self.peer_base[r] + self.layouts[r].slot(self.my_worker) + 4 * elem_off
+        return self.peer_base[r] + self.layouts[r].slot(self.my_worker) + self.grad_bytes * elem_off
 
     def _build_worker_tables(self) -> None:
         dev = self.device
@@ -289,8 +297,9 @@ class GpuClusterEngine(NativeEngine):
         d = self._direct_info[wname]
         nseg = len(d["slot"])
         nat.gemm_bf16_seg(X, 1, [dY.data_ptr()] + [0] * (nseg - 1), 1, d["rows"][-1], d["cols"], Bsz, None,
-                          mode=nat.EPI_STORE_F32, lda=X.stride(0), ldb=dY.stride(0), ld_out=d["cols"],
-                          seg_mode=nat.SEG_OUT_M, seg_rows=d["rows"], out_ptrs=d["slot"], bn=bn)
+                          mode=nat.EPI_STORE_BF16 if self.grad_dtype == "bf16" else nat.EPI_STORE_F32, lda=X.stride(0),
+                          ldb=dY.stride(0), ld_out=d["cols"], seg_mode=nat.SEG_OUT_M, seg_rows=d["rows"],
+                          out_ptrs=d["slot"], bn=bn)
 
     # ---- step pieces -----------------------------------------------------------------------
     def _pre_step(self, ws, training: bool) -> None:
@@ -379,7 +388,8 @@ class GpuClusterEngine(NativeEngine):
         return int(t.item())
 
     def describe(self) -> str:
-        return self.topo.describe() + (" async" if self.async_mode else " sync")
+        return self.topo.describe() + (" async" if self.async_mode else " sync") + \
+            (" bf16-grad-push" if self.grad_dtype == "bf16" else "")
 
     def _read_arena(self, which: str) -> Dict[str, torch.Tensor]:
         """Gather a full name->tensor dict by reading every shard's arena through the peer mapping."""
@@ -415,8 +425,9 @@ class GpuClusterEngine(NativeEngine):
             parts = []
             for p in sorted(self.placement.pieces[v.name], key=lambda q: q.row_start):
                 r = self._ps_rank(p.shard)
-                base = self.peer_base[r] + self.layouts[r].slot(worker) + 4 * p.offset
-                parts.append(nat.tensor_from_ptr(base, p.numel, torch.float32, self.device).cpu()
+                base = self.peer_base[r] + self.layouts[r].slot(worker) + self.grad_bytes * p.offset
+                dt = torch.bfloat16 if self.grad_dtype == "bf16" else torch.float32
+                parts.append(nat.tensor_from_ptr(base, p.numel, dt, self.device).float().cpu()
                              .view(p.row_end - p.row_start, p.cols))
             out[v.name] = torch.cat(parts, 0).reshape(v.shape).clone()
         return out
@@ -445,7 +456,8 @@ class GpuClusterEngine(NativeEngine):
     def from_bench_args(cls, spec, a, rank: int, world: int, device) -> "GpuClusterEngine":
         topo = Topology.make(world, a.layout, a.ps)
         return cls(spec, topo, rank, device, learning_rate=0.01, seed=0, init_stddev=a.init_stddev,
-                   async_mode=getattr(a, "async_mode", False), pull_mode=getattr(a, "pull", "auto"))
+                   async_mode=getattr(a, "async_mode", False), pull_mode=getattr(a, "pull", "auto"),
+                   grad_dtype=getattr(a, "grad_dtype", "fp32"))
 
     # ---- restore / release helpers used by the cluster program -------------------------------
     def set_adam_state(self, sd: dict) -> None:
@@ -521,7 +533,8 @@ def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
         log("Worker %d: %s" % (flags.task_index, "Initializing session..." if is_chief
                                else "Waiting for session to be initialized..."))
     eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
-                           init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas)
+                           init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas,
+                           grad_dtype=flags.grad_dtype)
     if flags.log_device_placement and (is_chief or flags.job_name == "ps"):
         log(eng.placement.table())
     sv = Supervisor(is_chief, spec, flags.train_dir, recovery_wait_secs=1.0, log=log)

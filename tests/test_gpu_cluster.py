@@ -84,3 +84,10 @@ def test_gpu_cluster_scripts_async(tmp_path):
     n = w1.count(": training step") + w2.count(": training step")
     assert n >= 6  # global_step counts worker updates (m:301)
     assert "Mean Accuracy :" in w1 and "Mean Accuracy :" in w2
+
+
+@needs2
+@pytest.mark.parametrize("model", ["cnn", "mlp"])
+def test_two_gpu_bf16_gradient_push(model):
+    out = _torchrun(2, ["--layout", "colocated", "--model", model, "--grad_dtype", "bf16"], 29615)
+    assert "OK" in out and "FAIL" not in out and "bf16-grad-push" in out
