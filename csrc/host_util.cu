@@ -1,6 +1,7 @@
 // Host utilities: error string, TMA tensor-map construction, device info.
 #include <stdarg.h>
 #include <stdlib.h>
+#include <set>
 #include <string.h>
 
 #include "../include/tfd_b200.h"
@@ -114,4 +115,22 @@ int tfd_pdl_enabled() {
 extern "C" int tfd_set_pdl(int on) {
   g_pdl = on ? 1 : 0;
   return 0;
+}
+
+void tfd_prefer_max_smem(const void* kernel) {
+  static std::set<const void*> done;
+  if (done.count(kernel)) return;
+  done.insert(kernel);
+  if (cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) !=
+      cudaSuccess)
+    cudaGetLastError();  // a hint only: never fail a launch over it
+}
+
+int tfd_uniform_carveout() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TFD_CARVEOUT");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v;
 }

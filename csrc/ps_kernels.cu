@@ -36,6 +36,8 @@ struct AdamArgs {
   int qlen;
   const unsigned* shutdown;     // non-zero: leave without applying (the ps is being released)
   int slots_bf16;               // gradient slots hold bf16 (halves the push bytes); accumulation stays fp32
+  long long skip_begin, skip_end;  // elements [skip_begin, skip_end) are left alone (updated by an earlier launch)
+  int finalize;                 // 1: bump t / global_step and publish the version; 0: partial launch of this step
 };
 
 // four gradient values at element index i of a staging slot (fp32 or bf16 storage)
@@ -85,14 +87,17 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   const float lr_t = a.lr * sqrtf(om_b2t) / om_b1t;
   // Two float4 groups per thread per iteration, one block-stride apart (every warp instruction touches 512
   // contiguous bytes); all eight streaming loads are issued before the first use (memory-level parallelism).
-  const long long n4 = a.n >> 2;
+  // index space = the arena minus the skipped range (already updated by the early launch of this step)
+  const long long skip4 = (a.skip_end - a.skip_begin) >> 2, skipb4 = a.skip_begin >> 2;
+  const long long n4 = (a.n >> 2) - skip4;
   const long long stride4 = (long long)gridDim.x * blockDim.x;
   const float* g0 = serve_slot ? serve_slot : a.slots[0];
   const int nslots = serve_slot ? 1 : a.num_slots;
   int cur = 0;  // cached piece index for the shadow lookup
   for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += 2 * stride4) {
-    long long idx[2] = {i4 << 2, (i4 + stride4) << 2};
-    const bool ok1 = (i4 + stride4) < n4;
+    const long long j0 = i4, j1 = i4 + stride4;
+    long long idx[2] = {(j0 < skipb4 ? j0 : j0 + skip4) << 2, (j1 < skipb4 ? j1 : j1 + skip4) << 2};
+    const bool ok0 = true, ok1 = j1 < n4;
     if (!ok1) idx[1] = idx[0];
     float4 w4[2], m4[2], v4[2], g4[2];
 #pragma unroll
@@ -111,7 +116,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
     }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      if (h == 1 && !ok1) break;
+      if ((h == 1 && !ok1) || (h == 0 && !ok0)) continue;
       float wv[4] = {w4[h].x, w4[h].y, w4[h].z, w4[h].w}, mv[4] = {m4[h].x, m4[h].y, m4[h].z, m4[h].w};
       float vv[4] = {v4[h].x, v4[h].y, v4[h].z, v4[h].w};
       const float gv[4] = {g4[h].x * a.scale, g4[h].y * a.scale, g4[h].z * a.scale, g4[h].w * a.scale};
@@ -163,6 +168,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
     const unsigned done = atomicAdd(&a.t_counter[1], 1u);
     if (done == gridDim.x - 1) {
       a.t_counter[1] = 0;
+      if (!a.finalize) return;
       a.t_counter[0] = t;
       if (a.queue) a.queue[(t - 1) % (unsigned)a.qlen] = 0;
       if (a.global_step) *a.global_step = *a.global_step + 1;
@@ -280,8 +286,10 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
                        float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
                        float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                        unsigned* version_flag, unsigned* global_step, unsigned* queue, int qlen,
-                       const unsigned* shutdown, int slots_bf16, void* stream) {
-  TFD_REQUIRE(n % 4 == 0, "adam: arena length %lld not a multiple of 4", n);
+                       const unsigned* shutdown, int slots_bf16, long long skip_begin, long long skip_end, int finalize,
+                       void* stream) {
+  TFD_REQUIRE(n % 4 == 0 && skip_begin % 4 == 0 && skip_end % 4 == 0 && skip_begin <= skip_end && skip_end <= n,
+              "adam: arena length %lld / skip range [%lld,%lld) must be multiples of 4 and nested", n, skip_begin, skip_end);
   TFD_REQUIRE(num_pieces <= kMaxPieces, "adam: too many pieces (%d)", num_pieces);
   TFD_REQUIRE(num_slots >= 1, "adam: need at least one gradient slot");
   PieceTable pt;
@@ -294,8 +302,12 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
   a.num_slots = num_slots; a.scale = scale; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
   a.t_counter = t_counter; a.wait_counter = wait_counter; a.version_flag = version_flag; a.global_step = global_step;
   a.queue = queue; a.qlen = qlen; a.shutdown = shutdown; a.slots_bf16 = slots_bf16;
-  long long blocks = (n / 8 + 255) / 256;
-  if (blocks > 148 * 3) blocks = 148 * 3;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
+  a.skip_begin = skip_begin; a.skip_end = skip_end; a.finalize = finalize;
+  long long blocks = ((n - (skip_end - skip_begin)) / 8 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  // finalize == 0: the early launch runs next to tcgen05 kernels; two blocks per SM leave them the registers
+  const long long cap = finalize ? 148 * 3 : 148 * 2;
+  if (blocks > cap) blocks = cap;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
   TFD_CUDA_CHECK(tfd_launch(adam_apply_kernel, dim3((unsigned)blocks), dim3(256), 0, ST(stream), a, pt));
   TFD_LAUNCH_CHECK();
   return 0;
@@ -306,7 +318,21 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
                               float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, stream);
+                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, 0, 0, 1, stream);
+}
+
+/* Partial form: update only part of the arena now and the rest later in the same step, so the Adam pass over a big
+ * tensor can start as soon as ITS gradient is complete and run under the rest of the backward pass.
+ *   early launch:  base pointers offset to the tensor, n = its length, finalize = 0   (uses t+1, publishes nothing)
+ *   last launch:   whole arena, [skip_begin, skip_end) = the range already done, finalize = 1 */
+extern "C" int tfd_adam_apply_part(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
+                                   float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr,
+                                   float beta1, float beta2, float eps, unsigned* t_counter,
+                                   const unsigned* wait_counter, unsigned* version_flag, unsigned* global_step,
+                                   long long skip_begin, long long skip_end, int finalize, void* stream) {
+  return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
+                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, skip_begin,
+                     skip_end, finalize, stream);
 }
 
 extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
@@ -315,7 +341,7 @@ extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const 
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   TFD_REQUIRE(queue != nullptr && qlen >= num_slots, "adam_serve: ring of %d cells cannot hold %d workers", qlen, num_slots);
   return adam_launch(w, m, v, shadow, slots, num_slots, 1.0f, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     nullptr, version_flag, global_step, queue, qlen, shutdown, g_next_slots_bf16, stream);
+                     nullptr, version_flag, global_step, queue, qlen, shutdown, g_next_slots_bf16, 0, 0, 1, stream);
 }
 
 /* Multi-segment push: segs[i] = {src, dst, n}; after every segment is written the last block adds 1 to each

@@ -162,6 +162,15 @@ int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const float* cons
                    float eps, unsigned* t_counter, const unsigned* wait_counter, unsigned* version_flag,
                    unsigned* global_step, void* stream);
 
+/* tfd_adam_apply in two launches per step: an early one over one big tensor (finalize = 0; pass w/m/v/slots already
+ * offset to the tensor, pieces with arena_off relative to that base) and a last one over the whole arena that skips
+ * [skip_begin, skip_end) and finalises (bumps t / global_step, publishes the version). */
+int tfd_adam_apply_part(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
+                        float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
+                        float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
+                        unsigned* version_flag, unsigned* global_step, long long skip_begin, long long skip_end,
+                        int finalize, void* stream);
+
 /* Storage type of the gradient staging slots used by tfd_adam_apply / tfd_adam_serve / tfd_push_multi[_async] from
  * now on in this process: 0 = fp32 (default), 1 = bf16 (halves the bytes a push moves over NVLink; the shard still
  * accumulates and applies in fp32).  The push-fused wgrad GEMM writes bf16 slots with TFD_EPI_STORE_BF16. */

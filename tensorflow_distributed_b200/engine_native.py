@@ -142,9 +142,11 @@ class NativeEngine:
     """Single-GPU engine: parameters live in one ShardState on the same device as the worker kernels."""
 
     name = "native-sm100a"
+    early_adam_var: Optional[str] = None  # big tensor whose Adam pass is launched early, under the rest of backward
 
     def __init__(self, spec: ModelSpec, learning_rate: float = 0.01, seed: int = 0, init_stddev: float = 1.0,
-                 device: Optional[str] = None, use_graphs: bool = True, conv2_ref: bool = False):
+                 device: Optional[str] = None, use_graphs: bool = True, conv2_ref: bool = False,
+                 early_adam: bool = False):
         if not torch.cuda.is_available():
             raise nat.NativeError("NativeEngine needs a CUDA device (backend=cpu selects the oracle engine)")
         nat.lib()
@@ -160,6 +162,9 @@ class NativeEngine:
         self.grad = torch.zeros(self.shard.n, dtype=torch.float32, device=self.device)
         self.slot_ptrs = [self.grad.data_ptr()]
         self.ws: Dict[int, Workspace] = {}
+        # Launching wd1's Adam pass early (under the conv backward chain) was measured: the step stays at ~0.120 ms
+        # because the overlapped kernels then contend for registers / DRAM (profiles/ANALYSIS.md); off by default.
+        self.early_adam_var = "weights/wd1" if (spec.kind == "cnn" and early_adam) else None
         self.init_variables(seed, init_stddev)
 
     # ---- variables -------------------------------------------------------------------------
@@ -295,6 +300,12 @@ class NativeEngine:
         # fc1 dgrad: dpool2[B,3136] = dhid wd1^T    (wd1 read K-major in place)
         self.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
                         split_stride=B * 3136, ld_out=3136)
+        if self.early_adam_var == "weights/wd1" and self._training_apply:
+            # wd1 is 98% of the parameter bytes: its Adam pass starts as soon as its gradient is complete (and the
+            # dgrad above has read the old weights) and runs under pool2-bwd / conv2-dgrad / conv1-wgrad
+            s1.wait_stream(main)
+            with torch.cuda.stream(s1):
+                self._apply_early("weights/wd1")
         main.wait_stream(s2)  # the zeroed accumulators
         nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"), B, nsplit=ws.dg_splits,
                       split_stride=B * 3136)
@@ -340,13 +351,28 @@ class NativeEngine:
                 nat.colsum_bf16(ws.dact[l - 1], _pad8(K), B, K, self.G("biases/b%d" % (l - 1)))
         main.wait_stream(s1)
 
+    _training_apply = False  # set by _sequence: True only when this step ends with an apply ("train" mode)
+
+    def _apply_early(self, var: str) -> None:
+        s = self.shard
+        p = s.piece_of(var)
+        o, n = p.offset, p.numel
+        piece = nat.Piece(0, n, p.cols, s.shadow_ld.get(var, 0), s.shadow_off.get(var, 0))
+        nat.adam_apply_part(s.w[o:], s.m[o:], s.v[o:], s.shadow, [self.grad.data_ptr() + 4 * o], 1, 1.0, n, [piece],
+                            self.lr, s.ctrl[CTRL_T:], 0, 0, False)
+
     def _apply(self) -> None:
         s = self.shard
-        nat.adam_apply(s.w, s.m, s.v, s.shadow, self.slot_ptrs, 1, 1.0, s.n, s.pieces, self.lr, s.ctrl[CTRL_T:], None,
-                       s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:])
+        skip = (0, 0)
+        if self.early_adam_var is not None:
+            p = s.piece_of(self.early_adam_var)
+            skip = (p.offset, p.offset + p.numel)
+        nat.adam_apply_part(s.w, s.m, s.v, s.shadow, self.slot_ptrs, 1, 1.0, s.n, s.pieces, self.lr, s.ctrl[CTRL_T:],
+                            skip[0], skip[1], True, None, s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:])
 
     def _sequence(self, ws: Workspace, mode: str, keep_prob: float, mask_out=None) -> None:
         training = mode in ("train", "grads")
+        self._training_apply = (mode == "train")
         self._pre_step(ws, training)
         if self.spec.kind == "cnn":
             self._cnn_forward(ws, training, keep_prob, mask_out)

@@ -229,6 +229,19 @@ def adam_apply(w, m, v, shadow, slots_dev, num_slots: int, scale: float, n: int,
     _count()
 
 
+def adam_apply_part(w, m, v, shadow, slots, num_slots: int, scale: float, n: int, pieces, lr: float, t_counter,
+                    skip_begin: int, skip_end: int, finalize: bool, wait_counter=None, version_flag=None,
+                    global_step=None, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8) -> None:
+    arr = (Piece * max(1, len(pieces)))(*pieces)
+    sl = (c_void_p * num_slots)(*[c_void_p(int(x)) for x in slots[:num_slots]])
+    _check(lib().tfd_adam_apply_part(_p(w), _p(m), _p(v), _p(shadow), sl, c_int(num_slots), c_float(scale), c_longlong(n),
+                                     arr, c_int(len(pieces)), c_float(lr), c_float(beta1), c_float(beta2), c_float(eps),
+                                     _p(t_counter), _p(wait_counter), _p(version_flag), _p(global_step),
+                                     c_longlong(skip_begin), c_longlong(skip_end), c_int(int(finalize)), _stream()),
+           "tfd_adam_apply_part")
+    _count()
+
+
 def push_multi(srcs, dsts, ns, arrive, scale: float, block_counter, local_step=None) -> None:
     n = len(srcs)
     S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])

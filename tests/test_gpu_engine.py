@@ -115,3 +115,19 @@ def test_run_single_on_gpu_prints_reference_lines():
     assert out["steps"] == 31 and out["engine"].name == "native-sm100a"
     assert sum(l.startswith("Iter ") for l in lines) == 3 and "Optimization Finished!" in lines
     assert out["mean_accuracy"] > 0.5
+
+
+def test_early_adam_launch_matches_single_launch():
+    """Adam split into an early launch for wd1 and a finalising launch for the rest gives the same update."""
+    spec = cnn_spec()
+    x, y = _batch(128, 6)
+    outs = []
+    for early in (False, True):
+        eng = _engine(spec, init_stddev=0.05, seed=6, use_graphs=False, early_adam=early)
+        eng.train_step(x, y, 1.0)
+        eng.train_step(x, y, 1.0)
+        outs.append((eng.get_params(), eng.global_step, eng.get_adam_state()["t"]))
+    assert outs[0][1] == outs[1][1] == 2 and outs[0][2] == outs[1][2] == 2
+    for k in outs[0][0]:
+        d = (outs[0][0][k] - outs[1][0][k]).abs()
+        assert d.mean().item() < 1e-4 and (d > 2e-2).float().mean().item() < 1e-3, k
