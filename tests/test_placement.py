@@ -27,7 +27,7 @@ def test_sharded_placement_splits_wd1_on_k_blocks():
             assert r0 % 128 == 0
         if S > 1:
             sizes = [r1 - r0 for _, r0, r1 in rows]
-            assert max(sizes) - min(sizes) <= 128
+            assert max(sizes) - min(sizes) < 2 * 128  # one 128-row block, plus a ragged last block
         for p in pl.shard_pieces(0):
             assert p.offset % 64 == 0
         assert "weights/wd1" in pl.table()
