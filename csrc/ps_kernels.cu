@@ -196,7 +196,7 @@ struct PushTable {
 };
 
 // grid (blocks_per_seg, nseg)
-__global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushTable t, float scale, unsigned* block_counter,
+__global__ void __launch_bounds__(1024) push_kernel(const __grid_constant__ PushTable t, float scale, unsigned* block_counter,
                                                    unsigned* local_step) {
   grid_dep_wait();
   grid_dep_launch();
@@ -221,10 +221,8 @@ __global__ void __launch_bounds__(256) push_kernel(const __grid_constant__ PushT
   if (threadIdx.x == 0) {
     const unsigned total = gridDim.x * gridDim.y;
     s_last = (atomicAdd(block_counter, 1u) == total - 1) ? 1u : 0u;
-    if (s_last) {
-      *block_counter = 0;
-      __threadfence_system();
-    }
+    if (s_last) *block_counter = 0;  // (every block fenced at system scope before its increment; the release
+                                      //  operations below are cumulative over what this thread has observed)
   }
   __syncthreads();
   if (!s_last) return;
@@ -264,11 +262,21 @@ __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullT
     if (threadIdx.x == 0) spin_until_ge(s.version, s.want_seg ? *s.want_seg : want, "pull: parameter version");
     __syncthreads();
   }
+  // peer reads are latency-bound (~2 us per round trip): four independent 16-byte loads in flight per thread
   const long long n4 = s.n >> 2;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x)
-    *reinterpret_cast<float4*>(s.dst + (i << 2)) = *reinterpret_cast<const float4*>(s.src + (i << 2));
-  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < s.n; i += (long long)gridDim.x * blockDim.x)
-    s.dst[i] = s.src[i];
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const float4* src4 = reinterpret_cast<const float4*>(s.src);
+  float4* dst4 = reinterpret_cast<float4*>(s.dst);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += 4 * stride) {
+    float4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (i + k * stride < n4) v[k] = __ldcs(src4 + i + k * stride);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (i + k * stride < n4) dst4[i + k * stride] = v[k];
+  }
+  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < s.n; i += stride) s.dst[i] = s.src[i];
 }
 
 }  // namespace
@@ -363,10 +371,12 @@ static int push_launch(const void* const* srcs, void* const* dsts, const long lo
     if (ns[i] > maxn) maxn = ns[i];
   }
   for (int i = 0; i < narrive; ++i) t.arrive[i] = arrive[i];
-  long long bx = (maxn / 4 + 255) / 256;
+  // Few, fat blocks: every block ends with a system-scope fence (an NVLink round trip when the slot is on a peer),
+  // so a handful of 1024-thread blocks per segment beats hundreds of small ones for these sub-MB payloads.
+  long long bx = (maxn / 4 + 4095) / 4096;
   if (bx < 1) bx = 1;
-  if (bx > 148) bx = 148;
-  TFD_CUDA_CHECK(tfd_launch(push_kernel, dim3((unsigned)bx, nseg), dim3(256), 0, ST(stream), t, scale, block_counter, local_step));
+  if (bx > 32) bx = 32;
+  TFD_CUDA_CHECK(tfd_launch(push_kernel, dim3((unsigned)bx, nseg), dim3(1024), 0, ST(stream), t, scale, block_counter, local_step));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -408,9 +418,9 @@ static int pull_launch(const void* const* srcs, void* const* dsts, const long lo
                         want_segs ? want_segs[i] : nullptr};
     if (ns[i] > maxn) maxn = ns[i];
   }
-  long long bx = (maxn / 4 + 255) / 256;
+  long long bx = (maxn / 4 + 1023) / 1024;  // ~4 float4 per thread
   if (bx < 1) bx = 1;
-  if (bx > 64) bx = 64;
+  if (bx > 148) bx = 148;
   TFD_CUDA_CHECK(tfd_launch(pull_kernel, dim3((unsigned)bx, nseg), dim3(256), 0, ST(stream), t, want_version, want_ptr));
   TFD_LAUNCH_CHECK();
   return 0;

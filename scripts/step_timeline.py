@@ -12,8 +12,19 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from tensorflow_distributed_b200.engine_native import NativeEngine  # noqa: E402
 from tensorflow_distributed_b200.models.spec import cnn_spec  # noqa: E402
 
-eng = NativeEngine(cnn_spec(), init_stddev=1.0)
-rng = np.random.RandomState(0)
+world = int(os.environ.get("WORLD_SIZE", "1"))
+rank = int(os.environ.get("RANK", "0"))
+if world > 1:  # under torchrun: colocated ps shards, one rank per GPU; rank 0 prints its own timeline
+    import torch.distributed as dist
+    from tensorflow_distributed_b200.parallel.ps_gpu import GpuClusterEngine, Topology
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local))
+    eng = GpuClusterEngine(cnn_spec(), Topology.make(world, os.environ.get("TFD_LAYOUT", "colocated")), rank,
+                           "cuda:%d" % local, init_stddev=1.0, pull_mode=os.environ.get("TFD_PULL", "auto"))
+else:
+    eng = NativeEngine(cnn_spec(), init_stddev=1.0)
+rng = np.random.RandomState(rank)
 x = rng.rand(128, 784).astype(np.float32)
 y = np.eye(10, dtype=np.float32)[rng.randint(0, 10, size=128)]
 ws = eng.workspace(128)
@@ -27,6 +38,11 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
         flush.fill_(1.0)
         eng.train_step_resident(ws, 0.75)
     torch.cuda.synchronize()
+if world > 1:
+    dist.barrier()
+if rank != 0:
+    eng.shutdown()
+    sys.exit(0)
 out = os.path.join("gpurun_out", "step_trace.json")
 prof.export_chrome_trace(out)
 ev = [e for e in json.load(open(out))["traceEvents"] if e.get("cat") == "kernel"]
@@ -40,3 +56,5 @@ for e in step:
     name = e["name"].replace("(anonymous namespace)::", "").split("(")[0][:52]
     print("%-52s %6s %8.1f %8.1f %8.1f" % (name, e["args"].get("stream", "?"), e["ts"] - t0, e["ts"] + e["dur"] - t0, e["dur"]))
 print("step span: %.1f us" % (step[-1]["ts"] + step[-1]["dur"] - t0))
+if world > 1:
+    eng.shutdown()

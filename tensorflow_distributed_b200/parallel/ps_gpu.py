@@ -177,11 +177,12 @@ class GpuClusterEngine(NativeEngine):
         # there are two strategies: "fused" -- forward and dgrad GEMMs TMA-load B from the owner GPUs (bandwidth-bound
         # layers: 97% of the NVLink roofline on 8192x8192); "prefetch" -- a few-MB matrix such as the CNN's wd1 is
         # copied once per step on a side stream *under* the conv layers and both GEMMs read the local copy, which
-        # takes two latency-bound NVLink reads off the critical path.  Measured on 2 GPUs the fused
-        # pull is the faster one even for wd1 (156 vs 166 us/step), so "auto" = fused; "prefetch" stays selectable.
+        # takes two latency-bound NVLink reads off the critical path (2 GPUs: 154.9 vs 157.7 us/step;
+        # 1 ps + 7 workers: 222 vs 317 us/step).  "auto" therefore prefetches matrices up to prefetch_max_numel
+        # elements and fuses the pull of everything bigger; "fused" / "prefetch" force one strategy.
         self.direct = {v.name for v in spec.variables if needs_shadow(spec, v.name) and v.numel >= DIRECT_THRESHOLD}
         self.prefetched = {n for n in self.direct
-                           if pull_mode == "prefetch" and spec.by_name()[n].numel <= prefetch_max_numel}
+                           if pull_mode in ("prefetch", "auto") and spec.by_name()[n].numel <= prefetch_max_numel}
         if self.is_worker:
             self._build_worker_tables()
         torch.cuda.synchronize(self.device)
