@@ -131,3 +131,27 @@ def test_early_adam_launch_matches_single_launch():
     for k in outs[0][0]:
         d = (outs[0][0][k] - outs[1][0][k]).abs()
         assert d.mean().item() < 1e-4 and (d > 2e-2).float().mean().item() < 1e-3, k
+
+
+def test_checkpoint_resume_gives_the_same_next_step(tmp_path):
+    """save -> (process would die here) -> restore into a fresh engine -> identical next step."""
+    from tensorflow_distributed_b200 import checkpoint
+    spec = cnn_spec()
+    x, y = _batch(128, 7)
+    a = _engine(spec, init_stddev=0.05, seed=7, use_graphs=False)
+    for _ in range(3):
+        a.train_step(x, y, 1.0)
+    path = checkpoint.save(str(tmp_path), spec, a.global_step, a.get_params(), a.get_adam_state())
+    blob = checkpoint.load(checkpoint.latest_checkpoint(str(tmp_path)), spec)
+    b = _engine(spec, init_stddev=0.05, seed=99, use_graphs=False)  # different init: everything must come from the file
+    b.set_params(blob["variables"])
+    b.set_adam_state(blob["adam"])
+    b.global_step = blob["global_step"]
+    assert b.global_step == 3 and b.get_adam_state()["t"] == 3
+    a.train_step(x, y, 1.0)
+    b.train_step(x, y, 1.0)
+    pa, pb = a.get_params(), b.get_params()
+    for k in pa:
+        d = (pa[k] - pb[k]).abs()
+        assert d.mean().item() < 1e-5 and (d > 2e-2).float().mean().item() < 1e-3, k
+    assert a.global_step == b.global_step == 4
