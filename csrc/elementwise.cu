@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
                                                         unsigned char* __restrict__ amax) {
   grid_dep_wait();
   grid_dep_launch();
-  __shared__ float patch[18][32];  // input rows 14*half-2 .. +17, cols -2 .. 29
+  __shared__ __align__(16) float patch[18][32];  // input rows 14*half-2 .. +17, cols -2 .. 29
   const int n = blockIdx.x, half = blockIdx.y;
   for (int i = threadIdx.x; i < 18 * 32; i += blockDim.x) {
     const int pr = i >> 5, pc = i & 31;
@@ -80,11 +80,17 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
   __syncthreads();
   const int ph = half * 7 + prow;
   for (int pw = 0; pw < 14; ++pw) {
-    float win[6][6];
+    float win[6][6];  // 8-byte shared loads: 18 LDS.64 instead of 36 LDS.32 (the kernel is LDS-issue bound)
 #pragma unroll
-    for (int i = 0; i < 6; ++i)
+    for (int i = 0; i < 6; ++i) {
+      const float2* pr = reinterpret_cast<const float2*>(&patch[2 * prow + i][2 * pw]);
 #pragma unroll
-      for (int j = 0; j < 6; ++j) win[i][j] = patch[2 * prow + i][2 * pw + j];
+      for (int j = 0; j < 3; ++j) {
+        const float2 t2 = pr[j];
+        win[i][2 * j] = t2.x;
+        win[i][2 * j + 1] = t2.y;
+      }
+    }
     float best = -1.f;
     int bi = 0;
 #pragma unroll

@@ -503,14 +503,8 @@ def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
     """The cluster program (mnist_python_{m,w1,w2}.py) when ps_hosts / worker_hosts name GPUs of one box
     (``gpu:<ordinal>``): one OS process per task, ps tasks on their own GPUs (``/root/reference/mnist_python_m.py:
     145-320``).  ps and worker tasks must name different GPUs here: two processes cannot share one GPU while their
-    kernels wait on each other; the colocated layout exists through the one-process-per-GPU launcher (bench.py)."""
-    import time
-
-    from .. import cluster as cl
-    from ..models.spec import make_spec
-    from ..supervisor import Supervisor
-    from .. import checkpoint
-
+    kernels wait on each other; the colocated layout is reached through ``python -m tensorflow_distributed_b200.launch``
+    (one process per GPU that is both worker and ps shard) and bench.py."""
     addr = cluster.task_address(flags.job_name, flags.task_index)
     gpus = [cluster.task_address(j, i).gpu_ordinal for j in ("ps", "worker") for i in range(cluster.num_tasks(j))]
     if len(set(gpus)) != len(gpus):
@@ -523,20 +517,33 @@ def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
     dist.init_process_group("nccl", init_method="tcp://%s:%d" % (host, port), rank=rank, world_size=world,
                             device_id=device, timeout=datetime.timedelta(seconds=flags.step_timeout_secs))
     topo = Topology(world, list(range(cluster.num_ps)), list(range(cluster.num_ps, world)), "dedicated")
+    return _gpu_task(flags, topo, rank, device, mnist, log)
+
+
+def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
+    """One rank of the GPU cluster program, whatever decided the topology (host lists or the single-box launcher)."""
+    import time
+
+    from .. import checkpoint
+    from .. import cluster as cl
+    from ..models.spec import make_spec
+    from ..supervisor import Supervisor
+
     spec = make_spec(flags.model, flags.hidden_units, flags.mlp_layers)
-    R = cl.effective_replicas_to_aggregate(flags, cluster.num_workers)
-    if flags.sync_replicas and R != cluster.num_workers:
+    R = cl.effective_replicas_to_aggregate(flags, topo.num_workers)
+    if flags.sync_replicas and R != topo.num_workers:
         log("note: the GPU path aggregates all %d workers per step (replicas_to_aggregate=%d is honoured on the "
-            "CPU/gloo path only)" % (cluster.num_workers, R))
-    is_worker = flags.job_name == "worker"
-    is_chief = is_worker and cl.is_chief(flags)
+            "CPU/gloo path only)" % (topo.num_workers, R))
+    widx = topo.worker_of(rank)
+    is_worker = widx is not None
+    is_chief = is_worker and widx == 0
     if is_worker:
-        log("Worker %d: %s" % (flags.task_index, "Initializing session..." if is_chief
+        log("Worker %d: %s" % (widx, "Initializing session..." if is_chief
                                else "Waiting for session to be initialized..."))
     eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
                            init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas,
                            grad_dtype=flags.grad_dtype)
-    if flags.log_device_placement and (is_chief or flags.job_name == "ps"):
+    if flags.log_device_placement and (is_chief or not is_worker):
         log(eng.placement.table())
     sv = Supervisor(is_chief, spec, flags.train_dir, recovery_wait_secs=1.0, log=log)
     start_step = 0
@@ -550,10 +557,10 @@ def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
         start_step = blob["global_step"]
         dist.barrier()
     if is_worker:
-        log("Worker %d: Session initialization complete." % flags.task_index)
+        log("Worker %d: Session initialization complete." % widx)
     steps_left = max(0, flags.train_steps - start_step)
     B = flags.batch_size
-    if flags.job_name == "ps":
+    if not is_worker:
         # server.join() (m:160-161): the ps only ever runs its shard's apply kernel until it is released
         if flags.sync_replicas:
             ws = eng.workspace(B)
@@ -577,7 +584,7 @@ def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
         eng.train_step(batch_xs, batch_ys, flags.keep_prob)
         local_step += 1
         step = (start_step + local_step) if flags.sync_replicas else eng.global_step  # X5
-        log("%f: Worker %d: training step %d done (global step: %d)" % (time.time(), flags.task_index, local_step, step))
+        log("%f: Worker %d: training step %d done (global step: %d)" % (time.time(), widx, local_step, step))
     eng.synchronize()
     time_end = time.time()
     log("Training ends @ %f" % time_end)
@@ -605,7 +612,7 @@ def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
                 time.sleep(0.01)
             eng.request_shutdown()
     dist.barrier()
-    out = {"role": "worker", "task_index": flags.task_index, "local_steps": local_step, "global_step": eng.global_step,
+    out = {"role": "worker", "task_index": widx, "local_steps": local_step, "global_step": eng.global_step,
            "mean_accuracy": mean_accuracy, "checkpoint": saved}
     eng.shutdown()
     return out

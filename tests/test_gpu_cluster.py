@@ -91,3 +91,17 @@ def test_gpu_cluster_scripts_async(tmp_path):
 def test_two_gpu_bf16_gradient_push(model):
     out = _torchrun(2, ["--layout", "colocated", "--model", model, "--grad_dtype", "bf16"], 29615)
     assert "OK" in out and "FAIL" not in out and "bf16-grad-push" in out
+
+
+@needs2
+def test_single_box_launcher_colocated(tmp_path):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29640", "-m", "tensorflow_distributed_b200.launch", "--layout=colocated",
+           "--train_steps=20", "--init_stddev=0.05", "--validation_batch_size=500", "--validation_batches=2",
+           "--train_dir=%s" % tmp_path]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT, env=dict(os.environ, PYTHONPATH=ROOT))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("training step 20 done (global step: 20)") == 2
+    accs = [float(l.split(":")[1]) for l in r.stdout.splitlines() if l.startswith("Mean Accuracy")]
+    assert len(accs) == 2 and min(accs) > 0.9
+    assert os.path.exists(os.path.join(str(tmp_path), "model.ckpt-20.pt"))
