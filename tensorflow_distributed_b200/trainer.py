@@ -161,6 +161,8 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
 
     sv.prepare_or_wait(init_fn=lambda: client.init_variables(eng.get_params()), restore_fn=_restore,
                        wait_fn=lambda s: client.wait_ready(s, flags.step_timeout_secs))
+    if sv.restored_from:
+        log("Worker %d: restored variables from %s" % (flags.task_index, sv.restored_from))
     log("Worker %d: Session initialization complete." % flags.task_index)
 
     if flags.sync_replicas and is_chief:
@@ -170,6 +172,7 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
     time_begin = time.time()
     log("Training begins @ %f" % time_begin)
     local_step = 0
+    last_saved = 0
     token = client.global_step()  # local_step_init_op: local step starts at the global step
     step = token
     while True:
@@ -186,6 +189,13 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
         local_step += 1
         now = time.time()
         log("%f: Worker %d: training step %d done (global step: %d)" % (now, flags.task_index, local_step, step))
+        if is_chief and flags.train_dir and flags.save_checkpoint_steps > 0 and \
+                step // flags.save_checkpoint_steps > last_saved // flags.save_checkpoint_steps:
+            # the Supervisor's periodic saver (every 600 s in TF, m:239-253); here every N global steps
+            st = client.get_state()
+            sv.save(st["global_step"], st["params"], {"t": st["t"], "m": st["m"], "v": st["v"],
+                                                      "beta1_power": 0.9 ** st["t"], "beta2_power": 0.999 ** st["t"]})
+            last_saved = step
         if step >= flags.train_steps:
             break
     time_end = time.time()
