@@ -261,23 +261,8 @@ class NativeEngine:
         return max(1, min(cap, kblocks, 148 // max(1, mtiles * ntiles)))
 
     def _cnn_forward(self, ws: Workspace, training: bool, keep_prob: float, mask_out=None) -> None:
-        B = ws.B
-        if training:  # accumulators of the atomic epilogues (all tiny): cleared off the critical path
-            main = torch.cuda.current_stream()
-            s2 = self._side_streams()[1]
-            s2.wait_stream(main)
-            with torch.cuda.stream(s2):
-                nat.zero_multi([self.G("weights/wc1"), self.G("biases/bc1"), self.G("weights/wc2"),
-                                self.G("biases/bc2")])
-        nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, B)
-        nat.conv2_fwd(ws.pool1, self.S("weights/wc2"), self.P("biases/bc2"), ws.pool2, ws.am2, B, ref=self.conv2_ref)
-        self.gemm_fwd("weights/wd1", ws.pool2.view(B, 3136), B, ws.fc1acc, mode=nat.EPI_STORE_F32, bn=64,
-                      splits=ws.fc1_splits, split_stride=B * 1024, ld_out=1024)
-        nat.head_rows(ws.fc1acc, None, self.P("biases/bd1"), self.P("weights/out"), self.P("biases/out"), ws.y, B,
-                      1024, 1024, keep_prob if training else 1.0, self.seed, 0, training, ws.hid,
-                      ws.dhid if training else None, ws.dlogits, ws.loss_row, ws.hit, mask_out,
-                      step_ptr=self.step_ptr() if training else None, pre_nsplit=ws.fc1_splits,
-                      pre_split_stride=B * 1024)
+        from .models import cnn
+        cnn.forward(self, ws, training, keep_prob, mask_out)
 
     def _side_streams(self):
         if not hasattr(self, "_sides"):
@@ -285,71 +270,16 @@ class NativeEngine:
         return self._sides
 
     def _cnn_backward(self, ws: Workspace) -> None:
-        """Backward as a DAG: the weight-gradient kernels are leaves (nothing downstream reads them before the
-        push/apply), so they run on side streams -- graph branches after capture -- next to the critical path
-        head -> fc1 dgrad -> pool2 bwd -> conv2 dgrad -> conv1 wgrad."""
-        B = ws.B
-        main = torch.cuda.current_stream()
-        s1, s2 = self._side_streams()
-        s1.wait_stream(main)
-        with torch.cuda.stream(s1):
-            nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, self.G("weights/out"),
-                          self.G("biases/bd1"), self.G("biases/out"), ws.scalars)
-            # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
-            self.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
-        # fc1 dgrad: dpool2[B,3136] = dhid wd1^T    (wd1 read K-major in place)
-        self.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
-                        split_stride=B * 3136, ld_out=3136)
-        if self.early_adam_var == "weights/wd1" and self._training_apply:
-            # wd1 is 98% of the parameter bytes: its Adam pass starts as soon as its gradient is complete (and the
-            # dgrad above has read the old weights) and runs under pool2-bwd / conv2-dgrad / conv1-wgrad
-            s1.wait_stream(main)
-            with torch.cuda.stream(s1):
-                self._apply_early("weights/wd1")
-        main.wait_stream(s2)  # the zeroed accumulators
-        nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"), B, nsplit=ws.dg_splits,
-                      split_stride=B * 3136)
-        s2.wait_stream(main)
-        with torch.cuda.stream(s2):
-            nat.conv2_wgrad(ws.pool1, ws.dy2, self.G("weights/wc2"), B, ref=self.conv2_ref)
-        nat.conv2_dgrad(ws.dy2, self.S("weights/wc2"), ws.dpool1, B, ref=self.conv2_ref)
-        nat.conv1_wgrad(ws.x, ws.dpool1, ws.pool1, ws.am1, self.G("weights/wc1"), self.G("biases/bc1"), B)
-        main.wait_stream(s1)
-        main.wait_stream(s2)
+        from .models import cnn
+        cnn.backward(self, ws)
 
     def _mlp_forward(self, ws: Workspace, training: bool) -> None:
-        B, dims = ws.B, [784] + list(self.spec.hidden)
-        L = len(dims) - 1
-        nat.cast_bf16(ws.x, ws.act[0], B, 784, 784, 784)
-        for l in range(1, L + 1):
-            H, K = dims[l], dims[l - 1]
-            self.gemm_fwd("weights/h%d" % l, ws.act[l - 1], B, ws.act[l], mode=nat.EPI_BIAS_RELU_BF16, bn=64,
-                          bias=self.P("biases/b%d" % l))
-        H = dims[L]
-        nat.head_rows(None, ws.act[L], None, self.P("weights/out"), self.P("biases/out"), ws.y, B, H, _pad8(H), 1.0,
-                      self.seed, 0, training, None, ws.dact[L] if training else None, ws.dlogits, ws.loss_row, ws.hit)
+        from .models import mlp
+        mlp.forward(self, ws, training)
 
     def _mlp_backward(self, ws: Workspace) -> None:
-        B, dims = ws.B, [784] + list(self.spec.hidden)
-        L = len(dims) - 1
-        H = dims[L]
-        nat.head_cols(ws.act[L], ws.dact[L], _pad8(H), ws.dlogits, ws.loss_row, ws.hit, B, H, self.G("weights/out"),
-                      self.G("biases/b%d" % L), self.G("biases/out"), ws.scalars)
-        # wgrad_l only needs dact[l] and act[l-1]; it runs on a side stream (a graph branch) while the main stream
-        # continues with dgrad_l.  On a multi-GPU run that also overlaps the two NVLink directions: wgrad pushes
-        # (egress) while dgrad pulls (ingress).
-        main = torch.cuda.current_stream()
-        s1 = self._side_streams()[0]
-        for l in range(L, 0, -1):
-            H, K = dims[l], dims[l - 1]
-            s1.wait_stream(main)
-            with torch.cuda.stream(s1):
-                self.gemm_wgrad("weights/h%d" % l, ws.act[l - 1], ws.dact[l], B, bn=128 if H >= 128 else 64)
-            if l > 1:
-                self.gemm_dgrad("weights/h%d" % l, ws.dact[l], B, ws.dact[l - 1], mode=nat.EPI_RELUMASK_BF16, bn=64,
-                                relu_mask=ws.act[l - 1])
-                nat.colsum_bf16(ws.dact[l - 1], _pad8(K), B, K, self.G("biases/b%d" % (l - 1)))
-        main.wait_stream(s1)
+        from .models import mlp
+        mlp.backward(self, ws)
 
     _training_apply = False  # set by _sequence: True only when this step ends with an apply ("train" mode)
 
