@@ -246,6 +246,11 @@ class NativeEngine:
         G = self.G(wname)
         nat.gemm_bf16(X, 1, dY, 1, G.shape[0], G.shape[1], Bsz, G, mode=nat.EPI_STORE_F32, bn=bn)
 
+    def gemm_dgrad_pool2(self, ws) -> None:
+        """fc1 dgrad -> ReLU' -> max-pool backward in one kernel: writes ws.dy2 and accumulates the conv2 bias grad."""
+        W = self.S("weights/wd1")
+        nat.gemm_dgrad_pool2(ws.dhid, [W.data_ptr()], W.stride(0), ws.B, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"))
+
     def step_ptr(self):
         """Device word that advances once per training step (dropout stream, version gates)."""
         return self.shard.ctrl[CTRL_T:]

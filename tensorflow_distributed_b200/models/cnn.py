@@ -44,18 +44,24 @@ def backward(eng, ws: Workspace) -> None:
                       eng.G("biases/bd1"), eng.G("biases/out"), ws.scalars)
         # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
         eng.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
-    # fc1 dgrad: dpool2[B,3136] = dhid wd1^T    (wd1 read K-major in place)
-    eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
-                    split_stride=B * 3136, ld_out=3136)
+    main.wait_stream(s2)  # the zeroed accumulators (d(bc2) is accumulated below)
+    if getattr(eng, "fuse_dgrad_pool", False):
+        # fc1 dgrad fused with ReLU' and the 2x2 max-pool backward in the GEMM epilogue.  Measured (B=128): 25.6 us
+        # for the fused kernel (it cannot use split-K, so only 49 CTAs) vs 12.4 + 9.4 us for the two kernels below.
+        eng.gemm_dgrad_pool2(ws)
+    else:
+        # fc1 dgrad: dpool2[B,3136] = dhid wd1^T (wd1 read K-major in place), split-K partial planes summed by the
+        # pool2 / ReLU backward kernel
+        eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
+                       split_stride=B * 3136, ld_out=3136)
+        nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, eng.G("biases/bc2"), B, nsplit=ws.dg_splits,
+                      split_stride=B * 3136)
     if eng.early_adam_var == "weights/wd1" and eng._training_apply:
-        # wd1 is 98% of the parameter bytes: its Adam pass starts as soon as its gradient is complete (and the
-        # dgrad above has read the old weights) and runs under pool2-bwd / conv2-dgrad / conv1-wgrad
+        # wd1 is 98% of the parameter bytes: its Adam pass may start as soon as its gradient is complete and the
+        # dgrad above has read the old weights (measured: no gain, see profiles/ANALYSIS.md; off by default)
         s1.wait_stream(main)
         with torch.cuda.stream(s1):
             eng._apply_early("weights/wd1")
-    main.wait_stream(s2)  # the zeroed accumulators
-    nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, eng.G("biases/bc2"), B, nsplit=ws.dg_splits,
-                  split_stride=B * 3136)
     s2.wait_stream(main)
     with torch.cuda.stream(s2):
         nat.conv2_wgrad(ws.pool1, ws.dy2, eng.G("weights/wc2"), B, ref=eng.conv2_ref)

@@ -292,6 +292,16 @@ class GpuClusterEngine(NativeEngine):
                           splits=splits, split_stride=split_stride, relu_mask=relu_mask,
                           ld_mask=relu_mask.stride(0) if relu_mask is not None else 0)
 
+    def gemm_dgrad_pool2(self, ws) -> None:
+        name = "weights/wd1"
+        if name in self.prefetched or name not in self.direct:
+            if name in self.prefetched:
+                self._join_prefetch()
+            return super().gemm_dgrad_pool2(ws)
+        d = self._direct_info[name]
+        nat.gemm_dgrad_pool2(ws.dhid, d["shadow"], d["ld"], ws.B, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"),
+                             seg_rows=d["rows"], wait_flags=d["ver"], wait_value_ptr=self.step_ptr())
+
     def gemm_wgrad(self, wname, X, dY, Bsz, *, bn):
         if wname not in self.direct:
             return super().gemm_wgrad(wname, X, dY, Bsz, bn=bn)

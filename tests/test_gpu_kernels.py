@@ -387,3 +387,27 @@ def test_gemm_segmented_operands_single_gpu(nat):
     assert rel_err(torch.cat(slots, 0), x.float().t() @ dy.float()) < 2e-3
     assert rel_err(planes.sum(0), x.float() @ W.float()) < 2e-3
     assert rel_err(dplanes.sum(0), dy.float() @ W.float().t()) < 2e-3
+
+
+@pytest.mark.parametrize("B", [128, 40])
+def test_gemm_dgrad_fused_with_pool2_backward(nat, B):
+    """fc1 dgrad -> ReLU' -> max-pool backward in the GEMM epilogue vs the unfused PyTorch formulation."""
+    torch.manual_seed(14)
+    dhid = bf(torch.randn(B, 1024, device=DEV))
+    W = bf(torch.randn(3136, 1024, device=DEV) * 0.05)
+    pre = torch.randn(B, 14, 14, 64, device=DEV)
+    act = torch.relu(pre)
+    pooled = oracle.maxpool2x2_nhwc(act)
+    win = act.reshape(B, 7, 2, 7, 2, 64).permute(0, 1, 3, 5, 2, 4).reshape(B, 7, 7, 64, 4)
+    am = win.argmax(dim=4).to(torch.uint8)
+    pool_bf = bf(pooled)
+    dy = torch.full((B, 14, 14, 64), 9.0, device=DEV, dtype=torch.bfloat16)
+    db = torch.zeros(64, device=DEV)
+    nat.gemm_dgrad_pool2(dhid, [W.data_ptr()], 1024, B, pool_bf, am, dy, db)
+    torch.cuda.synchronize()
+    dpool = (dhid.float() @ W.float().t()).reshape(B, 7, 7, 64)
+    g = dpool * (pool_bf.float() > 0)
+    ref = torch.zeros(B, 7, 7, 64, 4, device=DEV).scatter_(4, am.long().unsqueeze(-1), g.unsqueeze(-1))
+    ref = ref.reshape(B, 7, 7, 64, 2, 2).permute(0, 1, 4, 2, 5, 3).reshape(B, 14, 14, 64)
+    assert rel_err(dy, ref) < 1e-2
+    assert rel_err(db, g.sum(dim=(0, 1, 2))) < 2e-3
