@@ -38,6 +38,7 @@ struct AdamArgs {
   int slots_bf16;               // gradient slots hold bf16 (halves the push bytes); accumulation stays fp32
   long long skip_begin, skip_end;  // elements [skip_begin, skip_end) are left alone (updated by an earlier launch)
   int finalize;                 // 1: bump t / global_step and publish the version; 0: partial launch of this step
+  const unsigned* mask_ptr;     // backup workers: bit w set = slot w contributes to this update (decided by decide_kernel)
 };
 
 // four gradient values at element index i of a staging slot (fp32 or bf16 storage)
@@ -57,6 +58,15 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   if (a.wait_counter) {
     if (threadIdx.x == 0) spin_until_ge(a.wait_counter, (unsigned)a.num_slots * t, "adam: gradient arrivals");
     __syncthreads();
+  }
+  // backup workers (R of N): only the slots named in the mask are summed, the average is over their count; an empty
+  // mask means the ps is being released
+  unsigned use_mask = 0xffffffffu;
+  float scale = a.scale;
+  if (a.mask_ptr) {
+    use_mask = *a.mask_ptr;
+    if (use_mask == 0) return;
+    scale = 1.f / (float)__popc(use_mask);
   }
   const float* serve_slot = nullptr;
   if (a.queue) {
@@ -91,7 +101,9 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   const long long skip4 = (a.skip_end - a.skip_begin) >> 2, skipb4 = a.skip_begin >> 2;
   const long long n4 = (a.n >> 2) - skip4;
   const long long stride4 = (long long)gridDim.x * blockDim.x;
-  const float* g0 = serve_slot ? serve_slot : a.slots[0];
+  int first = 0;
+  if (a.mask_ptr) first = __ffs(use_mask) - 1;
+  const float* g0 = serve_slot ? serve_slot : a.slots[first];
   const int nslots = serve_slot ? 1 : a.num_slots;
   int cur = 0;  // cached piece index for the shadow lookup
   for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += 2 * stride4) {
@@ -107,7 +119,8 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
       v4[h] = __ldcs(reinterpret_cast<const float4*>(a.v + idx[h]));
       g4[h] = load_grad4(g0, idx[h], a.slots_bf16);
     }
-    for (int r = 1; r < nslots; ++r) {
+    for (int r = first + 1; r < nslots; ++r) {
+      if (!((use_mask >> r) & 1u)) continue;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const float4 x = load_grad4(a.slots[r], idx[h], a.slots_bf16);
@@ -119,7 +132,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
       if ((h == 1 && !ok1) || (h == 0 && !ok0)) continue;
       float wv[4] = {w4[h].x, w4[h].y, w4[h].z, w4[h].w}, mv[4] = {m4[h].x, m4[h].y, m4[h].z, m4[h].w};
       float vv[4] = {v4[h].x, v4[h].y, v4[h].z, v4[h].w};
-      const float gv[4] = {g4[h].x * a.scale, g4[h].y * a.scale, g4[h].z * a.scale, g4[h].w * a.scale};
+      const float gv[4] = {g4[h].x * scale, g4[h].y * scale, g4[h].z * scale, g4[h].w * scale};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         mv[j] = a.beta1 * mv[j] + (1.f - a.beta1) * gv[j];
@@ -193,6 +206,8 @@ struct PushTable {
   unsigned worker;              // this worker's index
   unsigned* my_ticket;          // async: local array [narrive]; receives ticket+1 = the version that serves it
   int dst_bf16;                 // destination slots hold bf16
+  const unsigned* tag_ptr;      // backup workers: stamp every shard with *tag_ptr instead of counting arrivals
+  unsigned* tag_cur;            //   ... and remember it (what the next pull waits for)
 };
 
 // grid (blocks_per_seg, nseg)
@@ -233,10 +248,13 @@ __global__ void __launch_bounds__(1024) push_kernel(const __grid_constant__ Push
       const unsigned tk = atom_add_release_sys_u32(t.arrive[k], 1u);
       st_release_sys_u32(t.queue[k] + (tk % (unsigned)t.qlen), t.worker + 1u);
       t.my_ticket[k] = tk + 1u;
+    } else if (t.tag_ptr) {
+      st_release_sys_u32(t.arrive[k], *t.tag_ptr);  // "my slot holds a gradient for update <tag>"
     } else {
       red_add_release_sys_u32(t.arrive[k], 1u);
     }
   }
+  if (k == 0 && t.tag_ptr) *t.tag_cur = *t.tag_ptr;
   if (k == 0 && local_step) *local_step = *local_step + 1;
 }
 
@@ -250,6 +268,8 @@ struct PullSeg {
 struct PullTable {
   PullSeg seg[kMaxSegs];
   int nseg;
+  int tag_seg;                  // backup workers: the block of this segment also derives the next push's tag
+  unsigned* tag_out;            //   = (version it observed) + 1
 };
 
 __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullTable t, unsigned want_base,
@@ -259,7 +279,10 @@ __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullT
   const PullSeg s = t.seg[blockIdx.y];
   const unsigned want = want_base + (want_ptr ? *want_ptr : 0u);
   if (s.version) {
-    if (threadIdx.x == 0) spin_until_ge(s.version, s.want_seg ? *s.want_seg : want, "pull: parameter version");
+    if (threadIdx.x == 0) {
+      spin_until_ge(s.version, s.want_seg ? *s.want_seg : want, "pull: parameter version");
+      if (t.tag_out && (int)blockIdx.y == t.tag_seg && blockIdx.x == 0) *t.tag_out = ld_acquire_sys_u32(s.version) + 1u;
+    }
     __syncthreads();
   }
   // peer reads are latency-bound (~2 us per round trip): four independent 16-byte loads in flight per thread
@@ -295,7 +318,7 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
                        float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                        unsigned* version_flag, unsigned* global_step, unsigned* queue, int qlen,
                        const unsigned* shutdown, int slots_bf16, long long skip_begin, long long skip_end, int finalize,
-                       void* stream) {
+                       const unsigned* mask_ptr, void* stream) {
   TFD_REQUIRE(n % 4 == 0 && skip_begin % 4 == 0 && skip_end % 4 == 0 && skip_begin <= skip_end && skip_end <= n,
               "adam: arena length %lld / skip range [%lld,%lld) must be multiples of 4 and nested", n, skip_begin, skip_end);
   TFD_REQUIRE(num_pieces <= kMaxPieces, "adam: too many pieces (%d)", num_pieces);
@@ -310,7 +333,7 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
   a.num_slots = num_slots; a.scale = scale; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
   a.t_counter = t_counter; a.wait_counter = wait_counter; a.version_flag = version_flag; a.global_step = global_step;
   a.queue = queue; a.qlen = qlen; a.shutdown = shutdown; a.slots_bf16 = slots_bf16;
-  a.skip_begin = skip_begin; a.skip_end = skip_end; a.finalize = finalize;
+  a.skip_begin = skip_begin; a.skip_end = skip_end; a.finalize = finalize; a.mask_ptr = mask_ptr;
   long long blocks = ((n - (skip_end - skip_begin)) / 8 + 255) / 256;
   if (blocks < 1) blocks = 1;
   // finalize == 0: the early launch runs next to tcgen05 kernels; two blocks per SM leave them the registers
@@ -326,7 +349,7 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
                               float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, 0, 0, 1, stream);
+                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, 0, 0, 1, nullptr, stream);
 }
 
 /* Partial form: update only part of the arena now and the rest later in the same step, so the Adam pass over a big
@@ -340,7 +363,45 @@ extern "C" int tfd_adam_apply_part(float* w, float* m, float* v, void* shadow, c
                                    long long skip_begin, long long skip_end, int finalize, void* stream) {
   return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
                      wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, skip_begin,
-                     skip_end, finalize, stream);
+                     skip_end, finalize, nullptr, stream);
+}
+
+// Backup workers (replicas_to_aggregate R < workers N; m:62-65, SyncReplicasOptimizer's stale-gradient drop): every
+// worker stamps its slot with the update index it computed for (tag = version it pulled + 1).  One thread waits
+// until at least R stamps equal the next update index t and publishes that set as a bit mask; the Adam launch that
+// follows sums exactly those slots.  Stamps older than t are stale and simply never match.
+__global__ void decide_kernel(const unsigned* stamps, int nworkers, int need, const unsigned* t_counter,
+                              unsigned* mask_out, const unsigned* shutdown) {
+  grid_dep_wait();
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const unsigned t = t_counter[0] + 1;
+  unsigned long long t0 = globaltimer_ns();
+  unsigned it = 0;
+  for (;;) {
+    unsigned mask = 0;
+    for (int w = 0; w < nworkers; ++w)
+      if (ld_acquire_sys_u32(stamps + w) == t) mask |= 1u << w;
+    if (__popc(mask) >= need) { *mask_out = mask; return; }
+    if (shutdown && ld_acquire_sys_u32(shutdown) != 0) { *mask_out = 0; return; }
+    __nanosleep(128);
+    if ((++it & 0xff) == 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) {
+      printf("tfd: waited 20 s for %d gradients of update %u (have mask %x)\n", need, t, mask);
+      __trap();
+    }
+  }
+}
+
+extern "C" int tfd_adam_apply_backup(float* w, float* m, float* v, void* shadow, const float* const* slots,
+                                     int num_slots, int replicas_to_aggregate, long long n, const tfd_piece_t* pieces,
+                                     int num_pieces, float lr, float beta1, float beta2, float eps, unsigned* t_counter,
+                                     const unsigned* stamps, unsigned* mask_word, const unsigned* shutdown,
+                                     unsigned* version_flag, unsigned* global_step, void* stream) {
+  TFD_REQUIRE(replicas_to_aggregate >= 1 && replicas_to_aggregate <= num_slots && num_slots <= 32,
+              "adam_backup: need 1 <= R (%d) <= workers (%d) <= 32", replicas_to_aggregate, num_slots);
+  decide_kernel<<<1, 32, 0, ST(stream)>>>(stamps, num_slots, replicas_to_aggregate, t_counter, mask_word, shutdown);
+  TFD_LAUNCH_CHECK();
+  return adam_launch(w, m, v, shadow, slots, num_slots, 1.0f, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
+                     nullptr, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, 0, 0, 1, mask_word, stream);
 }
 
 extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
@@ -349,7 +410,7 @@ extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const 
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   TFD_REQUIRE(queue != nullptr && qlen >= num_slots, "adam_serve: ring of %d cells cannot hold %d workers", qlen, num_slots);
   return adam_launch(w, m, v, shadow, slots, num_slots, 1.0f, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     nullptr, version_flag, global_step, queue, qlen, shutdown, g_next_slots_bf16, 0, 0, 1, stream);
+                     nullptr, version_flag, global_step, queue, qlen, shutdown, g_next_slots_bf16, 0, 0, 1, nullptr, stream);
 }
 
 /* Multi-segment push: segs[i] = {src, dst, n}; after every segment is written the last block adds 1 to each
@@ -357,12 +418,13 @@ extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const 
 static int push_launch(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
                        unsigned* const* arrive, int narrive, float scale, unsigned* block_counter,
                        unsigned* local_step, unsigned* const* queues, int qlen, unsigned worker, unsigned* my_ticket,
-                       void* stream) {
+                       const unsigned* tag_ptr, unsigned* tag_cur, void* stream) {
   TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSegs && narrive <= kMaxSegs, "push: bad segment count %d/%d", nseg, narrive);
   PushTable t;
   memset(&t, 0, sizeof(t));
   t.nseg = nseg; t.narrive = narrive;
   t.qlen = qlen; t.worker = worker; t.my_ticket = my_ticket; t.dst_bf16 = g_next_slots_bf16;
+  t.tag_ptr = tag_ptr; t.tag_cur = tag_cur;
   for (int i = 0; i < narrive && queues; ++i) t.queue[i] = queues[i];
   long long maxn = 0;
   for (int i = 0; i < nseg; ++i) {
@@ -384,7 +446,8 @@ static int push_launch(const void* const* srcs, void* const* dsts, const long lo
 extern "C" int tfd_push_multi(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
                               unsigned* const* arrive, int narrive, float scale, unsigned* block_counter,
                               unsigned* local_step, void* stream) {
-  return push_launch(srcs, dsts, ns, nseg, arrive, narrive, scale, block_counter, local_step, nullptr, 0, 0, nullptr, stream);
+  return push_launch(srcs, dsts, ns, nseg, arrive, narrive, scale, block_counter, local_step, nullptr, 0, 0, nullptr,
+                     nullptr, nullptr, stream);
 }
 
 extern "C" int tfd_push_multi_async(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
@@ -393,7 +456,15 @@ extern "C" int tfd_push_multi_async(const void* const* srcs, void* const* dsts, 
                                     void* stream) {
   TFD_REQUIRE(qlen > 0 && my_ticket != nullptr && queues != nullptr, "push_async: ring / ticket array missing");
   return push_launch(srcs, dsts, ns, nseg, tickets, nshards, 1.0f, block_counter, local_step, queues, qlen, worker,
-                     my_ticket, stream);
+                     my_ticket, nullptr, nullptr, stream);
+}
+
+extern "C" int tfd_push_multi_stamp(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
+                                    unsigned* const* stamps, int nshards, const unsigned* tag_ptr, unsigned* tag_cur,
+                                    unsigned* block_counter, unsigned* local_step, void* stream) {
+  TFD_REQUIRE(tag_ptr && tag_cur, "push_stamp: tag words missing");
+  return push_launch(srcs, dsts, ns, nseg, stamps, nshards, 1.0f, block_counter, local_step, nullptr, 0, 0, nullptr,
+                     tag_ptr, tag_cur, stream);
 }
 
 extern "C" int tfd_push_grads(const float* src, float* dst, long long n, float scale, unsigned* arrive_counter,
@@ -407,11 +478,12 @@ extern "C" int tfd_push_grads(const float* src, float* dst, long long n, float s
 
 static int pull_launch(const void* const* srcs, void* const* dsts, const long long* ns,
                        const unsigned* const* versions, const unsigned* const* want_segs, int nseg,
-                       unsigned want_version, const unsigned* want_ptr, void* stream) {
+                       unsigned want_version, const unsigned* want_ptr, int tag_seg, unsigned* tag_out, void* stream) {
   TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSegs, "pull: bad segment count %d", nseg);
   PullTable t;
   memset(&t, 0, sizeof(t));
   t.nseg = nseg;
+  t.tag_seg = tag_seg; t.tag_out = tag_out;
   long long maxn = 0;
   for (int i = 0; i < nseg; ++i) {
     t.seg[i] = PullSeg{static_cast<const float*>(srcs[i]), static_cast<float*>(dsts[i]), ns[i], versions ? versions[i] : nullptr,
@@ -429,13 +501,20 @@ static int pull_launch(const void* const* srcs, void* const* dsts, const long lo
 extern "C" int tfd_pull_multi(const void* const* srcs, void* const* dsts, const long long* ns,
                               const unsigned* const* versions, int nseg, unsigned want_version,
                               const unsigned* want_ptr, void* stream) {
-  return pull_launch(srcs, dsts, ns, versions, nullptr, nseg, want_version, want_ptr, stream);
+  return pull_launch(srcs, dsts, ns, versions, nullptr, nseg, want_version, want_ptr, -1, nullptr, stream);
 }
 
 extern "C" int tfd_pull_multi_async(const void* const* srcs, void* const* dsts, const long long* ns,
                                     const unsigned* const* versions, const unsigned* const* want_segs, int nseg,
                                     void* stream) {
-  return pull_launch(srcs, dsts, ns, versions, want_segs, nseg, 0, nullptr, stream);
+  return pull_launch(srcs, dsts, ns, versions, want_segs, nseg, 0, nullptr, -1, nullptr, stream);
+}
+
+extern "C" int tfd_pull_multi_tag(const void* const* srcs, void* const* dsts, const long long* ns,
+                                  const unsigned* const* versions, const unsigned* const* want_segs, int nseg,
+                                  int tag_seg, unsigned* tag_out, void* stream) {
+  TFD_REQUIRE(tag_out && tag_seg >= 0 && tag_seg < nseg, "pull_tag: bad tag segment %d", tag_seg);
+  return pull_launch(srcs, dsts, ns, versions, want_segs, nseg, 0, nullptr, tag_seg, tag_out, stream);
 }
 
 extern "C" int tfd_pull_params(const float* src, float* dst, long long n, const unsigned* version_flag, unsigned version,

@@ -223,6 +223,24 @@ int tfd_push_multi_async(const void* const* srcs, void* const* dsts, const long 
 int tfd_pull_multi_async(const void* const* srcs, void* const* dsts, const long long* ns,
                          const unsigned* const* versions, const unsigned* const* want_segs, int nseg, void* stream);
 
+/* ---- backup workers: aggregate the first R of N gradients, drop stale ones (m:62-65, m:210-220) ----
+ * Worker: tfd_pull_multi_tag waits (per segment) for *versions[i] >= *want_segs[i] (= the tag of its previous push)
+ * and stores tag = version+1 of segment tag_seg's shard in *tag_out; tfd_push_multi_stamp writes the slots and then
+ * stamps every shard's word for this worker with *tag_ptr (release) and copies it to *tag_cur.
+ * Shard: tfd_adam_apply_backup = a one-thread decide kernel that waits until >= R stamps equal the next update index
+ * t and publishes them as a bit mask, followed by the Adam kernel that sums exactly those slots (scale 1/count).
+ * A stamp older than t is a stale gradient: it never matches and is never read.  *shutdown != 0 releases the wait. */
+int tfd_adam_apply_backup(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
+                          int replicas_to_aggregate, long long n, const tfd_piece_t* pieces, int num_pieces, float lr,
+                          float beta1, float beta2, float eps, unsigned* t_counter, const unsigned* stamps,
+                          unsigned* mask_word, const unsigned* shutdown, unsigned* version_flag, unsigned* global_step,
+                          void* stream);
+int tfd_push_multi_stamp(const void* const* srcs, void* const* dsts, const long long* ns, int nseg,
+                         unsigned* const* stamps, int nshards, const unsigned* tag_ptr, unsigned* tag_cur,
+                         unsigned* block_counter, unsigned* local_step, void* stream);
+int tfd_pull_multi_tag(const void* const* srcs, void* const* dsts, const long long* ns, const unsigned* const* versions,
+                       const unsigned* const* want_segs, int nseg, int tag_seg, unsigned* tag_out, void* stream);
+
 /* ---- peer memory (symmetric heap over cudaIpc) ---- */
 int tfd_set_device(int device);
 int tfd_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out64);    /* cudaMalloc + cudaIpcGetMemHandle */

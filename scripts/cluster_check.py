@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--async_mode", action="store_true")
     ap.add_argument("--pull", default="auto")
     ap.add_argument("--grad_dtype", default="fp32")
+    ap.add_argument("--replicas", type=int, default=0)
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -45,7 +46,8 @@ def main():
     spec = make_spec(a.model, a.hidden, a.layers)
     topo = Topology.make(world, a.layout, a.ps)
     eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05,
-                           async_mode=a.async_mode, pull_mode=a.pull, grad_dtype=a.grad_dtype)
+                           async_mode=a.async_mode, pull_mode=a.pull, grad_dtype=a.grad_dtype,
+                           replicas_to_aggregate=a.replicas)
     B = 128
     keep = 1.0
     w = topo.worker_of(rank)

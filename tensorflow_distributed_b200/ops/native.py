@@ -312,6 +312,42 @@ def pull_multi_async(srcs, dsts, ns, versions, want_segs) -> None:
     _count()
 
 
+def adam_apply_backup(w, m, v, shadow, slots, num_slots: int, replicas_to_aggregate: int, n: int, pieces, lr: float,
+                      t_counter, stamps, mask_word, shutdown, version_flag, global_step, beta1: float = 0.9,
+                      beta2: float = 0.999, eps: float = 1e-8) -> None:
+    arr = (Piece * max(1, len(pieces)))(*pieces)
+    sl = (c_void_p * num_slots)(*[c_void_p(int(x)) for x in slots[:num_slots]])
+    _check(lib().tfd_adam_apply_backup(_p(w), _p(m), _p(v), _p(shadow), sl, c_int(num_slots),
+                                       c_int(replicas_to_aggregate), c_longlong(n), arr, c_int(len(pieces)), c_float(lr),
+                                       c_float(beta1), c_float(beta2), c_float(eps), _p(t_counter), _p(stamps),
+                                       _p(mask_word), _p(shutdown), _p(version_flag), _p(global_step), _stream()),
+           "tfd_adam_apply_backup")
+    _count(2)
+
+
+def push_multi_stamp(srcs, dsts, ns, stamps, tag_ptr, tag_cur, block_counter, local_step=None) -> None:
+    n, k = len(srcs), len(stamps)
+    S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
+    D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
+    NS = (c_longlong * n)(*[int(x) for x in ns])
+    T = (c_void_p * k)(*[c_void_p(int(x)) for x in stamps])
+    _check(lib().tfd_push_multi_stamp(S, D, NS, c_int(n), T, c_int(k), _p(tag_ptr), _p(tag_cur), _p(block_counter),
+                                      _p(local_step), _stream()), "tfd_push_multi_stamp")
+    _count()
+
+
+def pull_multi_tag(srcs, dsts, ns, versions, want_segs, tag_seg: int, tag_out) -> None:
+    n = len(srcs)
+    S = (c_void_p * n)(*[c_void_p(int(x)) for x in srcs])
+    D = (c_void_p * n)(*[c_void_p(int(x)) for x in dsts])
+    NS = (c_longlong * n)(*[int(x) for x in ns])
+    V = (c_void_p * n)(*[c_void_p(int(x)) for x in versions])
+    W = (c_void_p * n)(*[c_void_p(int(x)) for x in want_segs])
+    _check(lib().tfd_pull_multi_tag(S, D, NS, V, W, c_int(n), c_int(tag_seg), _p(tag_out), _stream()),
+           "tfd_pull_multi_tag")
+    _count()
+
+
 # ---- symmetric heap ----
 def ipc_alloc(nbytes: int):
     ptr = c_void_p()

@@ -36,6 +36,8 @@ from .placement import Placement
 WCTRL_STEP, WCTRL_PUSHBLK = 8, 9   # worker-local control words (inside the rank's own ctrl block)
 CTRL_TICKET, CTRL_SHUTDOWN = 6, 7  # async: ticket dispenser / release word of a shard
 CTRL_RING, RING_LEN = 16, 32       # async: arrival ring (worker id + 1 per served-in-order ticket)
+CTRL_STAMP, CTRL_MASK = 16, 24     # backup workers (sync, R < N): per-worker stamps and the decided slot mask
+WCTRL_TAG_CUR, WCTRL_TAG_NEXT = 10, 11  # backup workers: tag of my last push / of my next push (worker-local)
 CTRL_DONE = 56                     # async: shard 0 holds one 'worker finished' word per worker (56..63)
 WCTRL_MYTICKET = 48                # async: worker-local, one word per shard: version that serves my last push
 DIRECT_THRESHOLD = 1 << 18         # tensors at least this big are consumed in place over NVLink, never mirrored
@@ -119,7 +121,14 @@ class GpuClusterEngine(NativeEngine):
     def __init__(self, spec: ModelSpec, topo: Topology, rank: int, device, learning_rate: float = 0.01,
                  seed: int = 0, init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False,
                  async_mode: bool = False, pull_mode: str = "auto", prefetch_max_numel: int = 8 << 20,
-                 grad_dtype: str = "fp32"):
+                 grad_dtype: str = "fp32", replicas_to_aggregate: int = 0):
+        # backup workers: sync mode that aggregates only the first R of N gradients per update and drops stale ones
+        self.R = replicas_to_aggregate if 0 < replicas_to_aggregate < topo.num_workers else topo.num_workers
+        self.backup = (not async_mode) and self.R < topo.num_workers
+        if self.backup and topo.layout != "dedicated":
+            # a colocated rank applies its shard in its own worker stream: a straggling worker would stall its shard
+            # and with it everybody -- only ps-only GPUs can run ahead of stragglers
+            raise ValueError("replicas_to_aggregate < workers needs dedicated ps GPUs (layout='dedicated')")
         if grad_dtype not in ("fp32", "bf16"):
             raise ValueError("grad_dtype must be fp32 or bf16")
         self.grad_dtype, self.grad_bytes = grad_dtype, (2 if grad_dtype == "bf16" else 4)
@@ -252,7 +261,7 @@ class GpuClusterEngine(NativeEngine):
                 "rows": [q.row_start for q in pcs] + [pcs[-1].row_end], "cols": pcs[0].cols, "ld": _pad8(pcs[0].cols),
                 "shadow": [self._shadow_ptr(q.shard, name) for q in pcs],
                 "slot": [self._slot_ptr(q.shard, q.offset) for q in pcs],
-                "ver": None if self.async_mode else [self._ctrl_ptr(q.shard, CTRL_VERSION) for q in pcs]}
+                "ver": None if (self.async_mode or self.backup) else [self._ctrl_ptr(q.shard, CTRL_VERSION) for q in pcs]}
 
     # ---- parameter / gradient views used by the kernel sequences -----------------------------
     def P(self, name: str) -> torch.Tensor:
@@ -317,8 +326,19 @@ class GpuClusterEngine(NativeEngine):
         """Pull (X1): small tensors are copied once the owning shard's version has caught up with this
         worker's step counter; the same kernel thereby waits for every shard (slots are free to overwrite)."""
         if self._prefetch:
-            self._launch_prefetch()
+            self._launch_prefetch(training)
         p = self._pull
+        if self.backup and not training:
+            # evaluation after training: my last push may carry a tag the ps will never apply (it has already done
+            # its train_steps updates), so read whatever is published now
+            nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0)
+            return
+        if self.backup:  # wait until my last tagged push has been applied or overtaken; derive the next tag
+            tagcur = self.ctrl.data_ptr() + 4 * WCTRL_TAG_CUR
+            seg = next(i for i, q in enumerate(p) if q[4] == self.placement.global_step_shard)
+            nat.pull_multi_tag([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
+                               [tagcur] * len(p), seg, self.ctrl[WCTRL_TAG_NEXT:])
+            return
         if self.async_mode:  # wait (per shard) until my previous gradient has been applied: read-your-writes
             nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
                                  [self.ctrl.data_ptr() + 4 * (WCTRL_MYTICKET + s[4]) for s in p])
@@ -326,7 +346,7 @@ class GpuClusterEngine(NativeEngine):
         nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
                        want_ptr=self.step_ptr())
 
-    def _launch_prefetch(self) -> None:
+    def _launch_prefetch(self, training: bool = True) -> None:
         """Copy the prefetched matrices' bf16 shadow from the owner GPUs on a side stream (joined by the first GEMM
         that reads them), gated on the same parameter version as everything else."""
         main = torch.cuda.current_stream()
@@ -335,7 +355,12 @@ class GpuClusterEngine(NativeEngine):
         self._pf_stream.wait_stream(main)
         p = self._prefetch
         with torch.cuda.stream(self._pf_stream):
-            if self.async_mode:
+            if self.backup and not training:
+                nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0)
+            elif self.backup:
+                nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
+                                     [self.ctrl.data_ptr() + 4 * WCTRL_TAG_CUR] * len(p))
+            elif self.async_mode:
                 nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
                                      [self.ctrl.data_ptr() + 4 * (WCTRL_MYTICKET + s[4]) for s in p])
             else:
@@ -351,6 +376,13 @@ class GpuClusterEngine(NativeEngine):
     def _post_backward(self, ws) -> None:
         """Push (X2): small gradients into this worker's slots, then arrive += 1 on every shard."""
         p = self._push
+        if self.backup:
+            S = self.topo.num_shards
+            nat.push_multi_stamp([s[0] for s in p], [s[1] for s in p], [s[2] for s in p],
+                                 [self._ctrl_ptr(s, CTRL_STAMP + self.my_worker) for s in range(S)],
+                                 self.ctrl[WCTRL_TAG_NEXT:], self.ctrl[WCTRL_TAG_CUR:], self.ctrl[WCTRL_PUSHBLK:],
+                                 local_step=self.ctrl[WCTRL_STEP:])
+            return
         if self.async_mode:
             S = self.topo.num_shards
             nat.push_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p],
@@ -366,6 +398,11 @@ class GpuClusterEngine(NativeEngine):
         if not self.is_ps:
             return
         s = self.shard
+        if self.backup:  # first R of N gradients stamped for this update, averaged; stale stamps never match
+            nat.adam_apply_backup(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, self.R, s.n, s.pieces,
+                                  self.lr, s.ctrl[CTRL_T:], s.ctrl[CTRL_STAMP:], s.ctrl[CTRL_MASK:],
+                                  s.ctrl[CTRL_SHUTDOWN:], s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:])
+            return
         if self.async_mode:  # one arriving gradient, in ticket order, scale 1 (apply-on-arrival)
             nat.adam_serve(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, s.n, s.pieces, self.lr,
                            s.ctrl[CTRL_T:], s.ctrl[CTRL_RING:], RING_LEN, s.ctrl[CTRL_SHUTDOWN:], s.ctrl[CTRL_VERSION:],
@@ -400,6 +437,7 @@ class GpuClusterEngine(NativeEngine):
 
     def describe(self) -> str:
         return self.topo.describe() + (" async" if self.async_mode else " sync") + \
+            (" R=%d-of-%d" % (self.R, self.num_workers) if self.backup else "") + \
             (" bf16-grad-push" if self.grad_dtype == "bf16" else "")
 
     def _read_arena(self, which: str) -> Dict[str, torch.Tensor]:
@@ -480,8 +518,15 @@ class GpuClusterEngine(NativeEngine):
                     for arena, key in ((s.m, "m"), (s.v, "v")):
                         full = sd[key][v.name].to(torch.float32).reshape(-1, p.cols)
                         s.view(arena, v.name).copy_(full[p.row_start:p.row_end].to(self.device))
-            s.ctrl[CTRL_T] = int(sd["t"])
-            s.ctrl[CTRL_VERSION] = 0
+            # every protocol counter restarts at the restored update index T: version == applies so far, the
+            # arrival counter has seen workers*T pushes, the ticket dispenser has handed out T tickets
+            T = int(sd["t"])
+            s.ctrl[CTRL_T] = T
+            s.ctrl[CTRL_VERSION] = T
+            s.ctrl[CTRL_ARRIVE] = T * self.num_workers
+            s.ctrl[CTRL_TICKET] = T
+        if self.is_worker and not self.async_mode:
+            self.ctrl[WCTRL_STEP] = int(sd["t"])  # sync workers wait for version >= their step counter
         torch.cuda.synchronize(self.device)
         dist.barrier()
 
@@ -538,12 +583,13 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
     from .. import cluster as cl
     from ..models.spec import make_spec
     from ..supervisor import Supervisor
+    from ..trainer import _maybe_inject_fault
 
     spec = make_spec(flags.model, flags.hidden_units, flags.mlp_layers)
     R = cl.effective_replicas_to_aggregate(flags, topo.num_workers)
-    if flags.sync_replicas and R != topo.num_workers:
-        log("note: the GPU path aggregates all %d workers per step (replicas_to_aggregate=%d is honoured on the "
-            "CPU/gloo path only)" % (topo.num_workers, R))
+    if flags.sync_replicas and R != topo.num_workers and topo.layout != "dedicated":
+        log("note: colocated ps shards aggregate all %d workers per step (replicas_to_aggregate=%d needs dedicated "
+            "ps GPUs)" % (topo.num_workers, R))
     widx = topo.worker_of(rank)
     is_worker = widx is not None
     is_chief = is_worker and widx == 0
@@ -552,7 +598,8 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
                                else "Waiting for session to be initialized..."))
     eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
                            init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas,
-                           grad_dtype=flags.grad_dtype)
+                           grad_dtype=flags.grad_dtype,
+                           replicas_to_aggregate=R if topo.layout == "dedicated" else 0)
     if flags.log_device_placement and (is_chief or not is_worker):
         log(eng.placement.table())
     sv = Supervisor(is_chief, spec, flags.train_dir, recovery_wait_secs=1.0, log=log)
@@ -591,9 +638,11 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
     local_step, step = 0, start_step
     while step < flags.train_steps:
         batch_xs, batch_ys = mnist.train.next_batch(B)
+        _maybe_inject_fault(flags, local_step)
         eng.train_step(batch_xs, batch_ys, flags.keep_prob)
         local_step += 1
-        step = (start_step + local_step) if flags.sync_replicas else eng.global_step  # X5
+        # X5: strict sync knows the global step without asking; async / backup workers read it from shard 0
+        step = (start_step + local_step) if (flags.sync_replicas and not eng.backup) else eng.global_step
         log("%f: Worker %d: training step %d done (global step: %d)" % (time.time(), widx, local_step, step))
     eng.synchronize()
     time_end = time.time()

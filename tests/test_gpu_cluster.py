@@ -105,3 +105,36 @@ def test_single_box_launcher_colocated(tmp_path):
     accs = [float(l.split(":")[1]) for l in r.stdout.splitlines() if l.startswith("Mean Accuracy")]
     assert len(accs) == 2 and min(accs) > 0.9
     assert os.path.exists(os.path.join(str(tmp_path), "model.ckpt-20.pt"))
+
+
+needs4 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 4, reason="needs 4 GPUs")
+
+
+@needs4
+def test_gpu_backup_workers_drop_a_stragglers_stale_gradients(tmp_path):
+    """R-of-N on the GPU ps (m:62-65): 1 ps GPU + 3 worker GPUs, aggregate the first 2 gradients of every update;
+    worker 2 is stalled on the host before every step, so most of its gradients arrive stale and are never read."""
+    common = ["--ps_hosts=gpu:0", "--worker_hosts=gpu:1,gpu:2,gpu:3", "--train_steps=12", "--init_stddev=0.05",
+              "--replicas_to_aggregate=2", "--validation_batch_size=500", "--validation_batches=2",
+              "--step_timeout_secs=120", "--inject_fault=stall:2:0.05"]
+    env = dict(os.environ, PYTHONPATH=ROOT, TFD_MASTER_PORT="29730")
+    cmds = [("mnist_python_m.py", []), ("mnist_python_w1.py", []), ("mnist_python_w2.py", []),
+            ("mnist_python_w2.py", ["--task_index=2"])]
+    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, s)] + common + e, stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True, env=env, cwd=ROOT) for s, e in cmds]
+    outs = []
+    for p in procs:
+        try:
+            outs.append(p.communicate(timeout=280)[0])
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o[-3000:]
+    steps = [o.count(": training step") for o in outs[1:]]
+    assert steps[2] < min(steps[0], steps[1])          # the straggler did fewer local steps
+    assert max(steps[0], steps[1]) >= 12                # the fast workers carried every update
+    for o in outs[1:]:
+        assert "Mean Accuracy :" in o
+    assert any("(global step: 12)" in o for o in outs[1:])

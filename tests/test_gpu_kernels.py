@@ -411,3 +411,37 @@ def test_gemm_dgrad_fused_with_pool2_backward(nat, B):
     ref = ref.reshape(B, 7, 7, 64, 2, 2).permute(0, 1, 4, 2, 5, 3).reshape(B, 14, 14, 64)
     assert rel_err(dy, ref) < 1e-2
     assert rel_err(db, g.sum(dim=(0, 1, 2))) < 2e-3
+
+
+def test_backup_workers_decide_and_masked_apply(nat):
+    """R-of-N on the device: the shard averages exactly the slots stamped for the next update and ignores stale ones."""
+    from tensorflow_distributed_b200.ops.native import Piece
+    torch.manual_seed(15)
+    n = 64 * 8
+    w0 = torch.randn(n, device=DEV)
+    w, m, v = w0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    slots = [torch.randn(n, device=DEV) for _ in range(3)]
+    ptrs = [s.data_ptr() for s in slots]
+    ctrl = torch.zeros(64, dtype=torch.int32, device=DEV)  # [0]=t [1]=scratch [2]=version [3]=gstep [7]=shutdown [16..]=stamps [24]=mask
+    pieces = [Piece(0, n, 64, 0, 0)]
+    ref = {"w": w0.clone().cpu()}
+    opt = oracle.TFAdam(0.01)
+    # update 1: workers 0 and 2 delivered for update 1, worker 1 has not pushed yet
+    ctrl[16:19] = torch.tensor([1, 0, 1], dtype=torch.int32)
+    nat.adam_apply_backup(w, m, v, None, ptrs, 3, 2, n, pieces, 0.01, ctrl[0:], ctrl[16:], ctrl[24:], ctrl[7:], ctrl[2:], ctrl[3:])
+    torch.cuda.synchronize()
+    assert ctrl[24].item() == 0b101 and ctrl[0].item() == 1 and ctrl[2].item() == 1
+    opt.apply(ref, {"w": ((slots[0] + slots[2]) / 2).cpu()})
+    # update 2: worker 2's stamp is stale (still 1): only 0 and 1 count
+    ctrl[16:19] = torch.tensor([2, 2, 1], dtype=torch.int32)
+    nat.adam_apply_backup(w, m, v, None, ptrs, 3, 2, n, pieces, 0.01, ctrl[0:], ctrl[16:], ctrl[24:], ctrl[7:], ctrl[2:], ctrl[3:])
+    torch.cuda.synchronize()
+    assert ctrl[24].item() == 0b011 and ctrl[3].item() == 2
+    opt.apply(ref, {"w": ((slots[0] + slots[1]) / 2).cpu()})
+    assert torch.allclose(w.cpu(), ref["w"], atol=1e-5, rtol=1e-5)
+    # released ps: shutdown set, nobody delivered -> empty mask, nothing applied
+    ctrl[7] = 1
+    before = w.clone()
+    nat.adam_apply_backup(w, m, v, None, ptrs, 3, 2, n, pieces, 0.01, ctrl[0:], ctrl[16:], ctrl[24:], ctrl[7:], ctrl[2:], ctrl[3:])
+    torch.cuda.synchronize()
+    assert ctrl[24].item() == 0 and ctrl[0].item() == 2 and torch.equal(w, before)
