@@ -6,10 +6,8 @@ its own stream and the slowest rank's total counts.
 """
 from __future__ import annotations
 
-import json
 import os
 import sys
-import time
 from typing import Optional
 
 import numpy as np

@@ -16,7 +16,7 @@ TF-style boolean syntax is accepted: ``--sync_replicas=False``,
 from __future__ import annotations
 
 import dataclasses
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Any, Dict, List, Optional, Sequence
 
 

@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint, c_ulonglong, c_void_p, POINTER
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint, c_ulonglong, c_void_p
 from typing import Optional
 
 import torch
@@ -49,8 +49,6 @@ def lib() -> ctypes.CDLL:
         _lib = ctypes.CDLL(_LIB_PATH)
         _lib.tfd_last_error.restype = c_char_p
         _lib.tfd_version.restype = c_int
-        for name in dir(_lib):
-            pass
     return _lib
 
 

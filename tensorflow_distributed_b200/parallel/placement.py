@@ -14,7 +14,7 @@ from __future__ import annotations
 from dataclasses import dataclass
 from typing import Dict, List, Sequence, Tuple
 
-from ..models.spec import ModelSpec, VariableSpec
+from ..models.spec import ModelSpec
 
 ARENA_ALIGN = 64  # elements; keeps every piece 256-byte aligned in the fp32 arena
 

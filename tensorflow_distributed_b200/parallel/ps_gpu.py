@@ -23,12 +23,11 @@ from __future__ import annotations
 from dataclasses import dataclass
 from typing import Dict, List, Optional
 
-import numpy as np
 import torch
 import torch.distributed as dist
 
-from ..engine_native import (CTRL_ARRIVE, CTRL_GSTEP, CTRL_PUSHBLK, CTRL_T, CTRL_VERSION, NativeEngine, ShardState,
-                             Workspace, needs_shadow, _pad8)
+from ..engine_native import (CTRL_ARRIVE, CTRL_GSTEP, CTRL_T, CTRL_VERSION, NativeEngine, ShardState, Workspace,
+                             needs_shadow, _pad8)
 from ..models.spec import ModelSpec
 from ..ops import native as nat
 from .placement import Placement
