@@ -8,6 +8,7 @@
 // applied updates), written with release and read with acquire semantics at system scope.
 #include "../include/tfd_b200.h"
 #include "tfd_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -337,7 +338,12 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
   long long blocks = ((n - (skip_end - skip_begin)) / 8 + 255) / 256;
   if (blocks < 1) blocks = 1;
   // finalize == 0: the early launch runs next to tcgen05 kernels; two blocks per SM leave them the registers
-  const long long cap = finalize ? 148 * 3 : 148 * 2;
+  static const long long early_cap = [] {
+    const char* e = getenv("TFD_EARLY_ADAM_BLOCKS");  // tuning knob: how many SM slots the overlapped pass may take
+    const long long v = e ? atoll(e) : 0;
+    return v > 0 ? v : 148LL * 2;
+  }();
+  const long long cap = finalize ? 148 * 3 : early_cap;
   if (blocks > cap) blocks = cap;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
   TFD_CUDA_CHECK(tfd_launch(adam_apply_kernel, dim3((unsigned)blocks), dim3(256), 0, ST(stream), a, pt));
   TFD_LAUNCH_CHECK();

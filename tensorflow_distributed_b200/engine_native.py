@@ -11,6 +11,8 @@ kernel); fp32 gradients.
 """
 from __future__ import annotations
 
+import os
+
 from typing import Dict, List, Optional
 
 import numpy as np
@@ -146,7 +148,7 @@ class NativeEngine:
 
     def __init__(self, spec: ModelSpec, learning_rate: float = 0.01, seed: int = 0, init_stddev: float = 1.0,
                  device: Optional[str] = None, use_graphs: bool = True, conv2_ref: bool = False,
-                 early_adam: bool = False):
+                 early_adam: Optional[bool] = None):
         if not torch.cuda.is_available():
             raise nat.NativeError("NativeEngine needs a CUDA device (backend=cpu selects the oracle engine)")
         nat.lib()
@@ -164,6 +166,8 @@ class NativeEngine:
         self.ws: Dict[int, Workspace] = {}
         # Launching wd1's Adam pass early (under the conv backward chain) was measured: the step stays at ~0.120 ms
         # because the overlapped kernels then contend for registers / DRAM (profiles/ANALYSIS.md); off by default.
+        if early_adam is None:
+            early_adam = os.environ.get("TFD_EARLY_ADAM", "0") == "1"
         self.early_adam_var = "weights/wd1" if (spec.kind == "cnn" and early_adam) else None
         self.init_variables(seed, init_stddev)
 

@@ -45,6 +45,7 @@ def backward(eng, ws: Workspace) -> None:
         # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
         eng.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
     main.wait_stream(s2)  # the zeroed accumulators (d(bc2) is accumulated below)
+    early = eng.early_adam_var == "weights/wd1" and eng._training_apply
     if getattr(eng, "fuse_dgrad_pool", False):
         # fc1 dgrad fused with ReLU' and the 2x2 max-pool backward in the GEMM epilogue.  Measured (B=128): 25.6 us
         # for the fused kernel (it cannot use split-K, so only 49 CTAs) vs 12.4 + 9.4 us for the two kernels below.
@@ -54,12 +55,15 @@ def backward(eng, ws: Workspace) -> None:
         # pool2 / ReLU backward kernel
         eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
                        split_stride=B * 3136, ld_out=3136)
+        if early:
+            s1.wait_stream(main)  # the old weights have been read; wd1's Adam pass may overwrite them from here on
         nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, eng.G("biases/bc2"), B, nsplit=ws.dg_splits,
                       split_stride=B * 3136)
-    if eng.early_adam_var == "weights/wd1" and eng._training_apply:
+    if early:
         # wd1 is 98% of the parameter bytes: its Adam pass may start as soon as its gradient is complete and the
-        # dgrad above has read the old weights (measured: no gain, see profiles/ANALYSIS.md; off by default)
-        s1.wait_stream(main)
+        # dgrad above has read the old weights (see profiles/ANALYSIS.md; off by default)
+        if getattr(eng, "fuse_dgrad_pool", False):
+            s1.wait_stream(main)
         with torch.cuda.stream(s1):
             eng._apply_early("weights/wd1")
     s2.wait_stream(main)
