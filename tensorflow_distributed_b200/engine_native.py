@@ -273,6 +273,15 @@ class NativeEngine:
         from .models import cnn
         cnn.forward(self, ws, training, keep_prob, mask_out)
 
+    def _capture_stream(self):
+        """Stream the step graph is captured on.  With TFD_PRIO=1 it has the highest priority, so the kernels of the
+        critical path (everything on the main branch) get SMs before the weight-gradient kernels on the side
+        branches (default priority) whenever both are ready and cannot be co-resident."""
+        if not hasattr(self, "_cap"):
+            prio = -5 if os.environ.get("TFD_PRIO", "0") == "1" else 0
+            self._cap = torch.cuda.Stream(device=self.device, priority=prio)
+        return self._cap
+
     def _side_streams(self):
         if not hasattr(self, "_sides"):
             self._sides = [torch.cuda.Stream(device=self.device) for _ in range(2)]
@@ -343,7 +352,7 @@ class NativeEngine:
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
             before = nat.launch_count
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, stream=self._capture_stream()):
                 self._sequence(ws, mode, keep_prob)
             ws.graphs[key] = g
             ws.graph_kernels = getattr(ws, "graph_kernels", {})
