@@ -49,6 +49,9 @@ struct GemmParams {
   int M, N, K;          // logical problem
   int kblocks;          // ceil(K / BK)
   int splits;           // gridDim.z
+  int stages;           // pipeline depth actually used (<= Cfg::kStages): short K loops take less shared memory, so
+                        // several CTAs fit on an SM and one CTA's store drain overlaps another's loads
+  int bar_off;          // byte offset of the barrier block behind max(stages * stage bytes, epilogue staging bytes)
   int mode;             // TFD_EPI_*
   float alpha;
   float* out_f32;
@@ -85,7 +88,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.bar_off);
+  const int nstages = p.stages;
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tmem_full_bar = empty_bar + C::kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
@@ -100,7 +104,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmBs.m[0]);
-    for (int s = 0; s < C::kStages; ++s) {
+    for (int s = 0; s < nstages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
@@ -159,7 +163,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
           for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmBs.m[s], &full_bar[stage], n0 + c * 64, krow);
         }
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -183,7 +187,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           umma_bf16(tmem_base, da, db, idesc, (kb > kb_begin || ks > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
       umma_commit(tmem_full_bar);
     }
@@ -397,7 +401,19 @@ int launch(const CUtensorMap& tmA, const TmapArray& tmBs, const GemmParams& p, c
     attr_set = true;
   }
   dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, p.splits);
-  TFD_CUDA_CHECK(tfd_launch(kern, grid, dim3(kThreads), C::kSmemBytes, stream, tmA, tmBs, p, sg));
+  GemmParams q = p;
+  const int per_split = (p.kblocks + p.splits - 1) / p.splits;
+  q.stages = per_split < C::kStages ? per_split : C::kStages;
+  size_t staging = 0;  // the coalesced store epilogues stage the tile in the (then idle) pipeline buffers
+  if (p.mode == TFD_EPI_STORE_F32) staging = (size_t)BM * (BN + 4) * 4;
+  if (p.mode == TFD_EPI_STORE_BF16) staging = (size_t)BM * (BN * 2 + 16);
+  size_t data = (size_t)q.stages * C::kStageBytes;
+  if (data < staging) data = staging;
+  data = (data + 1023) & ~size_t(1023);
+  q.bar_off = (int)data;
+  const size_t smem = data + 1024 /*align slack*/ + 256 /*barriers*/;
+  TFD_REQUIRE(smem <= (size_t)C::kSmemBytes, "gemm: shared memory %zu exceeds the configured maximum", smem);
+  TFD_CUDA_CHECK(tfd_launch(kern, grid, dim3(kThreads), smem, stream, tmA, tmBs, q, sg));
   return 0;
 }
 

@@ -10,7 +10,12 @@ from torch.profiler import ProfilerActivity, profile
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from tensorflow_distributed_b200.engine_native import NativeEngine  # noqa: E402
-from tensorflow_distributed_b200.models.spec import cnn_spec  # noqa: E402
+from tensorflow_distributed_b200.models.spec import cnn_spec, mlp_spec  # noqa: E402
+
+MODEL = os.environ.get("TFD_MODEL", "cnn")
+SPEC = cnn_spec() if MODEL == "cnn" else mlp_spec(int(os.environ.get("TFD_HIDDEN", "8192")), int(os.environ.get("TFD_LAYERS", "4")))
+KEEP = 0.75 if MODEL == "cnn" else 1.0
+STD = 1.0 if MODEL == "cnn" else 0.05
 
 world = int(os.environ.get("WORLD_SIZE", "1"))
 rank = int(os.environ.get("RANK", "0"))
@@ -20,23 +25,23 @@ if world > 1:  # under torchrun: colocated ps shards, one rank per GPU; rank 0 p
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local))
-    eng = GpuClusterEngine(cnn_spec(), Topology.make(world, os.environ.get("TFD_LAYOUT", "colocated")), rank,
-                           "cuda:%d" % local, init_stddev=1.0, pull_mode=os.environ.get("TFD_PULL", "auto"))
+    eng = GpuClusterEngine(SPEC, Topology.make(world, os.environ.get("TFD_LAYOUT", "colocated")), rank,
+                           "cuda:%d" % local, init_stddev=STD, pull_mode=os.environ.get("TFD_PULL", "auto"))
 else:
-    eng = NativeEngine(cnn_spec(), init_stddev=1.0)
+    eng = NativeEngine(SPEC, init_stddev=STD)
 rng = np.random.RandomState(rank)
 x = rng.rand(128, 784).astype(np.float32)
 y = np.eye(10, dtype=np.float32)[rng.randint(0, 10, size=128)]
 ws = eng.workspace(128)
 eng.load_batch(ws, x, y)
 for _ in range(5):
-    eng.train_step_resident(ws, 0.75)
+    eng.train_step_resident(ws, KEEP)
 torch.cuda.synchronize()
 flush = torch.empty(64 * 1024 * 1024, device="cuda")
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(3):
         flush.fill_(1.0)
-        eng.train_step_resident(ws, 0.75)
+        eng.train_step_resident(ws, KEEP)
     torch.cuda.synchronize()
 if world > 1:
     dist.barrier()
