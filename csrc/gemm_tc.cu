@@ -21,6 +21,7 @@
 //                 worker's staging slot on the owner shard (no local gradient copy, no separate push of it)
 #include "../include/tfd_b200.h"
 #include "tfd_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -404,6 +405,15 @@ int launch(const CUtensorMap& tmA, const TmapArray& tmBs, const GemmParams& p, c
   GemmParams q = p;
   const int per_split = (p.kblocks + p.splits - 1) / p.splits;
   q.stages = per_split < C::kStages ? per_split : C::kStages;
+  static const int cap_kb = [] {  // tuning knob: cap the pipeline so two CTAs (of this or another kernel) share an SM
+    const char* e = getenv("TFD_GEMM_SMEM_KB");
+    return e ? atoi(e) : 0;
+  }();
+  if (cap_kb > 0) {
+    int cap_stages = (cap_kb * 1024 - 1280) / C::kStageBytes;
+    if (cap_stages < 2) cap_stages = 2;
+    if (q.stages > cap_stages) q.stages = cap_stages;
+  }
   size_t staging = 0;  // the coalesced store epilogues stage the tile in the (then idle) pipeline buffers
   if (p.mode == TFD_EPI_STORE_F32) staging = (size_t)BM * (BN + 4) * 4;
   if (p.mode == TFD_EPI_STORE_BF16) staging = (size_t)BM * (BN * 2 + 16);
