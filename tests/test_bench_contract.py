@@ -31,3 +31,17 @@ def test_performance_table_schema_matches_the_reference_file():
     txt = performance_table([(40, 200.0, 90.0, 0.01), (60, 290.0, 93.0, 0.01)])
     assert txt.splitlines()[0] == "Steps ,Time ,Accuracy, Learning rate"  # /root/reference/performance:1
     assert txt.splitlines()[1].split()[0] == "40" and txt.splitlines()[2].split()[-1] == "0.01"
+
+
+def test_committed_performance_record_has_the_reference_schema():
+    """`performance` at the repo root mirrors /root/reference/performance:1-6: a header and five rows of
+    steps / time / accuracy / learning rate at 40..120 steps."""
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lines = [l for l in open(os.path.join(root, "performance")).read().splitlines() if l and not l.startswith("#")]
+    assert lines[0] == "Steps ,Time ,Accuracy, Learning rate"
+    rows = [l.split() for l in lines[1:]]
+    assert [int(r[0]) for r in rows] == [40, 60, 80, 100, 120]
+    times = [float(r[1]) for r in rows]
+    assert times == sorted(times) and all(float(r[3]) == 0.01 for r in rows)
+    assert all(0.0 <= float(r[2]) <= 100.0 for r in rows)
