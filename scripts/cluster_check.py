@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--pull", default="auto")
     ap.add_argument("--grad_dtype", default="fp32")
     ap.add_argument("--replicas", type=int, default=0)
+    ap.add_argument("--digest", action="store_true", help="rank 0 prints a SHA-256 of the final parameters and Adam slots")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -105,6 +106,18 @@ def main():
     if eng.is_worker and not (losses[-1] < losses[0]):
         ok = False
         msgs.append("rank %d loss did not decrease: %.4f -> %.4f" % (rank, losses[0], losses[-1]))
+    if a.digest:
+        import hashlib
+        final = eng.get_params()
+        adam = eng.get_adam_state()
+        if rank == 0:
+            h = hashlib.sha256()
+            for k in sorted(final):
+                h.update(final[k].detach().float().cpu().contiguous().numpy().tobytes())
+            for slot in ("m", "v"):
+                for k in sorted(adam[slot]):
+                    h.update(adam[slot][k].detach().float().cpu().contiguous().numpy().tobytes())
+            print("DIGEST %s" % h.hexdigest(), flush=True)
     flag = torch.tensor([0 if ok else 1], device=device)
     dist.all_reduce(flag)
     print("rank %d %s %s losses %.4f -> %.4f acc %.3f gs %d %s" % (rank, eng.describe(), "OK" if ok else "FAIL",

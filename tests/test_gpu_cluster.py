@@ -31,6 +31,20 @@ def test_two_gpu_sync_ps(layout, model, pull):
 
 
 @needs2
+def test_two_gpu_fused_pull_is_bit_identical_to_copy_then_gemm():
+    """the pull-fused GEMM (weight tiles TMA-loaded from the owner GPUs inside the kernel) against
+    copy-then-unfused (the shadow copied to a local mirror first, same GEMM on local memory).  The MLP path has no
+    floating-point atomics, so after 12 synchronous steps parameters and Adam slots must agree bit for bit."""
+    import re
+    digests = []
+    for pull in ("fused", "prefetch"):
+        out = _torchrun(2, ["--layout", "colocated", "--model", "mlp", "--pull", pull, "--digest"], 29617)
+        assert "OK" in out and "FAIL" not in out
+        digests.append(re.search(r"DIGEST ([0-9a-f]{64})", out).group(1))
+    assert digests[0] == digests[1]
+
+
+@needs2
 def test_two_gpu_async_apply_on_arrival_counts_every_update():
     out = _torchrun(2, ["--layout", "dedicated", "--async_mode"], 29613)
     assert "OK" in out and "FAIL" not in out and "async" in out
