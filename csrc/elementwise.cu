@@ -60,12 +60,20 @@ __global__ void cast_bf16_kernel(const float* __restrict__ src, long long ld_src
 // conv1 forward: 5x5 SAME, 1 -> 32, + bias + ReLU + 2x2 max pool.  grid (B, 2): half image per block.
 // warp = pooled row, lane = output channel; the 6x6 input window is a shared-memory broadcast.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                                        const float* __restrict__ b, bf16* __restrict__ out,
-                                                        unsigned char* __restrict__ amax) {
+//
+// Gated form (parameter server on other GPUs): w and b point into the owner shards' peer-mapped arenas.  The block
+// first loads its input patch (local), then waits until the owners' parameter version flags have reached this
+// worker's step counter, and only then reads the 3.3 KB of filter + bias over NVLink, once per block through shared
+// memory.  The pull of conv1's parameters is thereby inside the first kernel of the step instead of in a copy
+// kernel in front of it.
+__global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict__ x, const float* w, const float* b,
+                                                        bf16* __restrict__ out, unsigned char* __restrict__ amax,
+                                                        const unsigned* gate0, const unsigned* gate1,
+                                                        const unsigned* want_ptr) {
   grid_dep_wait();
   grid_dep_launch();
   __shared__ __align__(16) float patch[18][32];  // input rows 14*half-2 .. +17, cols -2 .. 29
+  __shared__ __align__(16) float wsm[26 * 32];   // gated form only: filter [25][32] + bias [32]
   const int n = blockIdx.x, half = blockIdx.y;
   for (int i = threadIdx.x; i < 18 * 32; i += blockDim.x) {
     const int pr = i >> 5, pc = i & 31;
@@ -74,10 +82,29 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
   }
   const int c = threadIdx.x & 31, prow = threadIdx.x >> 5;  // pooled row inside the half: 0..6
   float wr[25];
+  float bias;
+  if (gate0) {
+    if (threadIdx.x == 0) {
+      const unsigned want = *want_ptr;
+      spin_until_ge(gate0, want, "conv1: parameter version");
+      if (gate1) spin_until_ge(gate1, want, "conv1: parameter version (bias shard)");
+    }
+    __syncthreads();
+    if (threadIdx.x < 200) {
+      reinterpret_cast<float4*>(wsm)[threadIdx.x] = __ldcg(reinterpret_cast<const float4*>(w) + threadIdx.x);
+    } else if (threadIdx.x < 208) {
+      reinterpret_cast<float4*>(wsm)[threadIdx.x] = __ldcg(reinterpret_cast<const float4*>(b) + (threadIdx.x - 200));
+    }
+    __syncthreads();
 #pragma unroll
-  for (int t = 0; t < 25; ++t) wr[t] = w[t * 32 + c];
-  const float bias = b[c];
-  __syncthreads();
+    for (int t = 0; t < 25; ++t) wr[t] = wsm[t * 32 + c];
+    bias = wsm[800 + c];
+  } else {
+#pragma unroll
+    for (int t = 0; t < 25; ++t) wr[t] = w[t * 32 + c];
+    bias = b[c];
+    __syncthreads();
+  }
   const int ph = half * 7 + prow;
   for (int pw = 0; pw < 14; ++pw) {
     float win[6][6];  // 8-byte shared loads: 18 LDS.64 instead of 36 LDS.32 (the kernel is LDS-issue bound)
@@ -536,7 +563,19 @@ extern "C" int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long
 
 extern "C" int tfd_conv1_fwd(const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
                              void* stream) {
-  TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel, dim3(B, 2), dim3(224), 0, ST(stream), x, w, b, (bf16*)pool_out, argmax));
+  TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel, dim3(B, 2), dim3(224), 0, ST(stream), x, w, b, (bf16*)pool_out, argmax,
+                            (const unsigned*)nullptr, (const unsigned*)nullptr, (const unsigned*)nullptr));
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int tfd_conv1_fwd_gated(const float* x, const float* w_peer, const float* b_peer, void* pool_out,
+                                   unsigned char* argmax, int B, const unsigned* gate_w, const unsigned* gate_b,
+                                   const unsigned* want_ptr, void* stream) {
+  TFD_REQUIRE(gate_w != nullptr && want_ptr != nullptr, "conv1_fwd_gated: version flag and step counter are required");
+  TFD_REQUIRE(((uintptr_t)w_peer & 15) == 0 && ((uintptr_t)b_peer & 15) == 0, "conv1_fwd_gated: w/b must be 16-byte aligned");
+  TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel, dim3(B, 2), dim3(224), 0, ST(stream), x, w_peer, b_peer, (bf16*)pool_out,
+                            argmax, gate_w, gate_b == gate_w ? (const unsigned*)nullptr : gate_b, want_ptr));
   TFD_LAUNCH_CHECK();
   return 0;
 }

@@ -95,6 +95,10 @@ int tfd_random_normal(float* out, long long n, unsigned long long seed, float st
  * out bf16 [B,14,14,32]; argmax u8 [B,14,14,32] (0..3 = position inside the 2x2 window). */
 int tfd_conv1_fwd(const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
                   void* stream);
+/* Same op with the parameter pull inside the kernel: w_peer / b_peer point into the owner shards' (peer-mapped)
+ * arenas; every block waits until *gate_w (and *gate_b, if it is another shard) >= *want_ptr before it reads them. */
+int tfd_conv1_fwd_gated(const float* x, const float* w_peer, const float* b_peer, void* pool_out, unsigned char* argmax,
+                        int B, const unsigned* gate_w, const unsigned* gate_b, const unsigned* want_ptr, void* stream);
 /* conv1 filter/bias gradient with pool+ReLU backward folded in.  dpool fp32 [B,14,14,32] is d(loss)/d(pool1).
  * dw fp32 [25,32] and db fp32 [32] are ACCUMULATED with atomics (zero them first). */
 int tfd_conv1_wgrad(const float* x, const float* dpool, const void* pool_out, const unsigned char* argmax, float* dw,

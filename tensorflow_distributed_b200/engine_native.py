@@ -275,6 +275,9 @@ class NativeEngine:
 
     _prio_default = "0"  # measured neutral on one GPU (0.1213 vs 0.1207 ms); the ps cluster engine turns it on
 
+    def conv1_fwd(self, ws: "Workspace") -> None:
+        nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, ws.B)
+
     def _capture_stream(self):
         """Stream the step graph is captured on.  With TFD_PRIO=1 it has the highest priority, so the kernels of the
         critical path (everything on the main branch) get SMs before the weight-gradient kernels on the side

@@ -20,7 +20,7 @@ def forward(eng, ws: Workspace, training: bool, keep_prob: float, mask_out=None)
         with torch.cuda.stream(s2):
             nat.zero_multi([eng.G("weights/wc1"), eng.G("biases/bc1"), eng.G("weights/wc2"),
                             eng.G("biases/bc2")])
-    nat.conv1_fwd(ws.x, eng.P("weights/wc1"), eng.P("biases/bc1"), ws.pool1, ws.am1, B)
+    eng.conv1_fwd(ws)  # (on a ps cluster the pull of wc1/bc1 may be folded into this kernel)
     nat.conv2_fwd(ws.pool1, eng.S("weights/wc2"), eng.P("biases/bc2"), ws.pool2, ws.am2, B, ref=eng.conv2_ref)
     eng.gemm_fwd("weights/wd1", ws.pool2.view(B, 3136), B, ws.fc1acc, mode=nat.EPI_STORE_F32, bn=64,
                   splits=ws.fc1_splits, split_stride=B * 1024, ld_out=1024)

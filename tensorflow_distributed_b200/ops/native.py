@@ -166,6 +166,14 @@ def conv1_fwd(x, w, b, pool_out, argmax, B: int) -> None:
     _count()
 
 
+def conv1_fwd_gated(x, w_peer, b_peer, pool_out, argmax, B: int, gate_w, gate_b, want_ptr) -> None:
+    """conv1 block whose filter/bias are read from the owner shards (peer pointers, ints or tensors) once their
+    version flags have reached ``*want_ptr``: the pull of conv1's parameters inside the step's first kernel."""
+    _check(lib().tfd_conv1_fwd_gated(_p(x), _p(w_peer), _p(b_peer), _p(pool_out), _p(argmax), c_int(B), _p(gate_w),
+                                     _p(gate_b), _p(want_ptr), _stream()), "tfd_conv1_fwd_gated")
+    _count()
+
+
 def conv1_wgrad(x, dpool, pool_out, argmax, dw, db, B: int) -> None:
     _check(lib().tfd_conv1_wgrad(_p(x), _p(dpool), _p(pool_out), _p(argmax), _p(dw), _p(db), c_int(B), _stream()),
            "tfd_conv1_wgrad")

@@ -20,6 +20,8 @@ ps-only and never run a model kernel, like the reference's ps process that sits 
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass
 from typing import Dict, List, Optional
 
@@ -325,12 +327,41 @@ class GpuClusterEngine(NativeEngine):
                           out_ptrs=d["slot"], bn=bn)
 
     # ---- step pieces -----------------------------------------------------------------------
+    @property
+    def fold_pull(self) -> bool:
+        """CNN, plain sync mode: conv1 reads its filter/bias straight from the owner shards (gated on their version
+        flags inside the kernel) and the copy of the other small tensors runs next to it on a side branch, joined
+        before conv2 -- instead of a pull kernel in front of the whole step.  TFD_FOLD_PULL=1 turns it on."""
+        return (self.spec.kind == "cnn" and not self.async_mode and not self.backup
+                and os.environ.get("TFD_FOLD_PULL", "0") == "1")
+
+    def conv1_fwd(self, ws) -> None:
+        if not self.fold_pull:
+            return super().conv1_fwd(ws)
+        (pw,), (pb,) = self.placement.pieces["weights/wc1"], self.placement.pieces["biases/bc1"]
+        nat.conv1_fwd_gated(ws.x, self._w_ptr(pw.shard, pw.offset), self._w_ptr(pb.shard, pb.offset), ws.pool1, ws.am1,
+                            ws.B, self._ctrl_ptr(pw.shard, CTRL_VERSION), self._ctrl_ptr(pb.shard, CTRL_VERSION),
+                            self.step_ptr())
+        if getattr(self, "_sp_pending", False):  # everything after conv1 reads the mirrors
+            torch.cuda.current_stream().wait_stream(self._sp_stream)
+            self._sp_pending = False
+
     def _pre_step(self, ws, training: bool) -> None:
         """Pull (X1): small tensors are copied once the owning shard's version has caught up with this
         worker's step counter; the same kernel thereby waits for every shard (slots are free to overwrite)."""
         if self._prefetch:
             self._launch_prefetch(training)
         p = self._pull
+        if self.fold_pull:
+            main = torch.cuda.current_stream()
+            if not hasattr(self, "_sp_stream"):
+                self._sp_stream = torch.cuda.Stream(device=self.device)
+            self._sp_stream.wait_stream(main)
+            with torch.cuda.stream(self._sp_stream):
+                nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
+                               want_ptr=self.step_ptr())
+            self._sp_pending = True
+            return
         if self.backup and not training:
             # evaluation after training: my last push may carry a tag the ps will never apply (it has already done
             # its train_steps updates), so read whatever is published now

@@ -152,6 +152,29 @@ def test_conv1_fwd_and_wgrad(nat, B):
     assert rel_err(db, bl.grad) < 2e-3
 
 
+def test_conv1_fwd_gated_equals_plain_once_the_version_is_there(nat):
+    """The gated form (parameters read from the owner shard inside the kernel after its version flag has reached
+    the worker's step counter) computes exactly what the plain form computes; flags already satisfied here."""
+    B = 37
+    torch.manual_seed(8)
+    x = torch.rand(B, 784, device=DEV)
+    w = torch.randn(25, 32, device=DEV)
+    b = torch.randn(32, device=DEV)
+    outs = []
+    for gated in (False, True):
+        pool = torch.zeros(B, 14, 14, 32, device=DEV, dtype=torch.bfloat16)
+        am = torch.zeros(B, 14, 14, 32, device=DEV, dtype=torch.uint8)
+        if gated:
+            flags = torch.tensor([7, 9], dtype=torch.int32, device=DEV)  # versions of the w shard and the b shard
+            want = torch.tensor([7], dtype=torch.int32, device=DEV)
+            nat.conv1_fwd_gated(x, w, b, pool, am, B, flags[0:], flags[1:], want)
+        else:
+            nat.conv1_fwd(x, w, b, pool, am, B)
+        torch.cuda.synchronize()
+        outs.append((pool, am))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
 def _conv2_inputs(B, seed):
     torch.manual_seed(seed)
     inp = bf(torch.rand(B, 14, 14, 32, device=DEV))
