@@ -11,7 +11,7 @@ if __name__ == "__main__":
     kw = {}
     casts = {"learning_rate": float, "training_iters": int, "batch_size": int, "display_step": int,
              "dropout": float, "train_flag": int, "nt": int, "val_batch": int, "seed": int,
-             "hidden_units": int, "mlp_layers": int, "init_stddev": float}
+             "hidden_units": int, "mlp_layers": int, "init_stddev": float, "trace_start": int, "trace_steps": int}
     for a in sys.argv[1:]:
         k, v = a.lstrip("-").split("=", 1)
         if k == "synthetic":

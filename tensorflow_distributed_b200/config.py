@@ -57,6 +57,9 @@ class Flags:
     sync_init_tokens: int = -1      # get_init_tokens_op(num_tokens); -1 => replicas_to_aggregate (m:233)
     layout: str = "auto"            # GPU cluster: auto | colocated | dedicated ps GPUs
     grad_dtype: str = "fp32"        # dtype of pushed gradients on the GPU path: fp32 | bf16
+    trace_file: str = ""            # write a Chrome trace of a window of steps (utils/trace.py)
+    trace_start: int = 2            # first local step of the window (1-based)
+    trace_steps: int = 3            # length of the window
 
     def replace(self, **kw) -> "Flags":
         return dataclasses.replace(self, **kw)

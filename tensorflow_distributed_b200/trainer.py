@@ -26,6 +26,7 @@ from .engine import OracleEngine, make_engine
 from .models.spec import make_spec
 from .parallel.placement import Placement
 from .supervisor import Supervisor
+from .utils.trace import StepTracer
 
 
 # --------------------------------------------------------------------------
@@ -35,8 +36,10 @@ def run_single(*, model: str = "cnn", learning_rate: float = 0.01, training_iter
                batch_size: int = 128, display_step: int = 10, dropout: float = 0.75, train_flag: int = 1,
                nt: int = 50, val_batch: int = 100, data_dir: str = "MNIST_data/", synthetic: Optional[bool] = None,
                backend: str = "auto", seed: int = 0, hidden_units: int = 100, mlp_layers: int = 1,
-               train_dir: str = "", init_stddev: float = 1.0, log: Callable[[str], None] = print) -> dict:
+               train_dir: str = "", init_stddev: float = 1.0, trace_file: str = "", trace_start: int = 2,
+               trace_steps: int = 3, log: Callable[[str], None] = print) -> dict:
     mnist = data_mod.read_data_sets(data_dir, True, synthetic, seed)
+    tracer = StepTracer(trace_file, trace_start, trace_steps, log)
     spec = make_spec(model, hidden_units, mlp_layers)
     start_time = time.time()  # the reference starts its timer before session creation (single:102)
     eng = make_engine(spec, backend, learning_rate=learning_rate, seed=seed, init_stddev=init_stddev)
@@ -53,13 +56,16 @@ def run_single(*, model: str = "cnn", learning_rate: float = 0.01, training_iter
     if train_flag == 1:
         while step * batch_size < training_iters:
             batch_x, batch_y = mnist.train.next_batch(batch_size)
+            tracer.before(step)
             eng.train_step(batch_x, batch_y, dropout)
+            tracer.after(step)
             if step % display_step == 0:
                 loss = eng.eval_loss(batch_x, batch_y)
                 losses.append(loss)
                 log("Iter " + str(step * batch_size) + ", Minibatch Loss= " + "{:.6f}".format(loss))
             step += 1
         eng.synchronize()
+        tracer.close()
         log("Optimization Finished!")
         training_end_time = time.time()
         log("--- %s seconds Time for Training ---" % (training_end_time - start_time))
@@ -77,7 +83,8 @@ def run_single(*, model: str = "cnn", learning_rate: float = 0.01, training_iter
     log("--- %s seconds Time for Inference ---" % (testing_end_time - training_end_time))
     return {"losses": losses, "mean_accuracy": mean_accuracy, "steps": step - 1,
             "train_seconds": training_end_time - start_time,
-            "inference_seconds": testing_end_time - training_end_time, "engine": eng, "data_source": mnist.source}
+            "inference_seconds": testing_end_time - training_end_time, "engine": eng, "data_source": mnist.source,
+            "trace": tracer.written}
 
 
 # --------------------------------------------------------------------------
@@ -175,8 +182,11 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
     last_saved = 0
     token = client.global_step()  # local_step_init_op: local step starts at the global step
     step = token
+    tracer = StepTracer(flags.trace_file and "%s.worker%d" % (flags.trace_file, flags.task_index), flags.trace_start,
+                        flags.trace_steps, log)
     while True:
         batch_xs, batch_ys = mnist.train.next_batch(flags.batch_size)
+        tracer.before(local_step + 1)
         params = client.pull()
         _maybe_inject_fault(flags, local_step)
         _, grads, _ = eng.loss_and_grads(batch_xs, batch_ys, flags.keep_prob, params=params)
@@ -187,6 +197,7 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
         else:
             step = client.push(grads, 0, sync=False)
         local_step += 1
+        tracer.after(local_step)
         now = time.time()
         log("%f: Worker %d: training step %d done (global step: %d)" % (now, flags.task_index, local_step, step))
         if is_chief and flags.train_dir and flags.save_checkpoint_steps > 0 and \
@@ -198,6 +209,7 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
             last_saved = step
         if step >= flags.train_steps:
             break
+    tracer.close()
     time_end = time.time()
     log("Training ends @ %f" % time_end)
     training_time = time_end - time_begin

@@ -44,8 +44,11 @@ def test_sync_two_workers_equals_large_batch_single_process(tmp_path, free_port)
     steps = 3
     extra = ["--model=mlp", "--hidden_units=32", "--init_stddev=0.1", "--train_steps=%d" % steps, "--keep_prob=1.0",
              "--sync_init_tokens=0", "--batch_size=64", "--validation_batch_size=200", "--train_dir=%s" % tmp_path,
-             "--log_device_placement"]
+             "--log_device_placement", "--trace_file=%s" % (tmp_path / "tr.json"), "--trace_start=2", "--trace_steps=1"]
     ps_out, w1_out, w2_out = _run3(free_port, extra)
+    for t in (0, 1):  # every worker traced its own step 2 (pull, forward/backward on the oracle, push)
+        assert os.path.getsize(str(tmp_path / ("tr.json.worker%d" % t))) > 0
+        assert "trace: steps 2..2 written to" in (w1_out, w2_out)[t]
     # log lines of the reference
     assert "job name = ps" in ps_out and "task index = 0" in ps_out
     assert "Worker 0: Initializing session..." in w1_out
