@@ -670,15 +670,21 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
     time_begin = time.time()
     log("Training begins @ %f" % time_begin)
     local_step, step = 0, start_step
+    from ..utils.trace import StepTracer
+    tracer = StepTracer(flags.trace_file and "%s.worker%d" % (flags.trace_file, widx), flags.trace_start,
+                        flags.trace_steps, log)  # a no-op unless --trace_file is given
     while step < flags.train_steps:
         batch_xs, batch_ys = mnist.train.next_batch(B)
         _maybe_inject_fault(flags, local_step)
+        tracer.before(local_step + 1)
         eng.train_step(batch_xs, batch_ys, flags.keep_prob)
         local_step += 1
+        tracer.after(local_step)
         # X5: strict sync knows the global step without asking; async / backup workers read it from shard 0
         step = (start_step + local_step) if (flags.sync_replicas and not eng.backup) else eng.global_step
         log("%f: Worker %d: training step %d done (global step: %d)" % (time.time(), widx, local_step, step))
     eng.synchronize()
+    tracer.close()
     time_end = time.time()
     log("Training ends @ %f" % time_end)
     log("Training elapsed time: %f s" % (time_end - time_begin))
