@@ -165,15 +165,31 @@ class GpuClusterEngine(NativeEngine):
                         for r in range(topo.world)]
         nat.set_slot_dtype(self.grad_dtype == "bf16")
         # ---- symmetric heap: allocate, exchange the 64-byte cudaIpc handles, map every ps rank's heap ----
-        self.heap_ptr, handle = nat.ipc_alloc(self.layouts[rank].total)
-        handles: List[Optional[bytes]] = [None] * topo.world
-        dist.all_gather_object(handles, handle)
-        self.peer_base: Dict[int, int] = {rank: self.heap_ptr}
+        self.mc_base = 0  # multicast (NVLS) alias of the heap; only the experimental symmetric-memory heap has one
         self._opened: List[int] = []
-        for r in topo.ps_ranks:
-            if r != rank:
-                self.peer_base[r] = nat.ipc_open(handles[r])
-                self._opened.append(self.peer_base[r])
+        if os.environ.get("TFD_HEAP", "ipc") == "symm":
+            # Experimental (not yet run on hardware): the heap comes from torch's symmetric-memory allocator (VMM
+            # allocations exchanged over the process group), which also yields the multicast address the NVLS
+            # plan in DESIGN.md needs.  Every rank allocates the same size; peers are addressed as before.
+            import torch.distributed._symmetric_memory as symm
+            total = max(l.total for l in self.layouts)
+            self._symm_buf = symm.empty(total, dtype=torch.uint8, device=self.device)
+            self._symm_buf.zero_()
+            torch.cuda.synchronize(self.device)
+            self._symm = symm.rendezvous(self._symm_buf, dist.group.WORLD)
+            self.heap_ptr = self._symm_buf.data_ptr()
+            self.peer_base: Dict[int, int] = {r: int(self._symm.buffer_ptrs[r]) for r in range(topo.world)}
+            if getattr(self._symm, "has_multicast_support", False):
+                self.mc_base = int(self._symm.multicast_ptr)
+        else:
+            self.heap_ptr, handle = nat.ipc_alloc(self.layouts[rank].total)
+            handles: List[Optional[bytes]] = [None] * topo.world
+            dist.all_gather_object(handles, handle)
+            self.peer_base = {rank: self.heap_ptr}
+            for r in topo.ps_ranks:
+                if r != rank:
+                    self.peer_base[r] = nat.ipc_open(handles[r])
+                    self._opened.append(self.peer_base[r])
         L = self.layouts[rank]
         self.ctrl = nat.tensor_from_ptr(self.heap_ptr + L.ctrl, 64, torch.int32, self.device)
         # ---- ps role ----
