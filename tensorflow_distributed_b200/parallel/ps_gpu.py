@@ -614,6 +614,10 @@ def run_gpu_cluster_task(flags, cluster, mnist, log) -> dict:
     gpus = [cluster.task_address(j, i).gpu_ordinal for j in ("ps", "worker") for i in range(cluster.num_tasks(j))]
     if len(set(gpus)) != len(gpus):
         raise ValueError("gpu cluster: every ps and worker task needs its own GPU (got %s)" % gpus)
+    if not torch.cuda.is_available() or torch.cuda.device_count() <= max(gpus):
+        raise RuntimeError("ps_hosts/worker_hosts name GPUs %s but this process sees %d CUDA device(s); use host:port "
+                           "entries with --backend=cpu for the CPU/gloo transport"
+                           % (sorted(gpus), torch.cuda.device_count() if torch.cuda.is_available() else 0))
     device = torch.device("cuda:%d" % addr.gpu_ordinal)
     torch.cuda.set_device(device)
     rank, world = cluster.rank_of(flags.job_name, flags.task_index), cluster.world_size

@@ -77,3 +77,14 @@ def test_replicas_to_aggregate_documented_default():
     assert cl.effective_replicas_to_aggregate(Flags(replicas_to_aggregate=None), 7) == 7
     assert cl.effective_replicas_to_aggregate(Flags(replicas_to_aggregate=0), 7) == 7
     assert cl.effective_replicas_to_aggregate(Flags(), 7) == 2
+
+
+def test_gpu_hosts_without_gpus_fail_with_a_clear_message():
+    """`gpu:<n>` host entries on a box without (enough) CUDA devices: a readable error, not a driver stack trace."""
+    import torch
+    if torch.cuda.is_available() and torch.cuda.device_count() >= 2:
+        pytest.skip("box has the GPUs the host lists name")
+    from tensorflow_distributed_b200.trainer import run_cluster
+    flags = parse_flags(["--ps_hosts=gpu:0", "--worker_hosts=gpu:1", "--job_name=worker", "--task_index=0"])
+    with pytest.raises(RuntimeError, match="name GPUs"):
+        run_cluster(flags, log=lambda s: None)
