@@ -91,6 +91,33 @@ _HELP = {
 }
 
 
+#: Help for the flags this framework adds (kept apart: ``_HELP`` is exactly the reference's flag set).
+_HELP_EXTRA = {
+    "model": "cnn (the reference's conv_net) or mlp (784 -> hidden_units x mlp_layers -> 10)",
+    "mlp_layers": "Hidden layers of the MLP",
+    "ps_shards": "Parameter shards (0 => one per ps task)",
+    "synthetic": "Use the deterministic MNIST-shaped synthetic set instead of idx files in data_dir",
+    "train_dir": "Checkpoint directory (chief saves, everybody restores on start); '' => fresh temp dir",
+    "precision": "bf16 tensor-core operands with fp32 master weights and accumulation",
+    "seed": "Seed of the parameter init, the data stream and dropout",
+    "keep_prob": "Dropout keep probability during training",
+    "backend": "auto | cpu (fp32 oracle) | cuda (sm_100a kernels)",
+    "save_checkpoint_steps": "Chief also saves every N global steps (0 => only when training ends)",
+    "validation_batches": "Validation batches after training",
+    "validation_batch_size": "Images per validation batch",
+    "init_stddev": "Standard deviation of the random_normal initialiser",
+    "step_timeout_secs": "Watchdog on every blocking wait of the cluster protocol",
+    "inject_fault": "Testing: stall:<task>:<secs> or kill:<task>:<local step>",
+    "log_device_placement": "Print the variable -> ps shard placement table",
+    "sync_init_tokens": "Tokens preloaded into the sync queue (-1 => replicas_to_aggregate)",
+    "layout": "GPU cluster: colocated (every GPU is worker + ps shard) or dedicated ps GPUs",
+    "grad_dtype": "Storage type of pushed gradients in the ps staging slots on the GPU path: fp32 | bf16",
+    "trace_file": "Write a Chrome trace (+ .txt per-op table) of a window of training steps",
+    "trace_start": "First local step of the traced window (1-based)",
+    "trace_steps": "Number of traced steps",
+}
+
+
 def _to_bool(s: str) -> bool:
     v = s.strip().lower()
     if v in ("1", "true", "t", "yes", "y"):
@@ -113,7 +140,7 @@ def help_text() -> str:
     lines = ["flags:"]
     d = Flags()
     for f in dataclasses.fields(Flags):
-        lines.append("  --%s (default %r) %s" % (f.name, getattr(d, f.name), _HELP.get(f.name, "")))
+        lines.append("  --%s (default %r) %s" % (f.name, getattr(d, f.name), _HELP.get(f.name) or _HELP_EXTRA.get(f.name, "")))
     return "\n".join(lines)
 
 

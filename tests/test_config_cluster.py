@@ -88,3 +88,10 @@ def test_gpu_hosts_without_gpus_fail_with_a_clear_message():
     flags = parse_flags(["--ps_hosts=gpu:0", "--worker_hosts=gpu:1", "--job_name=worker", "--task_index=0"])
     with pytest.raises(RuntimeError, match="name GPUs"):
         run_cluster(flags, log=lambda s: None)
+
+
+def test_every_flag_has_help_text():
+    from tensorflow_distributed_b200.config import _HELP, _HELP_EXTRA, flag_names
+    assert set(flag_names()) == set(_HELP) | set(_HELP_EXTRA)
+    assert not set(_HELP) & set(_HELP_EXTRA)
+    assert all(len(v) > 8 for v in list(_HELP.values()) + list(_HELP_EXTRA.values()))
