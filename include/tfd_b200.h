@@ -245,6 +245,33 @@ int tfd_push_multi_stamp(const void* const* srcs, void* const* dsts, const long 
 int tfd_pull_multi_tag(const void* const* srcs, void* const* dsts, const long long* ns, const unsigned* const* versions,
                        const unsigned* const* want_segs, int nseg, int tag_seg, unsigned* tag_out, void* stream);
 
+/* ---- parameter server over NVLS multicast (EXPERIMENTAL: host-checked, not yet run on hardware) ----
+ * Every GPU maps one symmetric heap at a unicast and at a multicast address (torch symmetric memory).  Workers
+ * write gradients into their own copy and signal with one multimem.red; the owner shard reads the gradient SUM
+ * with multimem.ld_reduce (ingress 1x instead of workers-x), applies TF-form Adam to its private master weights
+ * and stores the result into every worker's mirror with multimem.st (egress 1x); workers read parameters locally.
+ * One piece = the rows of one variable this shard owns. */
+typedef struct {
+  long long owner_off;  /* element offset in the owner's private w/m/v arenas                              */
+  long long numel;
+  int cols;
+  int ld_shadow;        /* 0: published in fp32 at mirror_off; else bf16 rows of ld_shadow at shadow_off   */
+  long long grad_off;   /* element offset in the (symmetric) gradient arena, single-shard layout            */
+  long long mirror_off; /* element offset in the (symmetric) fp32 mirror                                    */
+  long long shadow_off; /* element offset in the (symmetric) bf16 shadow mirror                             */
+} tfd_nvls_piece_t;
+/* adam = 1: wait until *arrive >= arrivals_per_step * (t+1), reduce, update, publish, version += 1 on every GPU.
+ * adam = 0: publish the current parameters only (initialisation / restore); no counter moves, the caller
+ *           synchronises on the host afterwards. */
+int tfd_nvls_apply(float* w, float* m, float* v, const float* mc_grad, float* mc_mirror_w, void* mc_mirror_shadow,
+                   const tfd_nvls_piece_t* pieces, int num_pieces, float scale, float lr, float beta1, float beta2,
+                   float eps, unsigned* t_counter, const unsigned* arrive, unsigned arrivals_per_step,
+                   unsigned* mc_version, unsigned* global_step, int adam, void* stream);
+/* Worker step brackets: wait on the LOCAL version word until *version >= base + per_step * *step; and, after the
+ * backward pass, add 1 to every shard's arrival counter through the multicast alias and advance *step. */
+int tfd_nvls_gate(const unsigned* version, const unsigned* step, unsigned per_step, unsigned base, void* stream);
+int tfd_nvls_signal(unsigned* mc_arrive, unsigned* step, void* stream);
+
 /* ---- peer memory (symmetric heap over cudaIpc) ---- */
 int tfd_set_device(int device);
 int tfd_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out64);    /* cudaMalloc + cudaIpcGetMemHandle */

@@ -72,7 +72,11 @@ def run_ours(a, rank: int, world: int, local: int) -> Optional[dict]:
         import torch.distributed as dist
         if not dist.is_initialized():
             dist.init_process_group("nccl", device_id=device)
-        eng = GpuClusterEngine.from_bench_args(spec, a, rank, world, device)
+        if os.environ.get("TFD_TRANSPORT", "peer") == "nvls":  # experimental multicast transport (parallel/ps_nvls.py)
+            from .parallel.ps_nvls import NvlsClusterEngine
+            eng = NvlsClusterEngine.from_bench_args(spec, a, rank, world, device)
+        else:
+            eng = GpuClusterEngine.from_bench_args(spec, a, rank, world, device)
         parallelism = eng.describe()
         workers = eng.num_workers
     rng = np.random.RandomState(1234 + rank)

@@ -32,6 +32,12 @@ class Piece(ctypes.Structure):
                 ("shadow_off", c_longlong)]
 
 
+class NvlsPiece(ctypes.Structure):
+    """tfd_nvls_piece_t: the rows of one variable a shard owns, with their places in the symmetric arenas."""
+    _fields_ = [("owner_off", c_longlong), ("numel", c_longlong), ("cols", c_int), ("ld_shadow", c_int),
+                ("grad_off", c_longlong), ("mirror_off", c_longlong), ("shadow_off", c_longlong)]
+
+
 def lib_path() -> str:
     return _LIB_PATH
 
@@ -395,3 +401,25 @@ def tensor_from_ptr(ptr: int, numel: int, dtype: torch.dtype, device) -> torch.T
         t = t.view(torch.int32)
     assert t.data_ptr() == ptr and t.element_size() == esz or dtype == torch.uint32
     return t
+
+
+# ---- parameter server over NVLS multicast (experimental; see csrc/nvls_kernels.cu) ----
+def nvls_apply(w, m, v, mc_grad, mc_mirror_w, mc_mirror_shadow, pieces, scale: float, lr: float, t_counter, arrive,
+               arrivals_per_step: int, mc_version, global_step=None, adam: bool = True, beta1: float = 0.9,
+               beta2: float = 0.999, eps: float = 1e-8) -> None:
+    arr = (NvlsPiece * max(1, len(pieces)))(*pieces)
+    _check(lib().tfd_nvls_apply(_p(w), _p(m), _p(v), _p(mc_grad), _p(mc_mirror_w), _p(mc_mirror_shadow), arr,
+                                c_int(len(pieces)), c_float(scale), c_float(lr), c_float(beta1), c_float(beta2),
+                                c_float(eps), _p(t_counter), _p(arrive), c_uint(arrivals_per_step), _p(mc_version),
+                                _p(global_step), c_int(int(adam)), _stream()), "tfd_nvls_apply")
+    _count()
+
+
+def nvls_gate(version, step, per_step: int, base: int = 0) -> None:
+    _check(lib().tfd_nvls_gate(_p(version), _p(step), c_uint(per_step), c_uint(base), _stream()), "tfd_nvls_gate")
+    _count()
+
+
+def nvls_signal(mc_arrive, step) -> None:
+    _check(lib().tfd_nvls_signal(_p(mc_arrive), _p(step), _stream()), "tfd_nvls_signal")
+    _count()

@@ -152,3 +152,15 @@ def test_gpu_backup_workers_drop_a_stragglers_stale_gradients(tmp_path):
     for o in outs[1:]:
         assert "Mean Accuracy :" in o
     assert any("(global step: 12)" in o for o in outs[1:])
+
+
+@needs2
+@pytest.mark.skipif(os.environ.get("TFD_TEST_NVLS", "0") != "1",
+                    reason="experimental NVLS transport: opt in with TFD_TEST_NVLS=1 (not yet validated on hardware)")
+@pytest.mark.parametrize("layout,model", [("colocated", "cnn"), ("dedicated", "cnn"), ("colocated", "mlp")])
+def test_two_gpu_nvls_transport_matches_the_peer_memory_transport(layout, model):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29631", os.path.join(ROOT, "scripts", "nvls_check.py"), "--layout", layout,
+           "--model", model]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert r.returncode == 0 and "OK" in r.stdout and "FAIL" not in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
