@@ -24,12 +24,12 @@ Sync mode with R = N only; async and backup workers stay on ``ps_gpu``.
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import torch
 import torch.distributed as dist
 
-from ..engine_native import NativeEngine, ShardState, Workspace, needs_shadow, _pad8
+from ..engine_native import NativeEngine, ShardState, Workspace, needs_shadow
 from ..models.spec import ModelSpec
 from ..ops import native as nat
 from .placement import Placement

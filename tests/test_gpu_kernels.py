@@ -3,7 +3,6 @@
 Inputs of tensor-core kernels are rounded to bf16 first and the reference runs in fp32 on those rounded values,
 so the only difference left is accumulation order (and bf16 rounding of bf16 outputs).
 """
-import math
 
 import pytest
 import torch
