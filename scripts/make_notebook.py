@@ -111,7 +111,7 @@ NB = {
         "language_info": {"name": "python", "version": "3.12"},
     },
     "nbformat": 4,
-    "nbformat_minor": 5,
+    "nbformat_minor": 4,
 }
 
 if __name__ == "__main__":
