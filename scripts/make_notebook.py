@@ -28,8 +28,6 @@ the whole step is one CUDA-graph launch; with `backend = "cpu"` the same API run
 code("""
 import time
 
-import numpy as np
-
 from tensorflow_distributed_b200 import data
 from tensorflow_distributed_b200.engine import make_engine
 from tensorflow_distributed_b200.models.spec import cnn_spec
