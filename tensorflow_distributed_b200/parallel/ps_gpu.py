@@ -650,10 +650,15 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
     if is_worker:
         log("Worker %d: %s" % (widx, "Initializing session..." if is_chief
                                else "Waiting for session to be initialized..."))
-    eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
-                           init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas,
-                           grad_dtype=flags.grad_dtype,
-                           replicas_to_aggregate=R if topo.layout == "dedicated" else 0)
+    if os.environ.get("TFD_TRANSPORT", "peer") == "nvls" and flags.sync_replicas and R == topo.num_workers:
+        from .ps_nvls import NvlsClusterEngine  # experimental multicast transport (strict sync only)
+        eng = NvlsClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
+                                init_stddev=flags.init_stddev)
+    else:
+        eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
+                               init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas,
+                               grad_dtype=flags.grad_dtype,
+                               replicas_to_aggregate=R if topo.layout == "dedicated" else 0)
     if flags.log_device_placement and (is_chief or not is_worker):
         log(eng.placement.table())
     sv = Supervisor(is_chief, spec, flags.train_dir, recovery_wait_secs=1.0, log=log)
