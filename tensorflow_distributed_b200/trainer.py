@@ -148,10 +148,19 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
 
     is_chief = cl.is_chief(flags)
     device = cl.worker_device(flags, cluster)
-    eng = OracleEngine(spec, flags.learning_rate, flags.seed, flags.init_stddev, cl.torch_device_of(device)
-                       if torch.cuda.is_available() else "cpu")
-    # per-worker dropout stream
-    eng._gen.manual_seed(flags.seed + 7919 + 31 * flags.task_index)
+    native_worker = flags.backend == "cuda"
+    if native_worker:
+        # The reference's literal deployment: ps tasks on CPU hosts, worker compute on a GPU (m:164-177).  Parameters
+        # arrive over gloo, go H2D, the sm_100a kernels compute the gradients, which go D2H and back over gloo.
+        from .engine_native import CTRL_T, NativeEngine
+        dev = cl.torch_device_of(device)
+        eng = NativeEngine(spec, flags.learning_rate, flags.seed + 31 * flags.task_index, flags.init_stddev,
+                           device=dev if dev != "cpu" else "cuda:0")
+    else:
+        eng = OracleEngine(spec, flags.learning_rate, flags.seed, flags.init_stddev, cl.torch_device_of(device)
+                           if torch.cuda.is_available() else "cpu")
+        # per-worker dropout stream
+        eng._gen.manual_seed(flags.seed + 7919 + 31 * flags.task_index)
     client = ps_cpu.PSClient(cluster, spec, placement, flags.task_index)
     sv = Supervisor(is_chief, spec, flags.train_dir, recovery_wait_secs=1.0, log=log)
 
@@ -189,7 +198,12 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
         tracer.before(local_step + 1)
         params = client.pull()
         _maybe_inject_fault(flags, local_step)
-        _, grads, _ = eng.loss_and_grads(batch_xs, batch_ys, flags.keep_prob, params=params)
+        if native_worker:
+            eng.set_params(params)
+            eng.shard.ctrl[CTRL_T] = local_step  # the dropout stream is indexed by this word; no Adam runs here
+            _, grads, _ = eng.loss_and_grads(batch_xs, batch_ys, flags.keep_prob)
+        else:
+            _, grads, _ = eng.loss_and_grads(batch_xs, batch_ys, flags.keep_prob, params=params)
         if flags.sync_replicas:
             client.push(grads, token, sync=True)
             token = client.dequeue_token()

@@ -164,3 +164,23 @@ def test_two_gpu_nvls_transport_matches_the_peer_memory_transport(layout, model)
            "--model", model]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert r.returncode == 0 and "OK" in r.stdout and "FAIL" not in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or os.environ.get("TFD_TEST_HYBRID", "0") != "1",
+                    reason="CPU-hosted ps + native GPU workers: opt in with TFD_TEST_HYBRID=1 (not yet validated on hardware)")
+def test_cpu_ps_with_native_gpu_workers(tmp_path):
+    """The reference's literal deployment (ps on a CPU host over the network transport, worker compute on a GPU):
+    host:port cluster over gloo, --backend=cuda on the workers."""
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    common = ["--ps_hosts=127.0.0.1:%d" % port, "--worker_hosts=127.0.0.1:%d,127.0.0.1:%d" % (port + 1, port + 2),
+              "--train_steps=6", "--validation_batches=1", "--validation_batch_size=200", "--init_stddev=0.05",
+              "--num_gpus=1"]
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, sc)] + common + extra, stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True, env=env, cwd=ROOT)
+             for sc, extra in (("mnist_python_m.py", ["--backend=cpu"]), ("mnist_python_w1.py", ["--backend=cuda"]),
+                               ("mnist_python_w2.py", ["--backend=cuda"]))]
+    outs = [p.communicate(timeout=300)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), "\n".join(outs)
+    assert "training step" in outs[1] and "Mean Accuracy" in outs[1] and "Mean Accuracy" in outs[2]
