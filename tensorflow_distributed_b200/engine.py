@@ -67,6 +67,16 @@ class OracleEngine:
         x, y = _as_tensor(x, self.device), _as_tensor(y, self.device)
         return float(oracle.accuracy(oracle.forward(self.spec.kind, x, self.params), y))
 
+    def predict_proba(self, x):
+        """Serving call: class probabilities softmax(model(x)) for a host batch, [B, 10] float32 (dropout off)."""
+        x = _as_tensor(x, self.device).reshape(-1, 784)
+        with torch.no_grad():
+            return torch.softmax(oracle.forward(self.spec.kind, x, self.params), dim=1).cpu().numpy()
+
+    def predict(self, x):
+        """argmax class per image (``tf.argmax(pred, 1)``, m:206)."""
+        return self.predict_proba(x).argmax(axis=1)
+
     # -- checkpoint plumbing --
     def get_params(self) -> Dict[str, torch.Tensor]:
         return {k: v.detach().cpu().clone() for k, v in self.params.items()}

@@ -405,6 +405,24 @@ class NativeEngine:
         self._run(ws, "eval", 1.0)
         return self._fetch_scalars(ws)[1]
 
+    def predict_proba(self, x) -> np.ndarray:
+        """Serving call: class probabilities softmax(model(x)) for a host batch, [B, 10] float32 (dropout off).
+
+        Runs the captured inference graph (forward + fused head) with a dummy one-hot label: the head kernel leaves
+        ``(softmax * sum(y) - y) / B`` in ``dlogits``, from which the probabilities follow without another kernel."""
+        x = np.ascontiguousarray(np.asarray(x, dtype=np.float32).reshape(-1, 784))
+        B = len(x)
+        y = np.zeros((B, 10), dtype=np.float32)
+        y[:, 0] = 1.0
+        ws = self.workspace(B)
+        self.load_batch(ws, x, y)
+        self._run(ws, "eval", 1.0)
+        return (ws.dlogits * float(B) + ws.y).cpu().numpy()  # the D2H copy synchronises the stream
+
+    def predict(self, x) -> np.ndarray:
+        """argmax class per image (``tf.argmax(pred, 1)``, m:206)."""
+        return self.predict_proba(x).argmax(axis=1)
+
     def loss_and_grads(self, x, y, keep_prob: float = 1.0):
         """Forward + backward without the apply (tests; cluster workers).  Returns (loss, grads, keep_mask)."""
         ws = self.workspace(len(x))

@@ -1,4 +1,6 @@
 """End-to-end GPU engine vs the CPU oracle: gradients of a full step, Adam trajectory, eval, trainer."""
+import os
+
 import pytest
 import torch
 
@@ -155,3 +157,18 @@ def test_checkpoint_resume_gives_the_same_next_step(tmp_path):
         d = (pa[k] - pb[k]).abs()
         assert d.mean().item() < 1e-5 and (d > 2e-2).float().mean().item() < 1e-3, k
     assert a.global_step == b.global_step == 4
+
+
+@pytest.mark.skipif(os.environ.get("TFD_TEST_PREDICT", "0") != "1",
+                    reason="predict_proba on the native engine: opt in with TFD_TEST_PREDICT=1 (added after the GPU budget ended)")
+def test_native_predict_proba_matches_the_oracle():
+    import numpy as np
+    spec = cnn_spec()
+    eng = _engine(spec, init_stddev=0.05, seed=4)
+    rng = np.random.RandomState(0)
+    x = rng.rand(50, 784).astype(np.float32)
+    p = eng.predict_proba(x)
+    params = eng.get_params()
+    want = torch.softmax(oracle.forward("cnn", torch.from_numpy(x), params), dim=1).numpy()
+    assert p.shape == (50, 10) and np.allclose(p.sum(axis=1), 1.0, atol=1e-4)
+    assert np.abs(p - want).max() < 0.03 and (p.argmax(1) == want.argmax(1)).mean() > 0.9

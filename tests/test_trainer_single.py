@@ -33,3 +33,18 @@ def test_single_mlp_learns_and_resumes(tmp_path):
     # resume: picks up global_step from the checkpoint and does no further training steps
     out2 = run_single(**kw)
     assert out2["engine"].global_step == 40 and out2["steps"] == 40
+
+
+def test_predict_is_consistent_with_eval_accuracy_on_the_oracle_engine():
+    import numpy as np
+    from tensorflow_distributed_b200 import data
+    from tensorflow_distributed_b200.engine import make_engine
+    from tensorflow_distributed_b200.models.spec import mlp_spec
+    ds = data.read_data_sets("", synthetic=True, seed=3)
+    eng = make_engine(mlp_spec(32, 1), "cpu", learning_rate=0.01, seed=0, init_stddev=0.1)
+    for _ in range(15):
+        eng.train_step(*ds.train.next_batch(64), 1.0)
+    x, y = ds.validation.next_batch(200)
+    p = eng.predict_proba(x)
+    assert p.shape == (200, 10) and np.allclose(p.sum(axis=1), 1.0, atol=1e-5) and (p >= 0).all()
+    assert abs(float((eng.predict(x) == y.argmax(axis=1)).mean()) - eng.eval_accuracy(x, y)) < 1e-6
