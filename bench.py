@@ -4,8 +4,9 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus N --steps K --warmup W
 
-One JSON line on rank 0.  `value` is device-timed (CUDA events per step, L2 flushed between steps, max over
-ranks); `e2e` goes through the public API (`engine.train_step(numpy_x, numpy_y, fetch_loss=True)`): pinned-host
+One JSON line on rank 0.  `value` is device-timed (CUDA events per step, L2 flushed between steps, ranks aligned
+by an untimed device-side rendezvous in front of every step, max over ranks; the K-step measurement is repeated
+for >= --min-seconds and the mean round is reported); `e2e` goes through the public API (`engine.train_step(numpy_x, numpy_y, fetch_loss=True)`): pinned-host
 H2D of the inputs and a D2H of the loss every step.  Synthetic 28x28 data, random-init weights (reference init
 N(0,1), /root/reference/mnist_python_m.py:186-195), batch 128 per worker (m:70), Adam lr 0.01 (m:71), keep 0.75.
 
@@ -25,7 +26,6 @@ import threading
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-BASELINE_IMG_S_PER_REPLICA = 128.0 / 4.875  # BASELINE.md section 1 (derived from performance:2-6; unit assumed s)
 
 
 class ClockSampler(threading.Thread):
@@ -77,7 +77,7 @@ class ClockSampler(threading.Thread):
                 self._sample_nvml() if self.nvml else self._sample_smi()
             except Exception:
                 pass
-            self._halt.wait(0.005 if self.nvml else 0.2)
+            self._halt.wait(0.002 if self.nvml else 0.2)
 
     def stop(self) -> dict:
         self._halt.set()
@@ -106,6 +106,13 @@ def parse():
                     help="storage type of the pushed gradients in the ps staging slots (multi-GPU)")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--init-stddev", type=float, default=1.0)
+    ap.add_argument("--min-seconds", dest="min_seconds", type=float, default=0.3,
+                    help="repeat the K-step measurement until this much wall time has been spent (stable mean, clock samples)")
+    ap.add_argument("--precision", default=None, choices=["tf32", "bf16"],
+                    help="tensor-core operand type: tf32 (fp32 activations/weights, the reference's precision class; "
+                         "default) or bf16 (bf16 operands, fp32 master weights)")
+    ap.add_argument("--graphs", action="store_true", help="--impl ddp: capture the whole DDP step in a CUDA graph")
+    ap.add_argument("--compile", action="store_true", help="--impl ddp: wrap the model in torch.compile")
     return ap.parse_args()
 
 

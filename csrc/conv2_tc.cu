@@ -308,16 +308,7 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
   }
 }
 
-int num_sms() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+int num_sms() { return tfd_num_sms(); }
 
 }  // namespace
 
@@ -329,11 +320,7 @@ extern "C" int tfd_conv2_fwd(const void* in, const void* w, const float* b, void
   rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
   if (rc) return rc;
   using C = ConvCfg<true>;
-  static bool attr = false;
-  if (!attr) {
-    TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
-    attr = true;
-  }
+  if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<true>), C::kSmem)) return arc;
   const int tiles = B * 2;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<true>, dim3(grid), dim3(kThreads), C::kSmem, static_cast<cudaStream_t>(stream),
@@ -348,11 +335,7 @@ extern "C" int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, 
   rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
   if (rc) return rc;
   using C = ConvCfg<false>;
-  static bool attr = false;
-  if (!attr) {
-    TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
-    attr = true;
-  }
+  if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<false>), C::kSmem)) return arc;
   const int tiles = B * 2;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<false>, dim3(grid), dim3(kThreads), C::kSmem, static_cast<cudaStream_t>(stream),
@@ -366,11 +349,7 @@ extern "C" int tfd_conv2_wgrad(const void* in, const void* dy, float* dw, int B,
   if (rc) return rc;
   rc = tfd_make_tmap_nhwc_bf16(&tmDy, dy, B, 14, 14, 64, 4, 2, 16, 128);
   if (rc) return rc;
-  static bool attr = false;
-  if (!attr) {
-    TFD_CUDA_CHECK(cudaFuncSetAttribute(conv2_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
-    attr = true;
-  }
+  if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel), kWgSmem)) return arc;
   const int tiles = ((B + 3) / 4) * 7;
   int chunks = num_sms() / 7;
   if (chunks > tiles) chunks = tiles;

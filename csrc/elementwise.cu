@@ -606,11 +606,8 @@ extern "C" int tfd_head_rows(const float* pre_f32, int pre_nsplit, long long pre
   TFD_REQUIRE(!training || dhid, "head_rows: training needs dhid");
   const size_t smem = (size_t)(H + 96) * sizeof(float);
   TFD_REQUIRE(smem <= 200 * 1024, "head_rows: H=%d too large", H);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    TFD_CUDA_CHECK(cudaFuncSetAttribute(head_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if (smem > 48 * 1024)
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_rows_kernel), (int)smem)) return arc;
   TFD_CUDA_CHECK(tfd_launch(head_rows_kernel, dim3(B), dim3(256), smem, ST(stream), pre_f32, pre_nsplit < 1 ? 1 : pre_nsplit, pre_split_stride,
                                                  (const bf16*)hid_bf16, hid_bias, out_w, out_b, labels, B, H, ld_h,
                                                  keep_prob, seed, step, step_ptr, training, (bf16*)hid_out, (bf16*)dhid, dlogits,
@@ -624,11 +621,8 @@ extern "C" int tfd_head_cols(const void* hid, const void* dhid, long long ld_h, 
                              float* d_hid_bias, float* d_out_b, float* scalars, void* stream) {
   const size_t smem = ((size_t)B * 10 + 8 * 11 * 32) * sizeof(float);
   TFD_REQUIRE(smem <= 200 * 1024, "head_cols: batch %d too large for the dlogits tile", B);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    TFD_CUDA_CHECK(cudaFuncSetAttribute(head_cols_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if (smem > 48 * 1024)
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_cols_kernel), (int)smem)) return arc;
   const int blocks = hid ? (H + 31) / 32 : 1;
   TFD_CUDA_CHECK(tfd_launch(head_cols_kernel, dim3(blocks), dim3(256), smem, ST(stream), (const bf16*)hid, (const bf16*)dhid, ld_h, dlogits, loss_row, hit, B,
                                                       H, d_out_w, d_hid_bias, d_out_b, scalars));

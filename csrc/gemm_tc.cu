@@ -396,11 +396,7 @@ template <int A_MN, int B_MN, int BN>
 int launch(const CUtensorMap& tmA, const TmapArray& tmBs, const GemmParams& p, const SegInfo& sg, cudaStream_t stream) {
   using C = Cfg<BN>;
   auto kern = gemm_tc_kernel<A_MN, B_MN, BN>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    TFD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    attr_set = true;
-  }
+  if (int rc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(kern), C::kSmemBytes)) return rc;
   dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, p.splits);
   GemmParams q = p;
   const int per_split = (p.kblocks + p.splits - 1) / p.splits;

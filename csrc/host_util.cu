@@ -1,8 +1,11 @@
 // Host utilities: error string, TMA tensor-map construction, device info.
 #include <stdarg.h>
 #include <stdlib.h>
+#include <map>
+#include <mutex>
 #include <set>
 #include <string.h>
+#include <utility>
 
 #include "../include/tfd_b200.h"
 #include "tfd_common.cuh"
@@ -117,10 +120,41 @@ extern "C" int tfd_set_pdl(int on) {
   return 0;
 }
 
+// cudaFuncSetAttribute applies to the CURRENT device only, so "already configured" is remembered per
+// (device, kernel): a second GPU driven from the same process gets its own opt-in to > 48 KB of dynamic shared memory.
+int tfd_ensure_dyn_smem(const void* kernel, int bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<int, const void*>, int> configured;
+  int dev = 0;
+  TFD_CUDA_CHECK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  int& have = configured[std::make_pair(dev, kernel)];
+  if (have >= bytes) return 0;
+  TFD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  have = bytes;
+  return 0;
+}
+
+int tfd_num_sms() {
+  static std::mutex mu;
+  static std::map<int, int> sms;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  std::lock_guard<std::mutex> lock(mu);
+  int& n = sms[dev];
+  if (n <= 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
+}
+
 void tfd_prefer_max_smem(const void* kernel) {
-  static std::set<const void*> done;
-  if (done.count(kernel)) return;
-  done.insert(kernel);
+  static std::mutex mu;
+  static std::set<std::pair<int, const void*>> done;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!done.insert(std::make_pair(dev, kernel)).second) return;
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) !=
       cudaSuccess)
     cudaGetLastError();  // a hint only: never fail a launch over it

@@ -257,6 +257,8 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t target
 // host: kernel launch with the PDL attribute (tfd_set_pdl(0) turns it into a plain serialized launch)
 // ---------------------------------------------------------------------------------------------
 int tfd_pdl_enabled();
+int tfd_ensure_dyn_smem(const void* kernel, int bytes);  // per (device, kernel) opt-in to > 48 KB dynamic smem
+int tfd_num_sms();                                       // SM count of the current device
 void tfd_prefer_max_smem(const void* kernel);
 int tfd_uniform_carveout();
 #ifdef __CUDACC__

@@ -92,7 +92,9 @@ def save(train_dir: str, spec: ModelSpec, global_step: int, params: Dict[str, to
 
 
 def load(path: str, spec: Optional[ModelSpec] = None) -> dict:
-    blob = torch.load(path, map_location="cpu", weights_only=False)
+    # weights_only: the blob holds tensors, dicts, strings and numbers only, so nothing in a checkpoint found in
+    # train_dir can execute code on load
+    blob = torch.load(path, map_location="cpu", weights_only=True)
     if blob.get("format") != "tfd_b200.ckpt.v1":
         raise ValueError("not a tfd_b200 checkpoint: %s" % path)
     if spec is not None:

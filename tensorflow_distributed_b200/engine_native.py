@@ -113,8 +113,9 @@ class Workspace:
         z = lambda *s, dtype=torch.float32: torch.zeros(*s, dtype=dtype, device=device)  # noqa: E731
         self.x = z(B, 784)
         self.y = z(B, 10)
-        self.x_host = torch.zeros(B, 784, dtype=torch.float32).pin_memory()
-        self.y_host = torch.zeros(B, 10, dtype=torch.float32).pin_memory()
+        self.stage = [(torch.zeros(B, 784, dtype=torch.float32).pin_memory(),
+                       torch.zeros(B, 10, dtype=torch.float32).pin_memory(), torch.cuda.Event()) for _ in range(2)]
+        self.stage_i = 0
         self.scalars = z(2)
         self.scalars_host = torch.zeros(2, dtype=torch.float32).pin_memory()
         self.dlogits, self.loss_row = z(B, 10), z(B)
@@ -158,6 +159,7 @@ class NativeEngine:
         nat.set_device(self.device.index or 0)
         nat.set_slot_dtype(False)
         self.lr, self.seed = learning_rate, seed
+        self.dropout_seed = seed
         self.use_graphs, self.conv2_ref = use_graphs, conv2_ref
         self.placement = Placement(spec, 1)
         self.shard = ShardState(spec, self.placement, 0, self.device)
@@ -372,10 +374,18 @@ class NativeEngine:
         if isinstance(x, torch.Tensor) and x.is_cuda:
             ws.x.copy_(x.reshape(ws.B, 784)); ws.y.copy_(y.reshape(ws.B, 10))
             return
-        ws.x_host.copy_(torch.as_tensor(np.ascontiguousarray(x) if isinstance(x, np.ndarray) else x).reshape(ws.B, 784))
-        ws.y_host.copy_(torch.as_tensor(np.ascontiguousarray(y) if isinstance(y, np.ndarray) else y).reshape(ws.B, 10))
-        ws.x.copy_(ws.x_host, non_blocking=True)
-        ws.y.copy_(ws.y_host, non_blocking=True)
+        # Two pinned staging pairs, each guarded by an event recorded behind its H2D copies: the host may run ahead of
+        # the device (train_step does not sync unless a loss is fetched), so a pair is only overwritten once the
+        # copies that last read it have completed.  Without this a fast caller tears or duplicates batches.
+        k = ws.stage_i
+        ws.stage_i ^= 1
+        xh, yh, ev = ws.stage[k]
+        ev.synchronize()
+        xh.copy_(torch.as_tensor(np.ascontiguousarray(x) if isinstance(x, np.ndarray) else x).reshape(ws.B, 784))
+        yh.copy_(torch.as_tensor(np.ascontiguousarray(y) if isinstance(y, np.ndarray) else y).reshape(ws.B, 10))
+        ws.x.copy_(xh, non_blocking=True)
+        ws.y.copy_(yh, non_blocking=True)
+        ev.record(torch.cuda.current_stream())
 
     def _fetch_scalars(self, ws: Workspace):
         ws.scalars_host.copy_(ws.scalars, non_blocking=True)

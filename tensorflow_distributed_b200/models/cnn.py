@@ -25,7 +25,7 @@ def forward(eng, ws: Workspace, training: bool, keep_prob: float, mask_out=None)
     eng.gemm_fwd("weights/wd1", ws.pool2.view(B, 3136), B, ws.fc1acc, mode=nat.EPI_STORE_F32, bn=64,
                   splits=ws.fc1_splits, split_stride=B * 1024, ld_out=1024)
     nat.head_rows(ws.fc1acc, None, eng.P("biases/bd1"), eng.P("weights/out"), eng.P("biases/out"), ws.y, B,
-                  1024, 1024, keep_prob if training else 1.0, eng.seed, 0, training, ws.hid,
+                  1024, 1024, keep_prob if training else 1.0, eng.dropout_seed, 0, training, ws.hid,
                   ws.dhid if training else None, ws.dlogits, ws.loss_row, ws.hit, mask_out,
                   step_ptr=eng.step_ptr() if training else None, pre_nsplit=ws.fc1_splits,
                   pre_split_stride=B * 1024)

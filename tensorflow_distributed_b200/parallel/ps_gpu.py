@@ -157,6 +157,9 @@ class GpuClusterEngine(NativeEngine):
         self.ws: Dict[int, Workspace] = {}
         self.my_shard = topo.shard_of(rank)
         self.my_worker = topo.worker_of(rank)
+        # the initialisation seed is shared (every shard generates its slice of one Philox stream); the dropout stream
+        # is per worker, as each of the reference's workers draws its own tf.nn.dropout mask (m:124)
+        self.dropout_seed = seed + 31 * (self.my_worker or 0)
         self.is_ps, self.is_worker = self.my_shard is not None, self.my_worker is not None
         self.num_workers = topo.num_workers
         S = topo.num_shards
@@ -575,8 +578,10 @@ class GpuClusterEngine(NativeEngine):
             s.ctrl[CTRL_VERSION] = T
             s.ctrl[CTRL_ARRIVE] = T * self.num_workers
             s.ctrl[CTRL_TICKET] = T
-        if self.is_worker and not self.async_mode:
-            self.ctrl[WCTRL_STEP] = int(sd["t"])  # sync workers wait for version >= their step counter
+        if self.is_worker:
+            # sync workers wait for version >= their step counter; in every mode the dropout stream is indexed by it,
+            # so a resumed run continues the stream instead of replaying the masks of step 0
+            self.ctrl[WCTRL_STEP] = int(sd["t"])
         torch.cuda.synchronize(self.device)
         dist.barrier()
 
@@ -695,6 +700,8 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
     time_begin = time.time()
     log("Training begins @ %f" % time_begin)
     local_step, step = 0, start_step
+    last_saved = start_step
+    every = flags.save_checkpoint_steps if (flags.train_dir and flags.save_checkpoint_steps > 0) else 0
     from ..utils.trace import StepTracer
     tracer = StepTracer(flags.trace_file and "%s.worker%d" % (flags.trace_file, widx), flags.trace_start,
                         flags.trace_steps, log)  # a no-op unless --trace_file is given
@@ -708,6 +715,14 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
         # X5: strict sync knows the global step without asking; async / backup workers read it from shard 0
         step = (start_step + local_step) if (flags.sync_replicas and not eng.backup) else eng.global_step
         log("%f: Worker %d: training step %d done (global step: %d)" % (time.time(), widx, local_step, step))
+        if every and is_chief and step // every > last_saved // every and step < flags.train_steps:
+            # the Supervisor's periodic saver (m:239-253; every 600 s in TF, here every N global steps).  The chief reads
+            # the shards through the peer mapping while the other workers may already be one step further: like TF's
+            # saver it snapshots a live model, so a tensor may be one update ahead of another (never torn inside a
+            # step on strict sync: the chief's own next push has not happened, so no shard can apply update step+1)
+            eng.synchronize()
+            sv.save(step, eng.get_params(), eng.get_adam_state())
+            last_saved = step
     eng.synchronize()
     tracer.close()
     time_end = time.time()

@@ -105,6 +105,7 @@ class NvlsClusterEngine(NativeEngine):
         nat.set_device(self.device.index or 0)
         nat.set_slot_dtype(False)
         self.lr, self.seed = learning_rate, seed
+        self.dropout_seed = seed + 31 * (topo.worker_of(rank) or 0)  # per-worker dropout stream, shared init seed
         self.use_graphs, self.conv2_ref = use_graphs, conv2_ref
         self.ws: Dict[int, Workspace] = {}
         self.my_shard, self.my_worker = topo.shard_of(rank), topo.worker_of(rank)

@@ -1,6 +1,8 @@
 """End-to-end GPU engine vs the CPU oracle: gradients of a full step, Adam trajectory, eval, trainer."""
 import os
 
+import numpy as np
+
 import pytest
 import torch
 
@@ -172,3 +174,25 @@ def test_native_predict_proba_matches_the_oracle():
     want = torch.softmax(oracle.forward("cnn", torch.from_numpy(x), params), dim=1).numpy()
     assert p.shape == (50, 10) and np.allclose(p.sum(axis=1), 1.0, atol=1e-4)
     assert np.abs(p - want).max() < 0.03 and (p.argmax(1) == want.argmax(1)).mean() > 0.9
+
+
+def test_train_step_back_to_back_feeds_the_batch_it_was_given():
+    """train_step(fetch_loss=False) does not synchronise, so the host runs ahead of the ~0.1 ms device step; the pinned
+    staging buffers are double-buffered behind events and must never be overwritten while an H2D copy that reads
+    them is still queued (round-1 advisor finding: torn / duplicated batches)."""
+    from tensorflow_distributed_b200.engine_native import NativeEngine
+    from tensorflow_distributed_b200.models.spec import cnn_spec
+    eng = NativeEngine(cnn_spec(), learning_rate=0.0, seed=1, init_stddev=0.05, device="cuda:0")
+    B, n = 128, 40
+    rng = np.random.RandomState(5)
+    xs = [np.full((B, 784), float(i), dtype=np.float32) + rng.rand(B, 784).astype(np.float32) * 0.25 for i in range(n)]
+    ys = [np.eye(10, dtype=np.float32)[np.full(B, i % 10)] for i in range(n)]
+    ws = eng.workspace(B)
+    seen = []
+    for i in range(n):
+        eng.train_step(xs[i], ys[i], 0.75, fetch_loss=False)
+        seen.append((ws.x.clone(), ws.y.clone()))  # stream-ordered snapshot of what step i actually consumed
+    torch.cuda.synchronize()
+    for i, (x, y) in enumerate(seen):
+        assert torch.equal(x.cpu(), torch.from_numpy(xs[i])), "step %d trained on another batch" % i
+        assert torch.equal(y.cpu(), torch.from_numpy(ys[i]))

@@ -103,3 +103,25 @@ def test_noalloc_rejects_requests_beyond_the_builtin_scratch():
     assert "exceeds the built-in scratch" in msg and "8 MiB" in msg
     torch.cuda.synchronize()
     assert torch.all(out == 5.0)  # rejected before anything ran
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs 2 GPUs in one process")
+def test_noalloc_first_call_on_a_second_device_of_the_same_process():
+    """The header promises per-device set-up on the first call on EACH device (scratch address and the kernel's
+    shared-memory opt-in are both per device): drive device 0, then device 1, from one process."""
+    lib = _lib()
+    from tensorflow_distributed_b200.ops import native
+    M, N, K = 128, 256, 640
+    for d in (0, 1):
+        torch.cuda.set_device(d)
+        native.set_device(d)
+        dev = "cuda:%d" % d
+        torch.manual_seed(3 + d)
+        A = torch.randn(M, K, device=dev).to(torch.bfloat16)
+        W = torch.randn(K, N, device=dev).to(torch.bfloat16)
+        out = torch.zeros(M, N, device=dev)
+        assert _noalloc(lib, A, W, M, N, K, 4, out) == 0, lib.tfd_last_error().decode()
+        torch.cuda.synchronize(d)
+        assert _rel(out, A.float() @ W.float()) < TOL
+    torch.cuda.set_device(0)
+    native.set_device(0)
