@@ -16,12 +16,12 @@ using namespace tfd;
 typedef __nv_bfloat16 bf16;
 
 constexpr int kThreads = 192;
-constexpr int kFilterBytes = 25 * 4096;  // [800][64] bf16
+constexpr int kFilterBytes = 25 * 4096;  // [800][64] bf16, or one 32-channel half of the fp32 filter
 
-__device__ __forceinline__ void load_filter(uint8_t* filt, const CUtensorMap* tmW, uint64_t* bar) {
+__device__ __forceinline__ void load_filter(uint8_t* filt, const CUtensorMap* tmW, uint64_t* bar, int c0) {
   mbar_arrive_expect_tx(bar, kFilterBytes);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) tma_load_2d(filt + i * 25600, tmW, bar, 0, i * 200);
+  for (int i = 0; i < 4; ++i) tma_load_2d(filt + i * 25600, tmW, bar, c0, i * 200);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -34,22 +34,31 @@ __device__ __forceinline__ void load_filter(uint8_t* filt, const CUtensorMap* tm
 // descriptor into that box at row offset kh*16 (a multiple of the swizzle atom), so the five row taps of a
 // column reuse one box: 5x less L2->SM traffic than one box per tap, which is what bounded this kernel.
 // ------------------------------------------------------------------------------------------------
-template <bool kFwd>
+// tf32 arm (TF = 1): activations and filter are fp32 in memory and are read by the tensor core as tf32.  The fp32 filter
+// is 200 KB, twice what fits next to the input ring, so a CTA works on ONE HALF of the 64 output channels and keeps
+// that half of the filter (25 taps x [32 ci][32 co] fp32 = 100 KB, the same bytes as the whole bf16 filter) resident:
+//   forward: the half is an N split -- work item = (pixel tile, co half), N = 32, epilogue writes 32 of the 64 pooled
+//            channels; the filter tile of a tap is the MN-major B operand ([32 ci rows][32 co], 32 B swizzle atoms);
+//   dgrad:   the half is a K split -- work item = (pixel tile, co half), A = that half of dy's channels, the same
+//            filter tile read K-major; the two halves write two partial planes of dx that the consumer
+//            (conv1_wgrad) adds, in a fixed order.
+// Even CTAs take half 0, odd CTAs half 1, so a CTA loads its filter half once.
+template <bool kFwd, int TF>
 struct ConvCfg {
-  static constexpr int kRowBytes = kFwd ? 64 : 128;
+  static constexpr int kRowBytes = TF ? 128 : (kFwd ? 64 : 128);
   static constexpr int kBoxBytes = 12 * 16 * kRowBytes;  // 12 KB / 24 KB
-  static constexpr int kStages = kFwd ? 8 : 5;           // ring of kw boxes
-  static constexpr int kN = kFwd ? 64 : 32;
-  static constexpr int kKSteps = kFwd ? 2 : 4;           // UMMA K=16 steps per tap
+  static constexpr int kStages = (kRowBytes == 64) ? 8 : 5;  // ring of kw boxes
+  static constexpr int kN = TF ? 32 : (kFwd ? 64 : 32);
+  static constexpr int kKSteps = TF ? 4 : (kFwd ? 2 : 4);  // MMAs per tap (UMMA K = 32 B)
   static constexpr int kSmem = kFilterBytes + kStages * kBoxBytes + 1024 + 512;
 };
 
-template <bool kFwd>
+template <bool kFwd, int TF>
 __global__ void __launch_bounds__(kThreads, 1)
 conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                const float* __restrict__ bias, bf16* __restrict__ pool_out, unsigned char* __restrict__ amax,
-                float* __restrict__ dx, int B, int num_tiles) {
-  using C = ConvCfg<kFwd>;
+                const float* __restrict__ bias, void* __restrict__ pool_out_v, unsigned char* __restrict__ amax,
+                float* __restrict__ dx, int B, int num_tiles, long long dx_plane_stride) {
+  using C = ConvCfg<kFwd, TF>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* filt = smem;
@@ -62,6 +71,10 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // work distribution: bf16 -- CTA b takes tiles b, b+grid, ...; tf32 -- CTA b takes channel half b&1 of tiles b>>1, ...
+  const int half = TF ? (int)(blockIdx.x & 1) : 0;
+  const int tile0 = TF ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tstride = TF ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmW);
@@ -85,25 +98,27 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int stage = 0;
       uint32_t phase = 0;
       bool filter_sent = false;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tstride) {
         const int n = tile >> 1, ht = tile & 1;
         for (int kw = 0; kw < 5; ++kw) {
           mbar_wait(&a_empty[stage], phase ^ 1);
           mbar_arrive_expect_tx(&a_full[stage], C::kBoxBytes);
-          tma_load_4d(abuf + stage * C::kBoxBytes, &tmA, &a_full[stage], 0, kFwd ? kw - 2 : 2 - kw, 8 * ht - 2, n);
+          // tf32 dgrad reads only this CTA's half of dy's channels (the K split)
+          tma_load_4d(abuf + stage * C::kBoxBytes, &tmA, &a_full[stage], (TF && !kFwd) ? half * 32 : 0,
+                      kFwd ? kw - 2 : 2 - kw, 8 * ht - 2, n);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
-          if (!filter_sent) { load_filter(filt, &tmW, filt_full); filter_sent = true; }
+          if (!filter_sent) { load_filter(filt, &tmW, filt_full, TF ? half * 32 : 0); filter_sent = true; }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, C::kN, 0, kFwd ? 1 : 0);
+      constexpr uint32_t idesc = TF ? make_idesc_tf32(128, C::kN, 0, kFwd ? 1 : 0) : make_idesc_bf16(128, C::kN, 0, kFwd ? 1 : 0);
       mbar_wait(filt_full, 0);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile0; tile < num_tiles; tile += tstride, ++it) {
         const int buf = it & 1;
         mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -120,14 +135,22 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
             for (int ks = 0; ks < C::kKSteps; ++ks) {
               uint64_t da, db;
-              if (kFwd) {
-                da = make_smem_desc(sa + ks * 32, 16, 512, kSwz64);         // [128 px][32 ci]  K-major, 64 B rows
-                db = make_smem_desc(sw + ks * 2048, 4096, 1024, kSwz128);   // [32 ci][64 co]   MN-major (co contiguous)
+              const bool acc = (kw > 0 || kh > 0 || ks > 0);
+              if (TF) {
+                da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);             // [128 px][32 ch fp32]  K-major
+                if (kFwd) db = make_smem_desc(sw + ks * 1024, 4096, 512, kSwz128B32);  // [32 ci][32 co]  MN-major
+                else      db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);        // [32 ci][32 co]  K-major (co = K)
+                umma_tf32(tacc, da, db, idesc, acc ? 1u : 0u);
               } else {
-                da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);       // [128 px][64 co]  K-major, 128 B rows
-                db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);       // [32 ci][64 co]   K-major  (co = K)
+                if (kFwd) {
+                  da = make_smem_desc(sa + ks * 32, 16, 512, kSwz64);         // [128 px][32 ci]  K-major, 64 B rows
+                  db = make_smem_desc(sw + ks * 2048, 4096, 1024, kSwz128);   // [32 ci][64 co]   MN-major (co contiguous)
+                } else {
+                  da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);       // [128 px][64 co]  K-major, 128 B rows
+                  db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);       // [32 ci][64 co]   K-major  (co = K)
+                }
+                umma_bf16(tacc, da, db, idesc, acc ? 1u : 0u);
               }
-              umma_bf16(tacc, da, db, idesc, (kw > 0 || kh > 0 || ks > 0) ? 1u : 0u);
             }
           }
           umma_commit(&a_empty[stage]);
@@ -140,7 +163,7 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int q = warp & 3;  // TMEM lane quadrant = two image rows of the tile
     const int hh = lane >> 4, ww = lane & 15;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile0; tile < num_tiles; tile += tstride, ++it) {
       const int buf = it & 1;
       const int n = tile >> 1, ht = tile & 1;
       const int h = 8 * ht + 2 * q + hh;  // conv output row of this lane
@@ -150,15 +173,15 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (kFwd) {
         const int self = hh * 2 + (ww & 1);
         const int ph = 4 * ht + q;  // pooled row
+        const int cbase = half * 32;  // first output channel of this CTA's accumulator columns (tf32: its half)
 #pragma unroll 1
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < C::kN / 16; ++j) {
           float v[16];
           tmem_ld16(tacc + j * 16, v);
-          uint32_t packed[8];
           uint32_t am[4] = {0, 0, 0, 0};
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            float x = fmaxf(v[i] + __ldg(bias + j * 16 + i), 0.f);
+            float x = fmaxf(v[i] + __ldg(bias + cbase + j * 16 + i), 0.f);
             int xi = self;
             float y = __shfl_xor_sync(0xffffffffu, x, 1);
             int yi = self ^ 1;
@@ -169,18 +192,28 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             v[i] = x;
             am[i >> 2] |= (uint32_t)xi << ((i & 3) * 8);
           }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) packed[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+          // the four lanes of a pooling window hold the same result: lane `self` == j stores chunk j
           if (j == self && ww < 14 && ph < 7 && n < B) {
-            const long long o = ((((long long)n * 7 + ph) * 7) + (ww >> 1)) * 64 + j * 16;
-            *reinterpret_cast<uint4*>(pool_out + o) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-            *reinterpret_cast<uint4*>(pool_out + o + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            const long long o = ((((long long)n * 7 + ph) * 7) + (ww >> 1)) * 64 + cbase + j * 16;
+            if (TF) {
+              float* po = static_cast<float*>(pool_out_v) + o;
+#pragma unroll
+              for (int i = 0; i < 16; i += 4)
+                *reinterpret_cast<float4*>(po + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+            } else {
+              bf16* po = static_cast<bf16*>(pool_out_v) + o;
+              uint32_t packed[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) packed[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+              *reinterpret_cast<uint4*>(po) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+              *reinterpret_cast<uint4*>(po + 8) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            }
             *reinterpret_cast<uint4*>(amax + o) = make_uint4(am[0], am[1], am[2], am[3]);
           }
         }
       } else {
         const bool ok = (ww < 14) && (h < 14) && (n < B);
-        float* o = dx + ((((long long)n * 14 + h) * 14) + ww) * 32;
+        float* o = dx + (long long)half * dx_plane_stride + ((((long long)n * 14 + h) * 14) + ww) * 32;
 #pragma unroll 1
         for (int j = 0; j < 2; ++j) {
           float v[16];
@@ -205,26 +238,41 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 }
 
 // ------------------------------------------------------------------------------------------------
-// filter gradient: dW[(tap,ci), co] += sum_px in[px + shift(tap), ci] * dy[px, co].
+// filter gradient: dW[(tap,ci), co] = sum_px in[px + shift(tap), ci] * dy[px, co].
 // GEMM view per tap group g (4 taps): M = 4*32 (tap_local, ci), N = 64 co, K = 128 pixels of the tile.
-//   A: four [128 px][32 ci] SW64 tiles (one TMA box per tap) read MN-major, stacked along M through LBO
-//   B: the [128 px][64 co] SW128 dy tile read MN-major
-// grid = (pixel chunks, 7 tap groups): a CTA owns ONE 128x64 accumulator (64 TMEM columns) over its share of
-// the pixel tiles, so only `chunks` CTAs ever red.add to the same dW element (7x fewer atomics than splitting
-// by pixels alone).
+//   A: four [128 px][32 ci] tiles (one TMA box per tap) read MN-major, stacked along M through LBO
+//   B: the [128 px][64 co] dy tile read MN-major
+//   bf16: A rows are 64 B (SW64), B rows 128 B (SW128).  tf32: every row is 128 B of fp32 (32 channels; dy as two
+//   channel halves), 128B swizzle with 32 B atoms, 8 pixels per MMA.
+// grid = (pixel chunks, 7 tap groups): a CTA owns ONE 128x64 accumulator (64 TMEM columns) over its share of the
+// pixel tiles.
+//
+// Deterministic reduction (no floating-point atomics): every CTA stores its partial tile into a scratch plane, the
+// `chunks` CTAs of a tap group meet at a counter, and each then sums a fixed slice of the group's output over all
+// planes IN PLANE ORDER and writes it to dW (which may be a staging slot on another GPU).  All CTAs of the grid fit
+// on the chip at once (<= 147 CTAs, one per SM), so a CTA spinning on its group's counter only ever waits for CTAs
+// that are running or will be scheduled as soon as an SM frees up; the wait is bounded and traps.
 // ------------------------------------------------------------------------------------------------
-constexpr int kWgStages = 4;
-constexpr int kWgStageBytes = 16384 + 4 * 8192;  // dy tile + up to four tap tiles
-constexpr int kWgSmem = kWgStages * kWgStageBytes + 1024 + 512;
+template <int TF>
+struct WgCfg {
+  static constexpr int kInTile = TF ? 16384 : 8192;           // [128 px][32 ci]
+  static constexpr int kDyTile = TF ? 32768 : 16384;          // [128 px][64 co]
+  static constexpr int kStageBytes = kDyTile + 4 * kInTile;   // 48 KB / 96 KB
+  static constexpr int kStages = TF ? 2 : 4;
+  static constexpr int kSmem = kStages * kStageBytes + 1024 + 512;
+};
+constexpr int kWgCounterWords = 64;  // head of the scratch buffer: one arrival counter per tap group
 
+template <int TF>
 __global__ void __launch_bounds__(kThreads, 1)
 conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmDy,
-                      float* __restrict__ dw, int num_tiles) {
+                      float* __restrict__ dw, float* __restrict__ scratch, int num_tiles) {
+  using C = WgCfg<TF>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
-  uint64_t* empty = full + kWgStages;
-  uint64_t* acc_full = empty + kWgStages;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty = full + C::kStages;
+  uint64_t* acc_full = empty + C::kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -233,7 +281,7 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmIn);
     prefetch_tmap(&tmDy);
-    for (int s = 0; s < kWgStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
     fence_barrier_init();
     fence_proxy_async_smem();
@@ -252,52 +300,91 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int nb = tile / 7, hp = tile % 7;
-        uint8_t* st = smem + stage * kWgStageBytes;
+        uint8_t* st = smem + stage * C::kStageBytes;
         mbar_wait(&empty[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full[stage], 16384 + ntap * 8192);
+        mbar_arrive_expect_tx(&full[stage], C::kDyTile + ntap * C::kInTile);
         tma_load_4d(st, &tmDy, &full[stage], 0, 0, 2 * hp, nb * 4);
+        if (TF) tma_load_4d(st + 16384, &tmDy, &full[stage], 32, 0, 2 * hp, nb * 4);  // channels 32..63
         for (int tl = 0; tl < ntap; ++tl) {
           const int tap = g * 4 + tl, kh = tap / 5, kw = tap % 5;
-          tma_load_4d(st + 16384 + tl * 8192, &tmIn, &full[stage], 0, kw - 2, 2 * hp + kh - 2, nb * 4);
+          tma_load_4d(st + C::kDyTile + tl * C::kInTile, &tmIn, &full[stage], 0, kw - 2, 2 * hp + kh - 2, nb * 4);
         }
-        if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
+      constexpr uint32_t idesc = TF ? make_idesc_tf32(128, 64, 1, 1) : make_idesc_bf16(128, 64, 1, 1);
       int stage = 0, it = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const uint32_t sdy = smem_u32(smem + stage * kWgStageBytes);
-        const uint32_t sa = sdy + 16384;
+        const uint32_t sdy = smem_u32(smem + stage * C::kStageBytes);
+        const uint32_t sa = sdy + C::kDyTile;
+        if (TF) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint64_t da = make_smem_desc(sa + ks * 1024, 8192, 512, kSwz64);     // 16 px = two 512 B atoms
-          const uint64_t dbb = make_smem_desc(sdy + ks * 2048, 8192, 1024, kSwz128);  // 16 px = two 1024 B atoms
-          umma_bf16(tmem_base, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < 16; ++ks) {  // 8 pixels (1024 B of every 128 B-wide tile) per MMA
+            const uint64_t da = make_smem_desc(sa + ks * 1024, C::kInTile, 512, kSwz128B32);   // M chunks = taps
+            const uint64_t dbb = make_smem_desc(sdy + ks * 1024, 16384, 512, kSwz128B32);       // N chunks = co halves
+            umma_tf32(tmem_base, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+          }
+        } else {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t da = make_smem_desc(sa + ks * 1024, 8192, 512, kSwz64);     // 16 px = two 512 B atoms
+            const uint64_t dbb = make_smem_desc(sdy + ks * 2048, 8192, 1024, kSwz128);  // 16 px = two 1024 B atoms
+            umma_bf16(tmem_base, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+          }
         }
         umma_commit(&empty[stage]);
-        if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
       umma_commit(acc_full);
     }
   } else {
+    // ---- epilogue warps: partial plane -> group rendezvous -> fixed-order slice reduction ----
     const int q = warp & 3;
-    const int tap = g * 4 + q;
+    const int et = (int)threadIdx.x - 64;  // 0..127
+    const int chunks = gridDim.x;
+    unsigned* counters = reinterpret_cast<unsigned*>(scratch);
+    float* planes = scratch + kWgCounterWords + (size_t)g * chunks * 8192;  // [chunks][128][64] of this group
+    float* mine = planes + (size_t)blockIdx.x * 8192;
     mbar_wait(acc_full, 0);
     tc_fence_after();
 #pragma unroll 1
     for (int j = 0; j < 4; ++j) {
       float v[16];
       tmem_ld16(tmem_base + j * 16 + ((uint32_t)(q * 32) << 16), v);
-      if (tap < 25) {
-        float* o = dw + ((long long)(tap * 32 + lane)) * 64 + j * 16;
+      float* o = mine + (q * 32 + lane) * 64 + j * 16;
 #pragma unroll
-        for (int i = 0; i < 16; i += 4) red_add_v4_f32(o + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
+      for (int i = 0; i < 16; i += 4) __stcg(reinterpret_cast<float4*>(o + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+    }
+    __threadfence();
+    asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps
+    if (et == 0) {
+      // monotonic counter: this launch's arrivals fill one block of `chunks` counts
+      const unsigned old = atomicAdd(&counters[g], 1u);
+      const unsigned target = (old / (unsigned)chunks + 1u) * (unsigned)chunks;
+      unsigned long long t0 = globaltimer_ns();
+      unsigned itn = 0;
+      while ((int)(*reinterpret_cast<volatile unsigned*>(&counters[g]) - target) < 0) {
+        __nanosleep(64);
+        if ((++itn & 0x3ff) == 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) {
+          printf("tfd: conv2 wgrad group %d rendezvous timed out\n", g);
+          __trap();
+        }
       }
+      __threadfence();
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    const int rows_valid = ntap * 32;                               // rows of this group that exist in dW
+    const int per = (rows_valid + chunks - 1) / chunks;             // rows this CTA finalises
+    const int r0 = blockIdx.x * per, r1 = min(rows_valid, r0 + per);
+    for (int idx = et + r0 * 64; idx < r1 * 64; idx += 128) {
+      float sacc = 0.f;
+      for (int c = 0; c < chunks; ++c) sacc += __ldcg(planes + (size_t)c * 8192 + idx);  // plane order: deterministic
+      dw[(size_t)g * 8192 + idx] = sacc;  // (g*4 + tap_local)*32*64 + ci*64 + co  ==  g*8192 + idx
     }
   }
   tc_fence_before();
@@ -312,49 +399,101 @@ int num_sms() { return tfd_num_sms(); }
 
 }  // namespace
 
-extern "C" int tfd_conv2_fwd(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
-                             void* stream) {
+static int conv2_grid(int tiles, int tf) {
+  int grid = tf ? 2 * tiles : tiles;  // tf32: (tile, channel half) work items, even CTAs half 0 / odd CTAs half 1
+  const int cap = tf ? (num_sms() & ~1) : num_sms();
+  return grid < cap ? grid : cap;
+}
+
+extern "C" int tfd_conv2_fwd(int dtype, const void* in, const void* w, const float* b, void* pool_out,
+                             unsigned char* argmax, int B, void* stream) {
+  TFD_REQUIRE(dtype == TFD_DTYPE_BF16 || dtype == TFD_DTYPE_TF32, "conv2_fwd: unknown operand type %d", dtype);
+  const int tf = dtype == TFD_DTYPE_TF32;
   CUtensorMap tmA, tmW;
-  int rc = tfd_make_tmap_nhwc_bf16(&tmA, in, B, 14, 14, 32, 1, 12, 16, 64);
+  int rc = tf ? tfd_make_tmap_nhwc(&tmA, in, B, 14, 14, 32, 1, 12, 16, 32, 128, 4)
+              : tfd_make_tmap_nhwc_bf16(&tmA, in, B, 14, 14, 32, 1, 12, 16, 64);
   if (rc) return rc;
-  rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
+  // filter [800][64]: bf16 whole rows; tf32 one 32-channel half per box, 32 B swizzle atoms (MN-major B operand)
+  rc = tf ? tfd_make_tmap_2d(&tmW, w, 800, 64, 64, 200, 32, 129, 4) : tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
   if (rc) return rc;
-  using C = ConvCfg<true>;
-  if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<true>), C::kSmem)) return arc;
   const int tiles = B * 2;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<true>, dim3(grid), dim3(kThreads), C::kSmem, static_cast<cudaStream_t>(stream),
-                            tmA, tmW, b, static_cast<bf16*>(pool_out), argmax, (float*)nullptr, B, tiles));
+  const int grid = conv2_grid(tiles, tf);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (tf) {
+    using C = ConvCfg<true, 1>;
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<true, 1>), C::kSmem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<true, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW, b, pool_out,
+                              argmax, (float*)nullptr, B, tiles, 0LL));
+  } else {
+    using C = ConvCfg<true, 0>;
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<true, 0>), C::kSmem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<true, 0>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW, b, pool_out,
+                              argmax, (float*)nullptr, B, tiles, 0LL));
+  }
   return 0;
 }
 
-extern "C" int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, void* stream) {
+extern "C" int tfd_conv2_dgrad(int dtype, const void* dy, const void* w, float* dx, int B, void* stream) {
+  TFD_REQUIRE(dtype == TFD_DTYPE_BF16 || dtype == TFD_DTYPE_TF32, "conv2_dgrad: unknown operand type %d", dtype);
+  const int tf = dtype == TFD_DTYPE_TF32;
   CUtensorMap tmA, tmW;
-  int rc = tfd_make_tmap_nhwc_bf16(&tmA, dy, B, 14, 14, 64, 1, 12, 16, 128);
+  int rc = tf ? tfd_make_tmap_nhwc(&tmA, dy, B, 14, 14, 64, 1, 12, 16, 32, 128, 4)
+              : tfd_make_tmap_nhwc_bf16(&tmA, dy, B, 14, 14, 64, 1, 12, 16, 128);
   if (rc) return rc;
-  rc = tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
+  rc = tf ? tfd_make_tmap_2d(&tmW, w, 800, 64, 64, 200, 32, 128, 4) : tfd_make_tmap_2d_bf16(&tmW, w, 800, 64, 64, 200, 64, 128);
   if (rc) return rc;
-  using C = ConvCfg<false>;
-  if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<false>), C::kSmem)) return arc;
   const int tiles = B * 2;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<false>, dim3(grid), dim3(kThreads), C::kSmem, static_cast<cudaStream_t>(stream),
-                            tmA, tmW, (const float*)nullptr, (bf16*)nullptr, (unsigned char*)nullptr, dx, B, tiles));
+  const int grid = conv2_grid(tiles, tf);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (tf) {
+    using C = ConvCfg<false, 1>;
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<false, 1>), C::kSmem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<false, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW,
+                              (const float*)nullptr, (void*)nullptr, (unsigned char*)nullptr, dx, B, tiles,
+                              (long long)B * 14 * 14 * 32));
+  } else {
+    using C = ConvCfg<false, 0>;
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<false, 0>), C::kSmem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<false, 0>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW,
+                              (const float*)nullptr, (void*)nullptr, (unsigned char*)nullptr, dx, B, tiles, 0LL));
+  }
   return 0;
 }
 
-extern "C" int tfd_conv2_wgrad(const void* in, const void* dy, float* dw, int B, void* stream) {
-  CUtensorMap tmIn, tmDy;
-  int rc = tfd_make_tmap_nhwc_bf16(&tmIn, in, B, 14, 14, 32, 4, 2, 16, 64);
-  if (rc) return rc;
-  rc = tfd_make_tmap_nhwc_bf16(&tmDy, dy, B, 14, 14, 64, 4, 2, 16, 128);
-  if (rc) return rc;
-  if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel), kWgSmem)) return arc;
+static int wgrad_chunks(int B) {
   const int tiles = ((B + 3) / 4) * 7;
   int chunks = num_sms() / 7;
   if (chunks > tiles) chunks = tiles;
   if (chunks < 1) chunks = 1;
-  TFD_CUDA_CHECK(tfd_launch(conv2_wgrad_tc_kernel, dim3(chunks, 7), dim3(kThreads), kWgSmem, static_cast<cudaStream_t>(stream),
-                            tmIn, tmDy, dw, tiles));
+  return chunks;
+}
+
+extern "C" long long tfd_conv2_wgrad_scratch_floats(int B) {
+  return (long long)kWgCounterWords + 7LL * wgrad_chunks(B) * 8192;
+}
+
+extern "C" int tfd_conv2_wgrad(int dtype, const void* in, const void* dy, float* dw, float* scratch, int B, void* stream) {
+  TFD_REQUIRE(dtype == TFD_DTYPE_BF16 || dtype == TFD_DTYPE_TF32, "conv2_wgrad: unknown operand type %d", dtype);
+  TFD_REQUIRE(scratch != nullptr, "conv2_wgrad: scratch planes missing (tfd_conv2_wgrad_scratch_floats(B) floats, zeroed once)");
+  const int tf = dtype == TFD_DTYPE_TF32;
+  CUtensorMap tmIn, tmDy;
+  int rc = tf ? tfd_make_tmap_nhwc(&tmIn, in, B, 14, 14, 32, 4, 2, 16, 32, 129, 4)
+              : tfd_make_tmap_nhwc_bf16(&tmIn, in, B, 14, 14, 32, 4, 2, 16, 64);
+  if (rc) return rc;
+  rc = tf ? tfd_make_tmap_nhwc(&tmDy, dy, B, 14, 14, 64, 4, 2, 16, 32, 129, 4)
+          : tfd_make_tmap_nhwc_bf16(&tmDy, dy, B, 14, 14, 64, 4, 2, 16, 128);
+  if (rc) return rc;
+  const int tiles = ((B + 3) / 4) * 7;
+  const int chunks = wgrad_chunks(B);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (tf) {
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel<1>), WgCfg<1>::kSmem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(conv2_wgrad_tc_kernel<1>, dim3(chunks, 7), dim3(kThreads), WgCfg<1>::kSmem, st, tmIn, tmDy, dw,
+                              scratch, tiles));
+  } else {
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel<0>), WgCfg<0>::kSmem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(conv2_wgrad_tc_kernel<0>, dim3(chunks, 7), dim3(kThreads), WgCfg<0>::kSmem, st, tmIn, tmDy, dw,
+                              scratch, tiles));
+  }
   return 0;
 }

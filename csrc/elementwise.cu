@@ -28,6 +28,26 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 }
 __device__ __forceinline__ float u01(uint32_t x) { return ((float)x + 0.5f) * 2.3283064365386963e-10f; }
 
+// Activation storage type of a precision arm: bf16 (bf16 tensor-core operands) or float (tf32 arm).
+__device__ __forceinline__ float to_f(bf16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f(float v) { return v; }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16(v); }
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+
+// "Last block" bookkeeping of the fixed-order reductions below: every block adds 1 to a monotonic counter after its
+// partial results are visible (fence); the block that takes the launch's last ticket does the final sum.  The counter
+// is never reset, so a kernel can sit in a CUDA graph and be replayed.
+__device__ __forceinline__ bool last_block_arrives(unsigned* counter, unsigned nblocks) {
+  __shared__ unsigned s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) % nblocks == nblocks - 1u) ? 1u : 0u;
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0;
+}
+
 __global__ void random_normal_kernel(float* __restrict__ out, long long n, unsigned long long seed, float stddev,
                                      long long off4) {
   grid_dep_wait();
@@ -59,21 +79,26 @@ __global__ void cast_bf16_kernel(const float* __restrict__ src, long long ld_src
 // ------------------------------------------------------------------------------------------------
 // conv1 forward: 5x5 SAME, 1 -> 32, + bias + ReLU + 2x2 max pool.  grid (B, 2): half image per block.
 // warp = pooled row, lane = output channel; the 6x6 input window is a shared-memory broadcast.
-// ------------------------------------------------------------------------------------------------
 //
-// Gated form (parameter server on other GPUs): w and b point into the owner shards' peer-mapped arenas.  The block
-// first loads its input patch (local), then waits until the owners' parameter version flags have reached this
-// worker's step counter, and only then reads the 3.3 KB of filter + bias over NVLink, once per block through shared
-// memory.  The pull of conv1's parameters is thereby inside the first kernel of the step instead of in a copy
-// kernel in front of it.
+// Gate (ps cluster workers): conv1 is the first kernel of a step.  Its blocks first load their input patch, then one
+// thread waits until every parameter shard's version word IN THIS GPU'S OWN MEMORY has reached the worker's step
+// counter -- the owner shards store the word (and, before it, the updated small parameters into this worker's mirror)
+// over NVLink at the end of their Adam kernel -- so the wait costs local L2 polls, not NVLink round trips, and no
+// stand-alone pull kernel sits in front of the step.
+// ------------------------------------------------------------------------------------------------
+struct GateList {
+  const unsigned* flag[TFD_MAX_SEG];
+  int n;
+  const unsigned* want_ptr;
+};
+
+template <typename T>
 __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict__ x, const float* w, const float* b,
-                                                        bf16* __restrict__ out, unsigned char* __restrict__ amax,
-                                                        const unsigned* gate0, const unsigned* gate1,
-                                                        const unsigned* want_ptr) {
+                                                        T* __restrict__ out, unsigned char* __restrict__ amax,
+                                                        const __grid_constant__ GateList gate) {
   grid_dep_wait();
   grid_dep_launch();
   __shared__ __align__(16) float patch[18][32];  // input rows 14*half-2 .. +17, cols -2 .. 29
-  __shared__ __align__(16) float wsm[26 * 32];   // gated form only: filter [25][32] + bias [32]
   const int n = blockIdx.x, half = blockIdx.y;
   for (int i = threadIdx.x; i < 18 * 32; i += blockDim.x) {
     const int pr = i >> 5, pc = i & 31;
@@ -83,22 +108,12 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
   const int c = threadIdx.x & 31, prow = threadIdx.x >> 5;  // pooled row inside the half: 0..6
   float wr[25];
   float bias;
-  if (gate0) {
-    if (threadIdx.x == 0) {
-      const unsigned want = *want_ptr;
-      spin_until_ge(gate0, want, "conv1: parameter version");
-      if (gate1) spin_until_ge(gate1, want, "conv1: parameter version (bias shard)");
-    }
-    __syncthreads();
-    if (threadIdx.x < 200) {
-      reinterpret_cast<float4*>(wsm)[threadIdx.x] = __ldcg(reinterpret_cast<const float4*>(w) + threadIdx.x);
-    } else if (threadIdx.x < 208) {
-      reinterpret_cast<float4*>(wsm)[threadIdx.x] = __ldcg(reinterpret_cast<const float4*>(b) + (threadIdx.x - 200));
-    }
+  if (gate.n > 0) {
+    if ((int)threadIdx.x < gate.n) spin_until_ge(gate.flag[threadIdx.x], *gate.want_ptr, "conv1: parameter version");
     __syncthreads();
 #pragma unroll
-    for (int t = 0; t < 25; ++t) wr[t] = wsm[t * 32 + c];
-    bias = wsm[800 + c];
+    for (int t = 0; t < 25; ++t) wr[t] = __ldcg(w + t * 32 + c);  // the mirror was written by another GPU: read at L2
+    bias = __ldcg(b + c);
   } else {
 #pragma unroll
     for (int t = 0; t < 25; ++t) wr[t] = w[t * 32 + c];
@@ -133,52 +148,60 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
         if (acc > best) { best = acc; bi = dy * 2 + dx; }
       }
     const long long o = (((long long)n * 14 + ph) * 14 + pw) * 32 + c;
-    out[o] = __float2bfloat16(best);
+    out[o] = from_f<T>(best);
     amax[o] = (unsigned char)bi;
   }
 }
 
 // conv1 filter gradient: pool/ReLU backward folded in (only the arg-max position of each 2x2 window carries
-// gradient).  grid (B, 2 pixel halves), 256 threads: lane = channel, 8 pixel groups; block-level reduce, then atomics.
-__global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
-                                                          const bf16* __restrict__ pool, const unsigned char* __restrict__ amax,
-                                                          float* __restrict__ dw, float* __restrict__ db) {
+// gradient).  One block per PAIR of images, 16 warps: warp = (image of the pair, pixel group), lane = channel.
+// dpool arrives as nsplit partial planes (the tf32 conv2 dgrad splits its K over two CTAs) that are added here in
+// plane order.  Reduction without atomics: warps -> shared memory (fixed order) -> one partial [26][32] per block in
+// `scratch` -> the last block to finish sums the blocks' partials in block order and writes dw / db (which may be
+// staging slots on another GPU).  scratch = 16 counter words + ceil(B/2) * 832 floats, zeroed once by the caller.
+template <typename T>
+__global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
+                                                          int nsplit, long long split_stride, const T* __restrict__ pool,
+                                                          const unsigned char* __restrict__ amax, float* __restrict__ dw,
+                                                          float* __restrict__ db, float* __restrict__ scratch, int B) {
   grid_dep_wait();
   grid_dep_launch();
-  __shared__ float img[32][33];
+  __shared__ float img[2][32][33];
   __shared__ float red[8][26][32];
-  const int n = blockIdx.x;
-  for (int i = threadIdx.x; i < 32 * 32; i += blockDim.x) {
-    const int r = (i >> 5) - 2, c = (i & 31) - 2;
-    img[i >> 5][i & 31] = (r >= 0 && r < 28 && c >= 0 && c < 28) ? x[(long long)n * 784 + r * 28 + c] : 0.f;
+  const int n0 = blockIdx.x * 2;
+  for (int i = threadIdx.x; i < 2 * 32 * 32; i += blockDim.x) {
+    const int im = i >> 10, r = ((i >> 5) & 31) - 2, c = (i & 31) - 2;
+    const int n = n0 + im;
+    img[im][(i >> 5) & 31][i & 31] = (n < B && r >= 0 && r < 28 && c >= 0 && c < 28) ? x[(long long)n * 784 + r * 28 + c] : 0.f;
   }
   __syncthreads();
-  const int c = threadIdx.x & 31, grp = threadIdx.x >> 5;
+  const int c = threadIdx.x & 31, wrp = threadIdx.x >> 5, im = wrp >> 3, grp = wrp & 7;
+  const int n = n0 + im;
   float acc[25];
 #pragma unroll
   for (int t = 0; t < 25; ++t) acc[t] = 0.f;
   float accb = 0.f;
-  const int pbeg = blockIdx.y * 98;
-  // 98 pixels / 8 groups = at most 13 per thread: issue all their global loads first (the loop below would
-  // otherwise sit on one dependent load chain per pixel), then do the shared-memory / FMA work
-  float gq[13];
-  int aq[13];
+  // 196 pixels / 8 groups = at most 25 per thread: issue all their global loads first (the loop below would otherwise
+  // sit on one dependent load chain per pixel), then do the shared-memory / FMA work
+  float gq[25];
+  int aq[25];
 #pragma unroll
-  for (int it = 0; it < 13; ++it) {
-    const int pix = pbeg + grp + it * 8;
+  for (int it = 0; it < 25; ++it) {
+    const int pix = grp + it * 8;
     gq[it] = 0.f;
     aq[it] = 0;
-    if (pix < pbeg + 98) {
+    if (pix < 196 && n < B) {
       const long long idx = ((long long)n * 196 + pix) * 32 + c;
-      const float g = dpool[idx];
-      gq[it] = (__bfloat162float(pool[idx]) > 0.f) ? g : 0.f;
+      float g = dpool[idx];
+      for (int sp = 1; sp < nsplit; ++sp) g += dpool[sp * split_stride + idx];
+      gq[it] = (to_f(pool[idx]) > 0.f) ? g : 0.f;
       aq[it] = amax[idx];
     }
   }
 #pragma unroll
-  for (int it = 0; it < 13; ++it) {
-    const int pix = pbeg + grp + it * 8;
-    if (pix >= pbeg + 98) break;
+  for (int it = 0; it < 25; ++it) {
+    const int pix = grp + it * 8;
+    if (pix >= 196) break;
     const int ph = pix / 14, pw = pix % 14;
     const float g = gq[it];
     const int h = 2 * ph + (aq[it] >> 1), wq = 2 * pw + (aq[it] & 1);
@@ -186,27 +209,56 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
 #pragma unroll
     for (int kh = 0; kh < 5; ++kh)
 #pragma unroll
-      for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(g, img[h + kh][wq + kw], acc[kh * 5 + kw]);
+      for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(g, img[im][h + kh][wq + kw], acc[kh * 5 + kw]);
   }
+  // image 1's warps deposit, image 0's warps add on top: a fixed order
+  if (im == 1) {
 #pragma unroll
-  for (int t = 0; t < 25; ++t) red[grp][t][c] = acc[t];
-  red[grp][25][c] = accb;
+    for (int t = 0; t < 25; ++t) red[grp][t][c] = acc[t];
+    red[grp][25][c] = accb;
+  }
   __syncthreads();
+  if (im == 0) {
+#pragma unroll
+    for (int t = 0; t < 25; ++t) red[grp][t][c] += acc[t];
+    red[grp][25][c] += accb;
+  }
+  __syncthreads();
+  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
+  float* parts = scratch + 16;
   for (int i = threadIdx.x; i < 26 * 32; i += blockDim.x) {
     const int t = i >> 5, cc = i & 31;
     float s = 0.f;
 #pragma unroll
-    for (int gq = 0; gq < 8; ++gq) s += red[gq][t][cc];
-    if (t < 25) atomicAdd(dw + t * 32 + cc, s);
-    else atomicAdd(db + cc, s);
+    for (int g8 = 0; g8 < 8; ++g8) s += red[g8][t][cc];
+    __stcg(parts + (size_t)blockIdx.x * 832 + i, s);
+  }
+  if (!last_block_arrives(counter, gridDim.x)) return;
+  for (int i = threadIdx.x; i < 26 * 32; i += blockDim.x) {
+    float s = 0.f;
+    int bk = 0;
+    for (; bk + 8 <= (int)gridDim.x; bk += 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(parts + (size_t)(bk + u) * 832 + i);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) s += v[u];
+    }
+    for (; bk < (int)gridDim.x; ++bk) s += __ldcg(parts + (size_t)bk * 832 + i);
+    if (i < 800) dw[i] = s;
+    else db[i - 800] = s;
   }
 }
 
 // pool2 + ReLU backward: dpool fp32 [nsplit][B,7,7,64] (split-K partials of the fc1 dgrad, summed here)
-// -> dy bf16 [B,14,14,64]; db[64] += sum.  Block = 64 channels x 4 pixel lanes, 16 pooled pixels per block.
+// -> dy [B,14,14,64] (activation type T); db[64] = sum.  Block = 64 channels x 4 pixel lanes, 16 pooled pixels per
+// block.  The bias gradient goes through per-block partials in `scratch` (16 counter words + nblocks * 64 floats,
+// zeroed once) and a last-block sum in block order: no atomics.
+template <typename T>
 __global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict__ dpool, int nsplit, long long split_stride,
-                                                        const bf16* __restrict__ pool, const unsigned char* __restrict__ amax,
-                                                        bf16* __restrict__ dy, float* __restrict__ db, long long npix) {
+                                                        const T* __restrict__ pool, const unsigned char* __restrict__ amax,
+                                                        T* __restrict__ dy, float* __restrict__ db,
+                                                        float* __restrict__ scratch, long long npix) {
   grid_dep_wait();
   grid_dep_launch();
   __shared__ float red[256];
@@ -223,7 +275,7 @@ __global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict_
     g[it] = 0.f; pv[it] = 0.f; am[it] = 0;
     if (pp[it] < npix) {
       for (int sp = 0; sp < nsplit; ++sp) g[it] += dpool[sp * split_stride + idx];
-      pv[it] = __bfloat162float(pool[idx]);
+      pv[it] = to_f(pool[idx]);
       am[it] = amax[idx];
     }
   }
@@ -234,7 +286,7 @@ __global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict_
     const float gg = pv[it] > 0.f ? g[it] : 0.f;
     const int pw = (int)(p % 7), ph = (int)((p / 7) % 7);
     const long long n = p / 49;
-    const bf16 gb = __float2bfloat16(gg), z = __float2bfloat16(0.f);
+    const T gb = from_f<T>(gg), z = from_f<T>(0.f);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const long long o = (((n * 14 + 2 * ph + (q >> 1)) * 14) + 2 * pw + (q & 1)) * 64 + c;
@@ -244,19 +296,30 @@ __global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict_
   }
   red[threadIdx.x] = gsum;
   __syncthreads();
+  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
+  float* parts = scratch + 16;
   if (threadIdx.x < 64)
-    atomicAdd(db + threadIdx.x, red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192]);
+    __stcg(parts + (size_t)blockIdx.x * 64 + threadIdx.x,
+           red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192]);
+  if (!last_block_arrives(counter, gridDim.x)) return;
+  // 4 row groups x 64 channels: each thread sums every 4th block's partial, then the four are added in order
+  float s = 0.f;
+  for (int bk = pl; bk < (int)gridDim.x; bk += 4) s += __ldcg(parts + (size_t)bk * 64 + c);
+  red[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x < 64) db[threadIdx.x] = red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192];
 }
 
 // ------------------------------------------------------------------------------------------------
 // head: rows phase
 // ------------------------------------------------------------------------------------------------
+template <typename T>
 __global__ void __launch_bounds__(256)
 head_rows_kernel(const float* __restrict__ pre, int pre_nsplit, long long pre_split_stride,
-                 const bf16* __restrict__ hid_in, const float* __restrict__ hid_bias,
+                 const T* __restrict__ hid_in, const float* __restrict__ hid_bias,
                  const float* __restrict__ out_w, const float* __restrict__ out_b, const float* __restrict__ labels,
                  int B, int H, long long ld_h, float keep_prob, unsigned long long seed, unsigned long long step_base,
-                 const unsigned* __restrict__ step_ptr, int training, bf16* __restrict__ hid_out, bf16* __restrict__ dhid, float* __restrict__ dlogits,
+                 const unsigned* __restrict__ step_ptr, int training, T* __restrict__ hid_out, T* __restrict__ dhid, float* __restrict__ dlogits,
                  float* __restrict__ loss_row, unsigned char* __restrict__ hit, unsigned char* __restrict__ keep_out) {
   grid_dep_wait();
   grid_dep_launch();
@@ -285,12 +348,12 @@ head_rows_kernel(const float* __restrict__ pre, int pre_nsplit, long long pre_sp
         a = keep ? a * inv_keep : 0.f;
         if (keep_out) keep_out[(long long)r * H + k] = keep;
       }
-      // the value every consumer sees is the bf16-rounded one
-      const bf16 ab = __float2bfloat16(a);
+      // the value every consumer sees is the stored one (bf16-rounded on the bf16 arm)
+      const T ab = from_f<T>(a);
       hid_out[(long long)r * ld_h + k] = ab;
-      a = __bfloat162float(ab);
+      a = to_f(ab);
     } else {
-      a = __bfloat162float(hid_in[(long long)r * ld_h + k]);
+      a = to_f(hid_in[(long long)r * ld_h + k]);
     }
     sh[k] = a;
   }
@@ -356,14 +419,15 @@ head_rows_kernel(const float* __restrict__ pre, int pre_nsplit, long long pre_sp
 #pragma unroll
     for (int j = 0; j < 10; ++j) g = fmaf(d[j], __ldg(wr + j), g);
     g = (sh[k] > 0.f) ? g * (pre ? inv_keep : 1.f) : 0.f;  // ReLU' and the dropout mask (kept <=> sh>0 or relu==0)
-    dhid[(long long)r * ld_h + k] = __float2bfloat16(g);
+    dhid[(long long)r * ld_h + k] = from_f<T>(g);
   }
 }
 
 // head: columns phase.  32 columns per block: lane = column, warp = row group; the 8 row groups are reduced
 // through shared memory in a fixed order (deterministic, no atomics).
+template <typename T>
 __global__ void __launch_bounds__(256)
-head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, long long ld_h,
+head_cols_kernel(const T* __restrict__ hid, const T* __restrict__ dhid, long long ld_h,
                  const float* __restrict__ dlogits, const float* __restrict__ loss_row,
                  const unsigned char* __restrict__ hit, int B, int H, float* __restrict__ d_out_w,
                  float* __restrict__ d_hid_bias, float* __restrict__ d_out_b, float* __restrict__ scalars) {
@@ -382,8 +446,8 @@ head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, lo
     float sb = 0.f;
     if (k < H) {
       for (int r = wv; r < B; r += 8) {
-        const float hv = __bfloat162float(hid[(long long)r * ld_h + k]);
-        sb += __bfloat162float(dhid[(long long)r * ld_h + k]);
+        const float hv = to_f(hid[(long long)r * ld_h + k]);
+        sb += to_f(dhid[(long long)r * ld_h + k]);
 #pragma unroll
         for (int j = 0; j < 10; ++j) acc[j] = fmaf(hv, dls[r * 10 + j], acc[j]);
       }
@@ -426,13 +490,14 @@ head_cols_kernel(const bf16* __restrict__ hid, const bf16* __restrict__ dhid, lo
   }
 }
 
-__global__ void colsum_bf16_kernel(const bf16* __restrict__ x, long long ld, int rows, int cols, float* __restrict__ out) {
+template <typename T>
+__global__ void colsum_kernel(const T* __restrict__ x, long long ld, int rows, int cols, float* __restrict__ out) {
   grid_dep_wait();
   grid_dep_launch();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= cols) return;
   float s = 0.f;
-  for (int r = 0; r < rows; ++r) s += __bfloat162float(x[(long long)r * ld + c]);
+  for (int r = 0; r < rows; ++r) s += to_f(x[(long long)r * ld + c]);
   out[c] = s;
 }
 
@@ -561,77 +626,121 @@ extern "C" int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long
   return 0;
 }
 
-extern "C" int tfd_conv1_fwd(const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
-                             void* stream) {
-  TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel, dim3(B, 2), dim3(224), 0, ST(stream), x, w, b, (bf16*)pool_out, argmax,
-                            (const unsigned*)nullptr, (const unsigned*)nullptr, (const unsigned*)nullptr));
+#define TFD_ACT_CHECK(name) \
+  TFD_REQUIRE(dtype == TFD_DTYPE_BF16 || dtype == TFD_DTYPE_TF32, name ": unknown activation type %d", dtype)
+
+extern "C" int tfd_conv1_fwd(int dtype, const float* x, const float* w, const float* b, void* pool_out,
+                             unsigned char* argmax, int B, const unsigned* const* gate_flags, int ngate,
+                             const unsigned* want_ptr, void* stream) {
+  TFD_ACT_CHECK("conv1_fwd");
+  TFD_REQUIRE(ngate >= 0 && ngate <= TFD_MAX_SEG && (ngate == 0 || (gate_flags && want_ptr)),
+              "conv1_fwd: bad gate list (%d flags)", ngate);
+  GateList gl;
+  memset(&gl, 0, sizeof(gl));
+  gl.n = ngate;
+  gl.want_ptr = want_ptr;
+  for (int i = 0; i < ngate; ++i) gl.flag[i] = gate_flags[i];
+  if (dtype == TFD_DTYPE_TF32)
+    TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel<float>, dim3(B, 2), dim3(224), 0, ST(stream), x, w, b, (float*)pool_out, argmax, gl));
+  else
+    TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel<bf16>, dim3(B, 2), dim3(224), 0, ST(stream), x, w, b, (bf16*)pool_out, argmax, gl));
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int tfd_conv1_fwd_gated(const float* x, const float* w_peer, const float* b_peer, void* pool_out,
-                                   unsigned char* argmax, int B, const unsigned* gate_w, const unsigned* gate_b,
-                                   const unsigned* want_ptr, void* stream) {
-  TFD_REQUIRE(gate_w != nullptr && want_ptr != nullptr, "conv1_fwd_gated: version flag and step counter are required");
-  TFD_REQUIRE(((uintptr_t)w_peer & 15) == 0 && ((uintptr_t)b_peer & 15) == 0, "conv1_fwd_gated: w/b must be 16-byte aligned");
-  TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel, dim3(B, 2), dim3(224), 0, ST(stream), x, w_peer, b_peer, (bf16*)pool_out,
-                            argmax, gate_w, gate_b == gate_w ? (const unsigned*)nullptr : gate_b, want_ptr));
+extern "C" long long tfd_conv1_wgrad_scratch_floats(int B) { return 16 + (long long)((B + 1) / 2) * 832; }
+extern "C" long long tfd_pool2_bwd_scratch_floats(int B) { return 16 + (((long long)B * 49 + 15) / 16) * 64; }
+
+extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, int nsplit, long long split_stride,
+                               const void* pool_out, const unsigned char* argmax, float* dw, float* db, float* scratch,
+                               int B, void* stream) {
+  TFD_ACT_CHECK("conv1_wgrad");
+  TFD_REQUIRE(scratch != nullptr && nsplit >= 1, "conv1_wgrad: scratch missing or nsplit %d < 1", nsplit);
+  const dim3 grid((B + 1) / 2);
+  if (dtype == TFD_DTYPE_TF32)
+    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<float>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
+                              (const float*)pool_out, argmax, dw, db, scratch, B));
+  else
+    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<bf16>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
+                              (const bf16*)pool_out, argmax, dw, db, scratch, B));
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int tfd_conv1_wgrad(const float* x, const float* dpool, const void* pool_out, const unsigned char* argmax,
-                               float* dw, float* db, int B, void* stream) {
-  TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel, dim3(B, 2), dim3(256), 0, ST(stream), x, dpool, (const bf16*)pool_out, argmax, dw, db));
-  TFD_LAUNCH_CHECK();
-  return 0;
-}
-
-extern "C" int tfd_pool2_bwd(const float* dpool, int nsplit, long long split_stride, const void* pool_out,
-                             const unsigned char* argmax, void* dy, float* db, int B, void* stream) {
+extern "C" int tfd_pool2_bwd(int dtype, const float* dpool, int nsplit, long long split_stride, const void* pool_out,
+                             const unsigned char* argmax, void* dy, float* db, float* scratch, int B, void* stream) {
+  TFD_ACT_CHECK("pool2_bwd");
+  TFD_REQUIRE(scratch != nullptr, "pool2_bwd: scratch missing");
   const long long npix = (long long)B * 49;
-  TFD_CUDA_CHECK(tfd_launch(pool2_bwd_kernel, dim3((unsigned)((npix + 15) / 16)), dim3(256), 0, ST(stream), dpool, nsplit < 1 ? 1 : nsplit, split_stride,
-                                                                       (const bf16*)pool_out, argmax, (bf16*)dy, db, npix));
+  const dim3 grid((unsigned)((npix + 15) / 16));
+  if (dtype == TFD_DTYPE_TF32)
+    TFD_CUDA_CHECK(tfd_launch(pool2_bwd_kernel<float>, grid, dim3(256), 0, ST(stream), dpool, nsplit < 1 ? 1 : nsplit,
+                              split_stride, (const float*)pool_out, argmax, (float*)dy, db, scratch, npix));
+  else
+    TFD_CUDA_CHECK(tfd_launch(pool2_bwd_kernel<bf16>, grid, dim3(256), 0, ST(stream), dpool, nsplit < 1 ? 1 : nsplit,
+                              split_stride, (const bf16*)pool_out, argmax, (bf16*)dy, db, scratch, npix));
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int tfd_head_rows(const float* pre_f32, int pre_nsplit, long long pre_split_stride, const void* hid_bf16, const float* hid_bias, const float* out_w,
-                             const float* out_b, const float* labels, int B, int H, long long ld_h, float keep_prob,
-                             unsigned long long seed, unsigned long long step, const unsigned* step_ptr, int training,
-                             void* hid_out, void* dhid, float* dlogits, float* loss_row, unsigned char* hit,
-                             unsigned char* keep_mask_out, void* stream) {
-  TFD_REQUIRE((pre_f32 != nullptr) != (hid_bf16 != nullptr), "head_rows: exactly one of pre_f32 / hid_bf16");
+extern "C" int tfd_head_rows(int dtype, const float* pre_f32, int pre_nsplit, long long pre_split_stride, const void* hid_in,
+                             const float* hid_bias, const float* out_w, const float* out_b, const float* labels, int B,
+                             int H, long long ld_h, float keep_prob, unsigned long long seed, unsigned long long step,
+                             const unsigned* step_ptr, int training, void* hid_out, void* dhid, float* dlogits,
+                             float* loss_row, unsigned char* hit, unsigned char* keep_mask_out, void* stream) {
+  TFD_ACT_CHECK("head_rows");
+  TFD_REQUIRE((pre_f32 != nullptr) != (hid_in != nullptr), "head_rows: exactly one of pre_f32 / hid_in");
   TFD_REQUIRE(!pre_f32 || (hid_bias && hid_out), "head_rows: pre_f32 mode needs hid_bias and hid_out");
   TFD_REQUIRE(!training || dhid, "head_rows: training needs dhid");
   const size_t smem = (size_t)(H + 96) * sizeof(float);
   TFD_REQUIRE(smem <= 200 * 1024, "head_rows: H=%d too large", H);
-  if (smem > 48 * 1024)
-    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_rows_kernel), (int)smem)) return arc;
-  TFD_CUDA_CHECK(tfd_launch(head_rows_kernel, dim3(B), dim3(256), smem, ST(stream), pre_f32, pre_nsplit < 1 ? 1 : pre_nsplit, pre_split_stride,
-                                                 (const bf16*)hid_bf16, hid_bias, out_w, out_b, labels, B, H, ld_h,
-                                                 keep_prob, seed, step, step_ptr, training, (bf16*)hid_out, (bf16*)dhid, dlogits,
-                                                 loss_row, hit, keep_mask_out));
+  if (dtype == TFD_DTYPE_TF32) {
+    if (smem > 48 * 1024)
+      if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_rows_kernel<float>), (int)smem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(head_rows_kernel<float>, dim3(B), dim3(256), smem, ST(stream), pre_f32, pre_nsplit < 1 ? 1 : pre_nsplit,
+                              pre_split_stride, (const float*)hid_in, hid_bias, out_w, out_b, labels, B, H, ld_h, keep_prob,
+                              seed, step, step_ptr, training, (float*)hid_out, (float*)dhid, dlogits, loss_row, hit,
+                              keep_mask_out));
+  } else {
+    if (smem > 48 * 1024)
+      if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_rows_kernel<bf16>), (int)smem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(head_rows_kernel<bf16>, dim3(B), dim3(256), smem, ST(stream), pre_f32, pre_nsplit < 1 ? 1 : pre_nsplit,
+                              pre_split_stride, (const bf16*)hid_in, hid_bias, out_w, out_b, labels, B, H, ld_h, keep_prob,
+                              seed, step, step_ptr, training, (bf16*)hid_out, (bf16*)dhid, dlogits, loss_row, hit,
+                              keep_mask_out));
+  }
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int tfd_head_cols(const void* hid, const void* dhid, long long ld_h, const float* dlogits,
+extern "C" int tfd_head_cols(int dtype, const void* hid, const void* dhid, long long ld_h, const float* dlogits,
                              const float* loss_row, const unsigned char* hit, int B, int H, float* d_out_w,
                              float* d_hid_bias, float* d_out_b, float* scalars, void* stream) {
+  TFD_ACT_CHECK("head_cols");
   const size_t smem = ((size_t)B * 10 + 8 * 11 * 32) * sizeof(float);
   TFD_REQUIRE(smem <= 200 * 1024, "head_cols: batch %d too large for the dlogits tile", B);
-  if (smem > 48 * 1024)
-    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_cols_kernel), (int)smem)) return arc;
   const int blocks = hid ? (H + 31) / 32 : 1;
-  TFD_CUDA_CHECK(tfd_launch(head_cols_kernel, dim3(blocks), dim3(256), smem, ST(stream), (const bf16*)hid, (const bf16*)dhid, ld_h, dlogits, loss_row, hit, B,
-                                                      H, d_out_w, d_hid_bias, d_out_b, scalars));
+  if (dtype == TFD_DTYPE_TF32) {
+    if (smem > 48 * 1024)
+      if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_cols_kernel<float>), (int)smem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(head_cols_kernel<float>, dim3(blocks), dim3(256), smem, ST(stream), (const float*)hid,
+                              (const float*)dhid, ld_h, dlogits, loss_row, hit, B, H, d_out_w, d_hid_bias, d_out_b, scalars));
+  } else {
+    if (smem > 48 * 1024)
+      if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(head_cols_kernel<bf16>), (int)smem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(head_cols_kernel<bf16>, dim3(blocks), dim3(256), smem, ST(stream), (const bf16*)hid,
+                              (const bf16*)dhid, ld_h, dlogits, loss_row, hit, B, H, d_out_w, d_hid_bias, d_out_b, scalars));
+  }
   TFD_LAUNCH_CHECK();
   return 0;
 }
 
-extern "C" int tfd_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out, void* stream) {
-  TFD_CUDA_CHECK(tfd_launch(colsum_bf16_kernel, dim3((cols + 255) / 256), dim3(256), 0, ST(stream), (const bf16*)x, ld, rows, cols, out));
+extern "C" int tfd_colsum(int dtype, const void* x, long long ld, int rows, int cols, float* out, void* stream) {
+  TFD_ACT_CHECK("colsum");
+  if (dtype == TFD_DTYPE_TF32)
+    TFD_CUDA_CHECK(tfd_launch(colsum_kernel<float>, dim3((cols + 255) / 256), dim3(256), 0, ST(stream), (const float*)x, ld, rows, cols, out));
+  else
+    TFD_CUDA_CHECK(tfd_launch(colsum_kernel<bf16>, dim3((cols + 255) / 256), dim3(256), 0, ST(stream), (const bf16*)x, ld, rows, cols, out));
   TFD_LAUNCH_CHECK();
   return 0;
 }

@@ -28,7 +28,7 @@ namespace {
 using namespace tfd;
 
 constexpr int BM = 128;
-constexpr int BK = 64;
+constexpr int kBKbf16 = 64;  // K elements per pipeline stage for bf16 operands (32 for tf32): 128 B either way
 constexpr int kThreads = 192;
 constexpr int kMaxSeg = TFD_MAX_SEG;
 
@@ -67,6 +67,22 @@ struct GemmParams {
   float* dbias;                 // [64] += sum of the surviving gradient (conv2 bias gradient)
 };
 
+// Element-type dependent tile constants.  A pipeline stage always holds BM x 128 B of A and BN x 128 B of B: 64 bf16 or
+// 32 tf32 (fp32 in memory; the tensor core reads the upper 19 bits) along K per stage, four MMAs per stage either way
+// (UMMA K = 32 B / element size).  An MN-major operand arrives as boxes of [BK k-rows][128 B]:
+//   bf16: 64 elements wide, 128B swizzle (16 B chunks), descriptor LBO = box stride, SBO = 1024 (8 k-rows)
+//   tf32: 32 elements wide, 128B swizzle with 32 B atoms (the only MN-major layout the tf32 MMA reads: 4 k-rows per
+//         swizzle atom), descriptor layout type 1, SBO = 512, eight k-rows (= one MMA) every 1024 B
+template <int TF>
+struct El {
+  static constexpr int kBK = TF ? 32 : 64;            // elements along K per stage
+  static constexpr int kMnW = TF ? 32 : 64;           // elements along M/N per MN-major box (128 B)
+  static constexpr int kMnBoxBytes = kBK * 128;       // 4 KB / 8 KB
+  static constexpr int kMnKStep = TF ? 1024 : 2048;   // bytes between consecutive MMAs' k-rows in an MN-major box
+  static constexpr uint32_t kMnSbo = TF ? 512 : 1024;
+  static constexpr uint32_t kMnSwz = TF ? kSwz128B32 : kSwz128;
+};
+
 template <int BN>
 struct Cfg {
   static constexpr int kStageBytes = BM * 128 + BN * 128;
@@ -82,11 +98,13 @@ __device__ __forceinline__ int find_seg(const SegInfo& sg, int row) {
   return s;
 }
 
-template <int A_MN, int B_MN, int BN>
+template <int A_MN, int B_MN, int BN, int TF>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ TmapArray tmBs, GemmParams p,
                const __grid_constant__ SegInfo sg) {
   using C = Cfg<BN>;
+  using E = El<TF>;
+  constexpr int BK = E::kBK;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.bar_off);
@@ -144,10 +162,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
         const int k0 = kb * BK;
         if (A_MN == 0) {
-          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);            // box [128 rows(m), 64 k]
+          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);            // box [128 rows(m), BK k]
         } else {
-          tma_load_2d(sa, &tmA, &full_bar[stage], m0, k0);            // box [64 rows(k), 64 m]
-          tma_load_2d(sa + 8192, &tmA, &full_bar[stage], m0 + 64, k0);
+#pragma unroll
+          for (int c = 0; c < BM / E::kMnW; ++c)                      // boxes [BK rows(k), 128 B of m]
+            tma_load_2d(sa + c * E::kMnBoxBytes, &tmA, &full_bar[stage], m0 + c * E::kMnW, k0);
         }
         if (B_MN == 0) {
           tma_load_2d(sb, &tmBs.m[seg_n], &full_bar[stage], k0, nrow0);  // box [BN rows(n), 64 k]
@@ -162,7 +181,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
 #pragma unroll
-          for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmBs.m[s], &full_bar[stage], n0 + c * 64, krow);
+          for (int c = 0; c < BN / E::kMnW; ++c)
+            tma_load_2d(sb + c * E::kMnBoxBytes, &tmBs.m[s], &full_bar[stage], n0 + c * E::kMnW, krow);
         }
         if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
@@ -170,7 +190,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+      constexpr uint32_t idesc = TF ? make_idesc_tf32(BM, BN, A_MN, B_MN) : make_idesc_bf16(BM, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
@@ -179,13 +199,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
         const uint32_t sb = sa + BM * 128;
 #pragma unroll
-        for (int ks = 0; ks < BK / 16; ++ks) {
-          // K-major: 16 bf16 = 32 B inside the 128 B swizzle row.  MN-major: 16 k-rows = two 1024 B atoms.
-          const uint64_t da = A_MN ? make_smem_desc(sa + ks * 2048, 8192, 1024, kSwz128)
+        for (int ks = 0; ks < 4; ++ks) {
+          // K-major: one MMA's K = 32 B inside the 128 B swizzle row.  MN-major: its k-rows are E::kMnKStep bytes
+          // further down the box (bf16: 16 rows = two 1024 B atoms; tf32: 8 rows = two 512 B atoms).
+          const uint64_t da = A_MN ? make_smem_desc(sa + ks * E::kMnKStep, E::kMnBoxBytes, E::kMnSbo, E::kMnSwz)
                                    : make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);
-          const uint64_t db = B_MN ? make_smem_desc(sb + ks * 2048, 8192, 1024, kSwz128)
+          const uint64_t db = B_MN ? make_smem_desc(sb + ks * E::kMnKStep, E::kMnBoxBytes, E::kMnSbo, E::kMnSwz)
                                    : make_smem_desc(sb + ks * 32, 16, 1024, kSwz128);
-          umma_bf16(tmem_base, da, db, idesc, (kb > kb_begin || ks > 0) ? 1u : 0u);
+          if (TF) umma_tf32(tmem_base, da, db, idesc, (kb > kb_begin || ks > 0) ? 1u : 0u);
+          else    umma_bf16(tmem_base, da, db, idesc, (kb > kb_begin || ks > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
         if (++stage == nstages) { stage = 0; phase ^= 1; }
@@ -341,9 +363,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 16; ++i)
           if (i < ncols) v[i] += __ldg(p.bias + col0 + i);
       }
-      if (p.mode == TFD_EPI_BIAS_RELU_BF16) {
+      if (p.mode == TFD_EPI_BIAS_RELU_BF16 || p.mode == TFD_EPI_BIAS_RELU_F32) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+      }
+      if (p.mode == TFD_EPI_RELUMASK_F32) {
+        const float* mrow = reinterpret_cast<const float*>(p.mask) + (long long)row * p.ld_mask + col0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (i < ncols && !(mrow[i] > 0.f)) v[i] = 0.f;
       }
       if (p.mode == TFD_EPI_RELUMASK_BF16) {
         const __nv_bfloat16* mrow = p.mask + (long long)row * p.ld_mask + col0;
@@ -351,7 +379,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 16; ++i)
           if (i < ncols && !(__bfloat162float(mrow[i]) > 0.f)) v[i] = 0.f;
       }
-      if (p.mode == TFD_EPI_STORE_F32) {
+      if (p.mode == TFD_EPI_STORE_F32 || p.mode == TFD_EPI_BIAS_RELU_F32 || p.mode == TFD_EPI_RELUMASK_F32) {
         float* o = out_f32 + (long long)blockIdx.z * p.split_stride + (long long)out_row * p.ld_out + col0;
         if (ncols == 16 && vec_ok) {
 #pragma unroll
@@ -392,10 +420,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
-template <int A_MN, int B_MN, int BN>
+template <int A_MN, int B_MN, int BN, int TF>
 int launch(const CUtensorMap& tmA, const TmapArray& tmBs, const GemmParams& p, const SegInfo& sg, cudaStream_t stream) {
   using C = Cfg<BN>;
-  auto kern = gemm_tc_kernel<A_MN, B_MN, BN>;
+  auto kern = gemm_tc_kernel<A_MN, B_MN, BN, TF>;
   if (int rc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(kern), C::kSmemBytes)) return rc;
   dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, p.splits);
   GemmParams q = p;
@@ -430,7 +458,7 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
                          const float* bias, const void* relu_mask, long long ld_mask, long long split_stride,
                          int seg_mode, int nseg, const int* seg_rows, void* const* out_ptrs,
                          const unsigned* const* wait_flags, unsigned wait_value, const unsigned* wait_value_ptr,
-                         const unsigned char* amax, float* dbias, void* stream);
+                         const unsigned char* amax, float* dbias, int dtype, void* stream);
 
 // Segmented form: the sharded operand is given as nseg pieces.  seg_rows[nseg+1] are the row boundaries of the
 // sharded dimension (K for TFD_SEG_B_K, N for TFD_SEG_B_N, M for TFD_SEG_OUT_M; multiples of 128, first = 0).
@@ -443,7 +471,21 @@ extern "C" int tfd_gemm_bf16_seg(const void* A, long long lda, int a_mn, const v
                                  const unsigned* wait_value_ptr, void* stream) {
   return gemm_seg_impl(A, lda, a_mn, B_ptrs, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
                        ld_mask, split_stride, seg_mode, nseg, seg_rows, out_ptrs, wait_flags, wait_value, wait_value_ptr,
-                       nullptr, nullptr, stream);
+                       nullptr, nullptr, TFD_DTYPE_BF16, stream);
+}
+
+// Same GEMM with the operand type as a parameter: TFD_DTYPE_BF16 (bf16 in memory) or TFD_DTYPE_TF32 (fp32 in memory,
+// tcgen05 kind::tf32: 10-bit mantissa products, fp32 accumulation) -- the precision arm that may be set against the
+// reference's fp32 graph (/root/reference/mnist_python_m.py:198-200).  Leading dimensions in elements of that type.
+extern "C" int tfd_gemm_seg(int dtype, const void* A, long long lda, int a_mn, const void* const* B_ptrs, long long ldb,
+                            int b_mn, int M, int N, int K, int bn, int splits, int mode, float alpha, void* out,
+                            long long ld_out, const float* bias, const void* relu_mask, long long ld_mask,
+                            long long split_stride, int seg_mode, int nseg, const int* seg_rows, void* const* out_ptrs,
+                            const unsigned* const* wait_flags, unsigned wait_value, const unsigned* wait_value_ptr,
+                            void* stream) {
+  return gemm_seg_impl(A, lda, a_mn, B_ptrs, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
+                       ld_mask, split_stride, seg_mode, nseg, seg_rows, out_ptrs, wait_flags, wait_value, wait_value_ptr,
+                       nullptr, nullptr, dtype, stream);
 }
 
 static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* const* B_ptrs, long long ldb, int b_mn, int M,
@@ -451,13 +493,20 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
                          const float* bias, const void* relu_mask, long long ld_mask, long long split_stride,
                          int seg_mode, int nseg, const int* seg_rows, void* const* out_ptrs,
                          const unsigned* const* wait_flags, unsigned wait_value, const unsigned* wait_value_ptr,
-                         const unsigned char* amax, float* dbias, void* stream) {
+                         const unsigned char* amax, float* dbias, int dtype, void* stream) {
   TFD_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+  TFD_REQUIRE(dtype == TFD_DTYPE_BF16 || dtype == TFD_DTYPE_TF32, "gemm: unknown operand type %d", dtype);
+  const int tf = dtype == TFD_DTYPE_TF32;
+  const int BK = tf ? 32 : 64, eb = tf ? 4 : 2, mnw = tf ? 32 : 64;
+  const int swz_mn = tf ? 129 : 128;  // MN-major boxes: 128B swizzle, 32 B atoms for tf32
   TFD_REQUIRE(bn == 64 || bn == 128 || bn == 256, "gemm: bn must be 64/128/256, got %d", bn);
   TFD_REQUIRE(nseg >= 1 && nseg <= kMaxSeg, "gemm: %d segments (max %d)", nseg, kMaxSeg);
   TFD_REQUIRE(seg_mode == TFD_SEG_NONE || seg_rows != nullptr, "gemm: segmented call without boundaries");
   TFD_REQUIRE(seg_mode != TFD_SEG_B_K || b_mn == 1, "gemm: TFD_SEG_B_K needs B stored [K,N]");
   TFD_REQUIRE(seg_mode != TFD_SEG_B_N || b_mn == 0, "gemm: TFD_SEG_B_N needs B stored [N,K]");
+  TFD_REQUIRE(!tf || mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32 || mode == TFD_EPI_BIAS_RELU_F32 ||
+                  mode == TFD_EPI_RELUMASK_F32,
+              "gemm: tf32 operands go with fp32 outputs (epilogue %d writes bf16)", mode);
   TFD_REQUIRE(seg_mode != TFD_SEG_OUT_M || mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32 ||
                   mode == TFD_EPI_STORE_BF16,
               "gemm: TFD_SEG_OUT_M needs a plain store epilogue (fp32, fp32 atomic or bf16)");
@@ -470,11 +519,13 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
   TFD_REQUIRE(p.splits == 1 || bias == nullptr, "gemm: bias with split-K would be added once per split");
   p.split_stride = split_stride;
   p.mode = mode; p.alpha = alpha;
-  p.out_f32 = (mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32) ? static_cast<float*>(out) : nullptr;
+  p.out_f32 = (mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32 || mode == TFD_EPI_BIAS_RELU_F32 ||
+               mode == TFD_EPI_RELUMASK_F32) ? static_cast<float*>(out) : nullptr;
   p.out_bf16 = p.out_f32 ? nullptr : static_cast<__nv_bfloat16*>(out);
   p.ld_out = ld_out; p.bias = bias;
   p.mask = static_cast<const __nv_bfloat16*>(relu_mask); p.ld_mask = ld_mask;
-  TFD_REQUIRE(mode != TFD_EPI_RELUMASK_BF16 || relu_mask, "gemm: relu-mask epilogue without a mask");
+  TFD_REQUIRE((mode != TFD_EPI_RELUMASK_BF16 && mode != TFD_EPI_RELUMASK_F32) || relu_mask,
+              "gemm: relu-mask epilogue without a mask");
   p.amax = amax; p.dbias = dbias;
   TFD_REQUIRE(mode != TFD_EPI_POOL2_BWD || (bn == 64 && N == 3136 && p.splits == 1 && relu_mask && amax && dbias),
               "gemm: the pool2-backward epilogue needs bn=64, N=3136, one split, pool2/argmax/dbias pointers");
@@ -497,24 +548,29 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
   CUtensorMap tmA;
   TmapArray tmBs;
   int rc;
-  if (a_mn == 0) rc = tfd_make_tmap_2d_bf16(&tmA, A, M, K, lda, BM, BK, 128);
-  else           rc = tfd_make_tmap_2d_bf16(&tmA, A, K, M, lda, BK, 64, 128);
+  if (a_mn == 0) rc = tfd_make_tmap_2d(&tmA, A, M, K, lda, BM, BK, 128, eb);
+  else           rc = tfd_make_tmap_2d(&tmA, A, K, M, lda, BK, mnw, swz_mn, eb);
   if (rc) return rc;
   const bool seg_b = (seg_mode == TFD_SEG_B_K || seg_mode == TFD_SEG_B_N);
   for (int s = 0; s < (seg_b ? nseg : 1); ++s) {
     const int rows = seg_b ? (sg.bound[s + 1] - sg.bound[s]) : (b_mn == 0 ? N : K);
     TFD_REQUIRE(rows > 0, "gemm: empty segment %d", s);
-    if (b_mn == 0) rc = tfd_make_tmap_2d_bf16(&tmBs.m[s], B_ptrs[s], rows, K, ldb, bn, BK, 128);
-    else           rc = tfd_make_tmap_2d_bf16(&tmBs.m[s], B_ptrs[s], rows, N, ldb, BK, 64, 128);
+    if (b_mn == 0) rc = tfd_make_tmap_2d(&tmBs.m[s], B_ptrs[s], rows, K, ldb, bn, BK, 128, eb);
+    else           rc = tfd_make_tmap_2d(&tmBs.m[s], B_ptrs[s], rows, N, ldb, BK, mnw, swz_mn, eb);
     if (rc) return rc;
   }
   for (int s = (seg_b ? nseg : 1); s < kMaxSeg; ++s) tmBs.m[s] = tmBs.m[0];
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-#define TFD_DISPATCH(AM, BMj)                                                  \
-  if (a_mn == AM && b_mn == BMj) {                                             \
-    if (bn == 64) return launch<AM, BMj, 64>(tmA, tmBs, p, sg, st);            \
-    if (bn == 128) return launch<AM, BMj, 128>(tmA, tmBs, p, sg, st);          \
-    return launch<AM, BMj, 256>(tmA, tmBs, p, sg, st);                         \
+#define TFD_DISPATCH(AM, BMj)                                                           \
+  if (a_mn == AM && b_mn == BMj) {                                                      \
+    if (tf) {                                                                           \
+      if (bn == 64) return launch<AM, BMj, 64, 1>(tmA, tmBs, p, sg, st);                \
+      if (bn == 128) return launch<AM, BMj, 128, 1>(tmA, tmBs, p, sg, st);              \
+      return launch<AM, BMj, 256, 1>(tmA, tmBs, p, sg, st);                             \
+    }                                                                                   \
+    if (bn == 64) return launch<AM, BMj, 64, 0>(tmA, tmBs, p, sg, st);                  \
+    if (bn == 128) return launch<AM, BMj, 128, 0>(tmA, tmBs, p, sg, st);                \
+    return launch<AM, BMj, 256, 0>(tmA, tmBs, p, sg, st);                               \
   }
   TFD_DISPATCH(0, 0) TFD_DISPATCH(0, 1) TFD_DISPATCH(1, 0) TFD_DISPATCH(1, 1)
 #undef TFD_DISPATCH
@@ -533,6 +589,15 @@ extern "C" int tfd_gemm_bf16(const void* A, long long lda, int a_mn, const void*
                            ld_mask, split_stride, TFD_SEG_NONE, 1, nullptr, nullptr, wf, wait_value, nullptr, stream);
 }
 
+extern "C" int tfd_gemm(int dtype, const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M,
+                        int N, int K, int bn, int splits, int mode, float alpha, void* out, long long ld_out,
+                        const float* bias, const void* relu_mask, long long ld_mask, long long split_stride,
+                        void* stream) {
+  const void* bp[1] = {B};
+  return tfd_gemm_seg(dtype, A, lda, a_mn, bp, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
+                      ld_mask, split_stride, TFD_SEG_NONE, 1, nullptr, nullptr, nullptr, 0, nullptr, stream);
+}
+
 // fc1 data gradient fused with the ReLU + 2x2 max-pool backward of the conv2 block: dy2 (bf16 [M,14,14,64], written
 // densely) and the conv2 bias gradient come straight out of the GEMM epilogue; the [M,3136] gradient of pool2 never
 // touches memory.  W is the [3136,1024] fc1 weight (bf16, row-sharded over nseg ps GPUs as in TFD_SEG_B_N).
@@ -543,7 +608,7 @@ extern "C" int tfd_gemm_dgrad_pool2(const void* dY, long long ldd, const void* c
   const int full[2] = {0, 3136};
   return gemm_seg_impl(dY, ldd, 0, W_ptrs, ldw, 0, M, 3136, 1024, 64, 1, TFD_EPI_POOL2_BWD, 1.0f, dy2, 0, nullptr, pool2,
                        3136, 0, nseg > 1 ? TFD_SEG_B_N : TFD_SEG_NONE, nseg, nseg > 1 ? seg_rows : full, nullptr,
-                       wait_flags, wait_value, wait_value_ptr, amax2, dbias, stream);
+                       wait_flags, wait_value, wait_value_ptr, amax2, dbias, TFD_DTYPE_BF16, stream);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -590,7 +655,7 @@ extern "C" int tfd_gemm_bf16_splitk_noalloc(const void* A, long long lda, int a_
                                             long long ld_out, const float* bias, int relu, void* stream) {
   TFD_REQUIRE(M > 0 && N > 0 && K > 0, "splitk_noalloc: empty problem %dx%dx%d", M, N, K);
   TFD_REQUIRE(splits >= 1, "splitk_noalloc: splits must be >= 1, got %d", splits);
-  const int kblocks = (K + BK - 1) / BK;
+  const int kblocks = (K + kBKbf16 - 1) / kBKbf16;
   if (splits > kblocks) splits = kblocks;
   const long long need = (long long)splits * M * N;
   TFD_REQUIRE(need <= kNoAllocScratchFloats,

@@ -40,52 +40,60 @@ static EncodeTiledFn get_encode_tiled() {
   return fn;
 }
 
-static CUtensorMapSwizzle swz(int bytes) {
-  switch (bytes) {
+static CUtensorMapSwizzle swz(int code) {
+  switch (code) {
+    case 129: return CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;  // 128 B span, 32 B atoms: MN-major tf32 operands
     case 128: return CU_TENSOR_MAP_SWIZZLE_128B;
     case 64: return CU_TENSOR_MAP_SWIZZLE_64B;
     case 32: return CU_TENSOR_MAP_SWIZZLE_32B;
     default: return CU_TENSOR_MAP_SWIZZLE_NONE;
   }
 }
+static int swz_span(int code) { return code == 129 ? 128 : code; }
 
-int tfd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                          uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+int tfd_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                     uint32_t box_cols, int swizzle, int elem_bytes) {
   EncodeTiledFn fn = get_encode_tiled();
   TFD_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  TFD_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "TMA element size %d unsupported", elem_bytes);
   TFD_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
-  TFD_REQUIRE((ld * 2) % 16 == 0, "TMA row pitch %llu B not a multiple of 16", (unsigned long long)(ld * 2));
-  TFD_REQUIRE(box_cols * 2 <= (uint32_t)(swizzle_bytes ? swizzle_bytes : 256) && box_rows <= 256 && box_cols <= 256,
-              "TMA box %ux%u does not fit swizzle %d", box_rows, box_cols, swizzle_bytes);
+  TFD_REQUIRE((ld * elem_bytes) % 16 == 0, "TMA row pitch %llu B not a multiple of 16",
+              (unsigned long long)(ld * elem_bytes));
+  TFD_REQUIRE(box_cols * elem_bytes <= (uint32_t)(swizzle ? swz_span(swizzle) : 256) && box_rows <= 256 && box_cols <= 256,
+              "TMA box %ux%u (%d-byte elements) does not fit swizzle %d", box_rows, box_cols, elem_bytes, swizzle);
   cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstr[1] = {ld * 2};
+  cuuint64_t gstr[1] = {ld * elem_bytes};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  TFD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2d %llux%llu ld %llu box %ux%u) failed: %d",
-              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols, (int)r);
+  CUresult r = fn(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(swizzle),
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TFD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2d %llux%llu ld %llu box %ux%u esz %d swz %d) failed: %d",
+              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols, elem_bytes,
+              swizzle, (int)r);
   return 0;
 }
 
-int tfd_make_tmap_nhwc_bf16(CUtensorMap* out, const void* base, uint64_t N, uint64_t H, uint64_t W, uint64_t C,
-                            uint32_t bn, uint32_t bh, uint32_t bw, int swizzle_bytes) {
+int tfd_make_tmap_nhwc(CUtensorMap* out, const void* base, uint64_t N, uint64_t H, uint64_t W, uint64_t C, uint32_t bn,
+                       uint32_t bh, uint32_t bw, uint32_t bc, int swizzle, int elem_bytes) {
   EncodeTiledFn fn = get_encode_tiled();
   TFD_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  TFD_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "TMA element size %d unsupported", elem_bytes);
   TFD_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
-  TFD_REQUIRE((C * 2) % 16 == 0 && (int)(C * 2) <= swizzle_bytes, "NHWC channel bytes %llu unsupported",
-              (unsigned long long)(C * 2));
+  TFD_REQUIRE((C * elem_bytes) % 16 == 0 && bc <= C && (int)(bc * elem_bytes) <= swz_span(swizzle),
+              "NHWC channel box %u of %llu (%d-byte elements) unsupported with swizzle %d", bc, (unsigned long long)C,
+              elem_bytes, swizzle);
+  const uint64_t e = (uint64_t)elem_bytes;
   cuuint64_t gdim[4] = {C, W, H, N};
-  cuuint64_t gstr[3] = {C * 2, W * C * 2, H * W * C * 2};
-  cuuint32_t box[4] = {(cuuint32_t)C, bw, bh, bn};
+  cuuint64_t gstr[3] = {C * e, W * C * e, H * W * C * e};
+  cuuint32_t box[4] = {bc, bw, bh, bn};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstr, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz(swizzle_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  TFD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(nhwc %llu,%llu,%llu,%llu box %u,%u,%u) failed: %d",
-              (unsigned long long)N, (unsigned long long)H, (unsigned long long)W, (unsigned long long)C, bn, bh, bw,
-              (int)r);
+  CUresult r = fn(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
+                  const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(swizzle),
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TFD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(nhwc %llu,%llu,%llu,%llu box %u,%u,%u,%u esz %d) failed: %d",
+              (unsigned long long)N, (unsigned long long)H, (unsigned long long)W, (unsigned long long)C, bn, bh, bw, bc,
+              elem_bytes, (int)r);
   return 0;
 }
 

@@ -184,7 +184,8 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
 
 // ---- UMMA descriptors (bit layout: cute/arch/mma_sm100_desc.hpp, SmemDescriptor / InstrDescriptor) ----
 // layout_type: 0 none(interleave), 2 = 128B swizzle, 4 = 64B swizzle, 6 = 32B swizzle
-constexpr uint32_t kSwz128 = 2, kSwz64 = 4, kSwz32 = 6, kSwzNone = 0;
+// 1 = 128B swizzle with 32 B atoms (the MN-major layout of 32-bit operands)
+constexpr uint32_t kSwz128 = 2, kSwz64 = 4, kSwz32 = 6, kSwzNone = 0, kSwz128B32 = 1;
 
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
                                                    uint32_t layout_type) {
@@ -206,6 +207,22 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn, i
          | ((uint32_t)b_mn << 16)     // b_major
          | ((uint32_t)(N >> 3) << 17) // n_dim
          | ((uint32_t)(M >> 4) << 24);// m_dim
+}
+
+// kind::tf32, A/B tf32 (fp32 words in shared memory), D fp32.  One MMA covers K = 8.
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4)                    // c_format  = F32
+         | (2u << 7)                  // a_format  = TF32
+         | (2u << 10)                 // b_format  = TF32
+         | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
 }
 
 // ---- misc ----
@@ -287,9 +304,18 @@ inline cudaError_t tfd_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 // ---------------------------------------------------------------------------------------------
 // host: tensor-map construction (driver entry point fetched at run time; no -lcuda needed)
 // ---------------------------------------------------------------------------------------------
-// 2D bf16 row-major [rows, cols] with leading dimension ld (elements).  box = [box_rows, box_cols].
-int tfd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                          uint32_t box_rows, uint32_t box_cols, int swizzle_bytes);
-// 4D bf16 NHWC [N,H,W,C]; box = [bn, bh, bw, C].
-int tfd_make_tmap_nhwc_bf16(CUtensorMap* out, const void* base, uint64_t N, uint64_t H, uint64_t W, uint64_t C,
-                            uint32_t bn, uint32_t bh, uint32_t bw, int swizzle_bytes);
+// 2D row-major [rows, cols] of elem_bytes-wide elements (2 = bf16, 4 = fp32) with leading dimension ld (elements).
+// box = [box_rows, box_cols].  swizzle: 0 / 32 / 64 / 128 bytes, or 129 = 128 B span swizzled in 32 B atoms.
+int tfd_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                     uint32_t box_cols, int swizzle, int elem_bytes);
+inline int tfd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                                 uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+  return tfd_make_tmap_2d(out, base, rows, cols, ld, box_rows, box_cols, swizzle_bytes, 2);
+}
+// 4D NHWC [N,H,W,C]; box = [bn, bh, bw, bc] starting at channel 0 (bc <= C: a channel-split box for fp32 maps).
+int tfd_make_tmap_nhwc(CUtensorMap* out, const void* base, uint64_t N, uint64_t H, uint64_t W, uint64_t C, uint32_t bn,
+                       uint32_t bh, uint32_t bw, uint32_t bc, int swizzle, int elem_bytes);
+inline int tfd_make_tmap_nhwc_bf16(CUtensorMap* out, const void* base, uint64_t N, uint64_t H, uint64_t W, uint64_t C,
+                                   uint32_t bn, uint32_t bh, uint32_t bw, int swizzle_bytes) {
+  return tfd_make_tmap_nhwc(out, base, N, H, W, C, bn, bh, bw, (uint32_t)C, swizzle_bytes, 2);
+}

@@ -27,6 +27,16 @@ int tfd_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, siz
 #define TFD_EPI_STORE_BF16 3     /* out bf16 = alpha*acc (+bias)                                    */
 #define TFD_EPI_RELUMASK_BF16 4  /* out bf16 = mask>0 ? alpha*acc : 0   (dgrad through a ReLU)      */
 #define TFD_EPI_POOL2_BWD 5      /* fc1 dgrad -> ReLU' -> max-pool backward, see tfd_gemm_dgrad_pool2 */
+#define TFD_EPI_BIAS_RELU_F32 6  /* out fp32 = relu(alpha*acc + bias)              (tf32 arm)       */
+#define TFD_EPI_RELUMASK_F32 7   /* out fp32 = mask>0 ? alpha*acc : 0, mask fp32   (tf32 arm)       */
+
+/* ---- operand types of the tensor-core kernels (the `dtype` / `precision` arguments) ----
+ * TFD_DTYPE_BF16: bf16 operands in memory (fp32 master weights keep a bf16 shadow), tcgen05 kind::f16.
+ * TFD_DTYPE_TF32: fp32 operands in memory, tcgen05 kind::tf32 (10-bit mantissa products, fp32 accumulation): no
+ *                 shadow, activations stay fp32 -- the arm comparable to the reference's all-fp32 graph
+ *                 (/root/reference/mnist_python_m.py:198-200). */
+#define TFD_DTYPE_BF16 0
+#define TFD_DTYPE_TF32 1
 
 /* tcgen05/TMEM/TMA GEMM, bf16 operands, fp32 accumulation: D[M,N] = A[M,K] * B[K,N].
  * a_mn=0: A stored [M,K] (K contiguous); a_mn=1: A stored [K,M].  b_mn=0: B stored [N,K]; b_mn=1: B stored [K,N].
@@ -54,6 +64,17 @@ int tfd_gemm_bf16_seg(const void* A, long long lda, int a_mn, const void* const*
                       const float* bias, const void* relu_mask, long long ld_mask, long long split_stride, int seg_mode,
                       int nseg, const int* seg_rows, void* const* out_ptrs, const unsigned* const* wait_flags,
                       unsigned wait_value, const unsigned* wait_value_ptr, void* stream);
+
+/* tfd_gemm_bf16 / tfd_gemm_bf16_seg with the operand type as the first argument (TFD_DTYPE_*); leading dimensions
+ * are in elements of that type; tf32 operands go with the fp32-output epilogues (0, 1, 6, 7). */
+int tfd_gemm(int dtype, const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M, int N,
+             int K, int bn, int splits, int mode, float alpha, void* out, long long ld_out, const float* bias,
+             const void* relu_mask, long long ld_mask, long long split_stride, void* stream);
+int tfd_gemm_seg(int dtype, const void* A, long long lda, int a_mn, const void* const* B_ptrs, long long ldb, int b_mn,
+                 int M, int N, int K, int bn, int splits, int mode, float alpha, void* out, long long ld_out,
+                 const float* bias, const void* relu_mask, long long ld_mask, long long split_stride, int seg_mode,
+                 int nseg, const int* seg_rows, void* const* out_ptrs, const unsigned* const* wait_flags,
+                 unsigned wait_value, const unsigned* wait_value_ptr, void* stream);
 
 /* Split-K GEMM that allocates nothing: out[M,N] fp32 = A*B (+bias, optional ReLU), same operand conventions as
  * tfd_gemm_bf16.  No counterpart in the reference (it has no native code and no allocator contract at all).
@@ -91,62 +112,75 @@ int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long long ld_ds
 int tfd_random_normal(float* out, long long n, unsigned long long seed, float stddev, long long elem_offset,
                       void* stream);
 
+/* ---- the CNN's layer kernels.  `dtype` selects the precision arm: TFD_DTYPE_BF16 -> activations are bf16 and the
+ * tensor-core weights are bf16 shadows; TFD_DTYPE_TF32 -> activations and weights are fp32 (read as tf32). ---- */
+
 /* conv1 5x5 SAME 1->32 + bias + ReLU + 2x2 max-pool (m:109-111).  x fp32 [B,784]; w fp32 [25,32] (HWIO);
- * out bf16 [B,14,14,32]; argmax u8 [B,14,14,32] (0..3 = position inside the 2x2 window). */
-int tfd_conv1_fwd(const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
-                  void* stream);
-/* Same op with the parameter pull inside the kernel: w_peer / b_peer point into the owner shards' (peer-mapped)
- * arenas; every block waits until *gate_w (and *gate_b, if it is another shard) >= *want_ptr before it reads them. */
-int tfd_conv1_fwd_gated(const float* x, const float* w_peer, const float* b_peer, void* pool_out, unsigned char* argmax,
-                        int B, const unsigned* gate_w, const unsigned* gate_b, const unsigned* want_ptr, void* stream);
-/* conv1 filter/bias gradient with pool+ReLU backward folded in.  dpool fp32 [B,14,14,32] is d(loss)/d(pool1).
- * dw fp32 [25,32] and db fp32 [32] are ACCUMULATED with atomics (zero them first). */
-int tfd_conv1_wgrad(const float* x, const float* dpool, const void* pool_out, const unsigned char* argmax, float* dw,
-                    float* db, int B, void* stream);
+ * out [B,14,14,32] (activation type); argmax u8 [B,14,14,32] (0..3 = position inside the 2x2 window).
+ * gate_flags (optional, ngate <= TFD_MAX_SEG): every block first waits until each of these LOCAL version words has
+ * reached *want_ptr -- the parameter-server worker's wait for the owner shards' updates, folded into the step's
+ * first kernel (the owners store the words into this GPU's memory; nothing is polled over NVLink). */
+int tfd_conv1_fwd(int dtype, const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
+                  const unsigned* const* gate_flags, int ngate, const unsigned* want_ptr, void* stream);
+/* conv1 filter/bias gradient with pool+ReLU backward folded in.  dpool fp32: nsplit partial planes of
+ * d(loss)/d(pool1) [B,14,14,32], split_stride elements apart, added here in plane order.  dw fp32 [25,32] and db fp32
+ * [32] are WRITTEN (fixed-order reduction through `scratch`, no atomics; they may be peer-mapped staging slots).
+ * scratch: tfd_conv1_wgrad_scratch_floats(B) floats, zeroed once by the caller and then owned by this kernel. */
+long long tfd_conv1_wgrad_scratch_floats(int B);
+int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, int nsplit, long long split_stride, const void* pool_out,
+                    const unsigned char* argmax, float* dw, float* db, float* scratch, int B, void* stream);
 
 /* conv2 5x5 SAME 32->64 + bias + ReLU + 2x2 max-pool (m:114-116) on tcgen05: implicit GEMM, im2col by TMA
- * 4-D boxes with out-of-bounds zero fill, filter resident in shared memory.  in bf16 [B,14,14,32];
- * w bf16 [800,64] (HWIO flattened; may be a peer pointer); out bf16 [B,7,7,64]; argmax u8 [B,7,7,64]. */
-int tfd_conv2_fwd(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
+ * 4-D boxes with out-of-bounds zero fill, filter resident in shared memory (tf32: one 32-channel half per CTA).
+ * in [B,14,14,32]; w [800,64] (HWIO flattened; bf16 shadow or the fp32 master; may be a peer pointer);
+ * out [B,7,7,64]; argmax u8 [B,7,7,64]. */
+int tfd_conv2_fwd(int dtype, const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
                   void* stream);
-/* d(loss)/d(pool1) fp32 [B,14,14,32] = conv2 data gradient of dy bf16 [B,14,14,64] (tcgen05 implicit GEMM). */
-int tfd_conv2_dgrad(const void* dy, const void* w, float* dx, int B, void* stream);
-/* dW fp32 [800,64] += im2col(in)^T dy (tcgen05, split over pixel tiles, red.add epilogue; zero dW first). */
-int tfd_conv2_wgrad(const void* in, const void* dy, float* dw, int B, void* stream);
-/* CUDA-core references of the three conv2 kernels (validation only; same argument meaning). */
+/* d(loss)/d(pool1) fp32 = conv2 data gradient of dy [B,14,14,64] (tcgen05 implicit GEMM).  bf16: dx is ONE plane
+ * [B,14,14,32]; tf32: TWO partial planes (one per half of dy's channels), B*14*14*32 floats apart, which
+ * tfd_conv1_wgrad adds (nsplit = 2). */
+int tfd_conv2_dgrad(int dtype, const void* dy, const void* w, float* dx, int B, void* stream);
+/* dW fp32 [800,64] = im2col(in)^T dy (tcgen05, split over pixel tiles; per-CTA partial planes in `scratch`, summed in
+ * plane order: deterministic, no atomics; dW is WRITTEN and may be a peer-mapped staging slot).
+ * scratch: tfd_conv2_wgrad_scratch_floats(B) floats, zeroed once by the caller. */
+long long tfd_conv2_wgrad_scratch_floats(int B);
+int tfd_conv2_wgrad(int dtype, const void* in, const void* dy, float* dw, float* scratch, int B, void* stream);
+/* CUDA-core references of the three conv2 kernels (bf16 arm, validation only; wgrad ACCUMULATES into a zeroed dw). */
 int tfd_conv2_fwd_ref(const void* in, const void* w, const float* b, void* pool_out, unsigned char* argmax, int B,
                       void* stream);
 int tfd_conv2_dgrad_ref(const void* dy, const void* w, float* dx, int B, void* stream);
 int tfd_conv2_wgrad_ref(const void* in, const void* dy, float* dw, int B, void* stream);
 
 /* max-pool + ReLU backward of the conv2 block: dpool fp32 [nsplit][B,7,7,64] (split-K partials, summed here;
- * split_stride in elements) -> dy bf16 [B,14,14,64] (dense, zeros written); db fp32 [64] accumulated with atomics. */
-int tfd_pool2_bwd(const float* dpool, int nsplit, long long split_stride, const void* pool_out,
-                  const unsigned char* argmax, void* dy, float* db, int B, void* stream);
+ * split_stride in elements) -> dy [B,14,14,64] (dense, zeros written); db fp32 [64] WRITTEN (fixed-order reduction
+ * through `scratch` = tfd_pool2_bwd_scratch_floats(B) floats, zeroed once). */
+long long tfd_pool2_bwd_scratch_floats(int B);
+int tfd_pool2_bwd(int dtype, const float* dpool, int nsplit, long long split_stride, const void* pool_out,
+                  const unsigned char* argmax, void* dy, float* db, float* scratch, int B, void* stream);
 
 /* Head, row phase (one block per example): optional fc bias + ReLU + inverted dropout (m:121-124), output
  * layer (m:127), softmax cross entropy with dense labels (m:205), dlogits=(softmax-y)/B, accuracy hit
  * (m:206-207) and the gradient flowing back into the hidden layer.
  *   pre_f32 != NULL: hidden = dropout(relu(sum_s pre_f32[s] + hid_bias))   (CNN fc1; pre_f32 holds pre_nsplit
  *                    split-K partial planes, pre_split_stride elements apart: the GEMM never needs atomics)
- *   else           : hidden = hid_bf16 (already bias+ReLU'd by the GEMM epilogue; MLP)
- * Writes hid_out bf16 [B,ld_h] (post-dropout, for the output-layer wgrad), dhid bf16 [B,ld_h] (training only),
- * dlogits fp32 [B,10], loss_row fp32 [B], hit u8 [B]. keep_prob>=1 disables dropout.  The dropout stream is
- * Philox(seed; step + *step_ptr, element): step_ptr (optional, device) lets a captured CUDA graph advance it. */
-int tfd_head_rows(const float* pre_f32, int pre_nsplit, long long pre_split_stride, const void* hid_bf16, const float* hid_bias, const float* out_w,
-                  const float* out_b, const float* labels, int B, int H, long long ld_h, float keep_prob,
-                  unsigned long long seed, unsigned long long step, const unsigned* step_ptr, int training,
-                  void* hid_out, void* dhid, float* dlogits, float* loss_row, unsigned char* hit,
-                  unsigned char* keep_mask_out, void* stream);
+ *   else           : hidden = hid_in (already bias+ReLU'd by the GEMM epilogue; MLP)
+ * Writes hid_out [B,ld_h] (post-dropout, for the output-layer wgrad), dhid [B,ld_h] (training only) in the
+ * activation type, dlogits fp32 [B,10], loss_row fp32 [B], hit u8 [B]. keep_prob>=1 disables dropout.  The dropout
+ * stream is Philox(seed; step + *step_ptr, element): step_ptr (optional, device) lets a captured CUDA graph advance it. */
+int tfd_head_rows(int dtype, const float* pre_f32, int pre_nsplit, long long pre_split_stride, const void* hid_in,
+                  const float* hid_bias, const float* out_w, const float* out_b, const float* labels, int B, int H,
+                  long long ld_h, float keep_prob, unsigned long long seed, unsigned long long step,
+                  const unsigned* step_ptr, int training, void* hid_out, void* dhid, float* dlogits, float* loss_row,
+                  unsigned char* hit, unsigned char* keep_mask_out, void* stream);
 /* Head, column phase: d_out_w[H,10] = hid^T dlogits, d_hid_bias[H] = colsum(dhid), d_out_b[10], loss = mean,
  * acc = mean(hit).  Deterministic (no atomics).  scalars: fp32[2] = {loss, accuracy}. */
-int tfd_head_cols(const void* hid, const void* dhid, long long ld_h, const float* dlogits, const float* loss_row,
-                  const unsigned char* hit, int B, int H, float* d_out_w, float* d_hid_bias, float* d_out_b,
-                  float* scalars, void* stream);
-/* zero up to 16 fp32 buffers in one launch (accumulators of the atomic epilogues). */
+int tfd_head_cols(int dtype, const void* hid, const void* dhid, long long ld_h, const float* dlogits,
+                  const float* loss_row, const unsigned char* hit, int B, int H, float* d_out_w, float* d_hid_bias,
+                  float* d_out_b, float* scalars, void* stream);
+/* zero up to 16 fp32 buffers in one launch. */
 int tfd_zero_multi(float* const* ptrs, const long long* ns, int count, void* stream);
-/* column sums of a bf16 matrix (MLP hidden-layer bias gradients): out[N] = sum_r x[r, :]. */
-int tfd_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out, void* stream);
+/* column sums of an activation matrix (MLP hidden-layer bias gradients): out[N] = sum_r x[r, :]. */
+int tfd_colsum(int dtype, const void* x, long long ld, int rows, int cols, float* out, void* stream);
 
 /* ---- parameter-server kernels ---- */
 #define TFD_MAX_SLOTS 8 /* gradient staging slots (= workers) one shard reduces */

@@ -114,7 +114,8 @@ def run_ours(a, rank: int, world: int, local: int) -> Optional[dict]:
     B = a.batch
     if world == 1:
         from .engine_native import NativeEngine
-        eng = NativeEngine(spec, learning_rate=0.01, seed=0, init_stddev=a.init_stddev, device=str(device))
+        eng = NativeEngine(spec, learning_rate=0.01, seed=0, init_stddev=a.init_stddev, device=str(device),
+                           precision=a.precision)
         parallelism = "ps1+w1 on one GPU (sync)"
         workers = 1
     else:

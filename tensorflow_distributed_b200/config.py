@@ -43,7 +43,7 @@ class Flags:
     ps_shards: int = 0              # 0 => len(ps_hosts)
     synthetic: bool = True          # no network on the box: synthetic MNIST-shape data by default
     train_dir: str = ""             # "" => fresh tempfile.mkdtemp() like the reference (m:236)
-    precision: str = "bf16"         # bf16 tensor-core operands, fp32 master weights / accumulation
+    precision: str = "tf32"         # tensor-core operand type on the GPU path: tf32 (fp32 in memory) | bf16
     seed: int = 0
     keep_prob: float = 0.75         # m:292
     backend: str = "auto"           # auto | cpu | cuda
@@ -98,7 +98,9 @@ _HELP_EXTRA = {
     "ps_shards": "Parameter shards (0 => one per ps task)",
     "synthetic": "Use the deterministic MNIST-shaped synthetic set instead of idx files in data_dir",
     "train_dir": "Checkpoint directory (chief saves, everybody restores on start); '' => fresh temp dir",
-    "precision": "bf16 tensor-core operands with fp32 master weights and accumulation",
+    "precision": "Tensor-core operand type of the sm_100a kernels: tf32 (fp32 activations/weights read as tf32; the "
+                 "arm comparable to the reference's fp32 graph) | bf16 (bf16 activations + bf16 weight shadow); master "
+                 "weights, Adam slots, gradients and accumulation are fp32 in both",
     "seed": "Seed of the parameter init, the data stream and dropout",
     "keep_prob": "Dropout keep probability during training",
     "backend": "auto | cpu (fp32 oracle) | cuda (sm_100a kernels)",

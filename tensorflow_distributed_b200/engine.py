@@ -105,6 +105,7 @@ def make_engine(spec: ModelSpec, backend: str = "auto", **kw):
     if backend == "auto":
         backend = "cuda" if torch.cuda.is_available() else "cpu"
     if backend == "cpu":
+        kw.pop("precision", None)  # the oracle is fp32
         return OracleEngine(spec, device="cpu", **kw)
     if backend == "cuda":
         from .engine_native import NativeEngine

@@ -5,9 +5,14 @@ What the reference delegates to ``tf.Session.run`` on a graph TF differentiated 
 as an explicit forward + hand-written backward over the kernels of ``libtfd_b200.so``, captured once per
 (batch, mode) in a CUDA graph and replayed: one graph launch per training step, no host round trip inside.
 
-Precision policy: fp32 master weights, Adam slots and accumulators on the ps shard; bf16
-tensor-core operands (activations, and a bf16 shadow of the weights the ps publishes from inside the Adam
-kernel); fp32 gradients.
+Precision arms (the reference is fp32 end to end, m:198-200).  Both keep fp32 master weights, Adam
+slots, gradients and accumulators (TMEM) on the ps shard; they differ in what the tensor cores read:
+
+* ``tf32`` (default): activations and weights stay fp32 in memory and are read as tf32 by ``tcgen05 kind::tf32``
+  (10-bit mantissa products, fp32 accumulation); no weight shadow exists.  This is the arm whose numbers may be set
+  against an fp32 reference.
+* ``bf16``: bf16 activations and a bf16 shadow of the tensor-core weights that the ps republishes from inside the
+  Adam kernel: half the operand bytes.
 """
 from __future__ import annotations
 
@@ -29,11 +34,26 @@ def _pad8(n: int) -> int:
     return (n + 7) // 8 * 8
 
 
-def needs_shadow(spec: ModelSpec, name: str) -> bool:
-    """Tensors consumed by tensor-core kernels get a bf16 shadow; the rest are read in fp32."""
+PRECISIONS = ("tf32", "bf16")
+
+
+def default_precision() -> str:
+    p = os.environ.get("TFD_PRECISION", "tf32")
+    if p not in PRECISIONS:
+        raise ValueError("TFD_PRECISION must be one of %s" % (PRECISIONS,))
+    return p
+
+
+def tc_operand(spec: ModelSpec, name: str) -> bool:
+    """Weights consumed by tensor-core kernels (everything else is read in fp32 by CUDA-core kernels)."""
     if spec.kind == "cnn":
         return name in ("weights/wc2", "weights/wd1")
     return name.startswith("weights/h")
+
+
+def needs_shadow(spec: ModelSpec, name: str, precision: str = "bf16") -> bool:
+    """bf16 arm: tensor-core weights get a bf16 shadow.  tf32 arm: the kernels read the fp32 master, no shadow."""
+    return precision == "bf16" and tc_operand(spec, name)
 
 
 class ShardState:
@@ -43,10 +63,11 @@ class ShardState:
     peer-mapped (cudaIpc) heap; by default they are ordinary torch allocations.
     """
 
-    def __init__(self, spec: ModelSpec, placement: Placement, shard: int, device, alloc=None):
+    def __init__(self, spec: ModelSpec, placement: Placement, shard: int, device, alloc=None, precision: str = "bf16"):
         self.spec, self.placement, self.shard, self.device = spec, placement, shard, device
+        self.precision = precision
         self.n = placement.shard_sizes[shard]
-        self.pieces, self.shadow_off, self.shadow_ld, self.shadow_n = self.layout(spec, placement, shard)
+        self.pieces, self.shadow_off, self.shadow_ld, self.shadow_n = self.layout(spec, placement, shard, precision)
         alloc = alloc or (lambda name, numel, dtype: torch.zeros(numel, dtype=dtype, device=device))
         self.w = alloc("w", self.n, torch.float32)
         self.m = alloc("m", self.n, torch.float32)
@@ -55,13 +76,13 @@ class ShardState:
         self.ctrl = alloc("ctrl", 64, torch.int32)
 
     @staticmethod
-    def layout(spec: ModelSpec, placement: Placement, shard: int):
+    def layout(spec: ModelSpec, placement: Placement, shard: int, precision: str = "bf16"):
         pieces: List[nat.Piece] = []
         shadow_off: Dict[str, int] = {}
         shadow_ld: Dict[str, int] = {}
         off = 0
         for p in placement.shard_pieces(shard):
-            if needs_shadow(spec, p.var):
+            if needs_shadow(spec, p.var, precision):
                 ld = _pad8(p.cols)
                 pieces.append(nat.Piece(p.offset, p.numel, p.cols, ld, off))
                 shadow_off[p.var], shadow_ld[p.var] = off, ld
@@ -108,8 +129,10 @@ class ShardState:
 class Workspace:
     """Activations / gradients-of-activations for one batch size (all static: graph-capturable)."""
 
-    def __init__(self, spec: ModelSpec, B: int, device):
+    def __init__(self, spec: ModelSpec, B: int, device, precision: str = "bf16"):
         self.B = B
+        tf32 = precision == "tf32"
+        adt = torch.float32 if tf32 else torch.bfloat16  # activation storage type of the precision arm
         z = lambda *s, dtype=torch.float32: torch.zeros(*s, dtype=dtype, device=device)  # noqa: E731
         self.x = z(B, 784)
         self.y = z(B, 10)
@@ -121,23 +144,30 @@ class Workspace:
         self.dlogits, self.loss_row = z(B, 10), z(B)
         self.hit = z(B, dtype=torch.uint8)
         if spec.kind == "cnn":
-            self.pool1 = z(B, 14, 14, 32, dtype=torch.bfloat16)
+            self.pool1 = z(B, 14, 14, 32, dtype=adt)
             self.am1 = z(B, 14, 14, 32, dtype=torch.uint8)
-            self.pool2 = z(B, 7, 7, 64, dtype=torch.bfloat16)
+            self.pool2 = z(B, 7, 7, 64, dtype=adt)
             self.am2 = z(B, 7, 7, 64, dtype=torch.uint8)
-            self.fc1_splits = max(1, min(8, 148 // (((B + 127) // 128) * 16)))
+            kb = 3136 // (32 if tf32 else 64)  # K blocks of the fc1 forward GEMM
+            self.fc1_splits = max(1, min(8, kb, 148 // (((B + 127) // 128) * 16)))
             self.fc1acc = z(self.fc1_splits, B, 1024)   # split-K partial planes (summed by the head kernel)
-            self.hid = z(B, 1024, dtype=torch.bfloat16)
-            self.dhid = z(B, 1024, dtype=torch.bfloat16)
+            self.hid = z(B, 1024, dtype=adt)
+            self.dhid = z(B, 1024, dtype=adt)
             self.dg_splits = max(1, min(3, 148 // (((B + 127) // 128) * 49)))
             self.dpool2 = z(self.dg_splits, B, 3136)    # split-K partial planes (summed by pool2_bwd)
-            self.dy2 = z(B, 14, 14, 64, dtype=torch.bfloat16)
-            self.dpool1 = z(B, 14, 14, 32)
+            self.dy2 = z(B, 14, 14, 64, dtype=adt)
+            self.dp1_splits = 2 if tf32 else 1          # tf32 conv2 dgrad: one partial plane per half of dy's channels
+            self.dpool1 = z(self.dp1_splits, B, 14, 14, 32)
+            # reduction scratch of the deterministic gradient kernels (zeroed once; the kernels own the counters)
+            self.c1w_scratch = z(nat.scratch_floats("conv1_wgrad", B))
+            self.c2w_scratch = z(nat.scratch_floats("conv2_wgrad", B))
+            self.p2b_scratch = z(nat.scratch_floats("pool2_bwd", B))
             self.keep_mask = None
         else:
             dims = [784] + list(spec.hidden)
-            self.act = [z(B, _pad8(d), dtype=torch.bfloat16) for d in dims]
-            self.dact = [None] + [z(B, _pad8(d), dtype=torch.bfloat16) for d in dims[1:]]
+            # tf32: the fp32 input batch IS the first GEMM's A operand; bf16: it is cast once per step
+            self.act = [self.x if tf32 else z(B, _pad8(784), dtype=adt)] + [z(B, _pad8(d), dtype=adt) for d in dims[1:]]
+            self.dact = [None] + [z(B, _pad8(d), dtype=adt) for d in dims[1:]]
         self.graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
 
 
@@ -145,15 +175,15 @@ class NativeEngine:
     """Single-GPU engine: parameters live in one ShardState on the same device as the worker kernels."""
 
     name = "native-sm100a"
-    early_adam_var: Optional[str] = None  # big tensor whose Adam pass is launched early, under the rest of backward
 
     def __init__(self, spec: ModelSpec, learning_rate: float = 0.01, seed: int = 0, init_stddev: float = 1.0,
                  device: Optional[str] = None, use_graphs: bool = True, conv2_ref: bool = False,
-                 early_adam: Optional[bool] = None):
+                 precision: Optional[str] = None):
         if not torch.cuda.is_available():
             raise nat.NativeError("NativeEngine needs a CUDA device (backend=cpu selects the oracle engine)")
         nat.lib()
         self.spec = spec
+        self._set_precision(precision, conv2_ref)
         self.device = torch.device(device or ("cuda:%d" % torch.cuda.current_device()))
         torch.cuda.set_device(self.device)
         nat.set_device(self.device.index or 0)
@@ -162,16 +192,25 @@ class NativeEngine:
         self.dropout_seed = seed
         self.use_graphs, self.conv2_ref = use_graphs, conv2_ref
         self.placement = Placement(spec, 1)
-        self.shard = ShardState(spec, self.placement, 0, self.device)
+        self.shard = ShardState(spec, self.placement, 0, self.device, precision=self.precision)
         self.grad = torch.zeros(self.shard.n, dtype=torch.float32, device=self.device)
         self.slot_ptrs = [self.grad.data_ptr()]
         self.ws: Dict[int, Workspace] = {}
-        # Launching wd1's Adam pass early (under the conv backward chain) was measured: the step stays at ~0.120 ms
-        # because the overlapped kernels then contend for registers / DRAM (profiles/ANALYSIS.md); off by default.
-        if early_adam is None:
-            early_adam = os.environ.get("TFD_EARLY_ADAM", "0") == "1"
-        self.early_adam_var = "weights/wd1" if (spec.kind == "cnn" and early_adam) else None
         self.init_variables(seed, init_stddev)
+
+    def _set_precision(self, precision: Optional[str], conv2_ref: bool = False) -> None:
+        precision = precision or default_precision()
+        if precision not in PRECISIONS:
+            raise ValueError("precision must be one of %s, got %r" % (PRECISIONS, precision))
+        if conv2_ref and precision != "bf16":
+            raise ValueError("conv2_ref (CUDA-core validation kernels) exists for the bf16 arm only")
+        self.precision, self.tf32 = precision, precision == "tf32"
+        self.dtype_name = "tf32" if self.tf32 else "bf16"
+        if self.tf32:
+            for v in self.spec.variables:
+                if tc_operand(self.spec, v.name) and v.cols % 4:
+                    raise ValueError("tf32 arm: %s has %d columns; fp32 tensor-core operands need a multiple of 4"
+                                     % (v.name, v.cols))
 
     # ---- variables -------------------------------------------------------------------------
     def init_variables(self, seed: int, stddev: float) -> None:
@@ -191,7 +230,8 @@ class NativeEngine:
         return self.shard.view(self.shard.w, name)
 
     def S(self, name: str) -> torch.Tensor:
-        return self.shard.shadow_view(name)
+        """What the tensor cores read for weight `name`: its bf16 shadow, or (tf32 arm) the fp32 master itself."""
+        return self.P(name) if self.tf32 else self.shard.shadow_view(name)
 
     def G(self, name: str) -> torch.Tensor:
         return self.shard.view(self.grad, name)
@@ -227,7 +267,7 @@ class NativeEngine:
 
     def workspace(self, B: int) -> Workspace:
         if B not in self.ws:
-            self.ws[B] = Workspace(self.spec, B, self.device)
+            self.ws[B] = Workspace(self.spec, B, self.device, self.precision)
         return self.ws[B]
 
     # ---- GEMM hooks: the multi-GPU worker overrides these to address ps shards over NVLink ----------
@@ -237,7 +277,7 @@ class NativeEngine:
         W = self.S(wname)
         K, N = W.shape[0], self.spec.by_name()[wname].cols
         nat.gemm_bf16(A, 0, W, 1, M, N, K, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride, bias=bias,
-                      ld_out=ld_out)
+                      ld_out=ld_out, tf32=self.tf32)
 
     def gemm_dgrad(self, wname: str, dY, M: int, out, *, mode: int, bn: int, splits: int = 1, split_stride: int = 0,
                    relu_mask=None, ld_out: Optional[int] = None) -> None:
@@ -245,17 +285,12 @@ class NativeEngine:
         W = self.S(wname)
         K, N = W.shape[0], self.spec.by_name()[wname].cols
         nat.gemm_bf16(dY, 0, W, 0, M, K, N, out, mode=mode, bn=bn, splits=splits, split_stride=split_stride,
-                      relu_mask=relu_mask, ld_out=ld_out)
+                      relu_mask=relu_mask, ld_out=ld_out, tf32=self.tf32)
 
     def gemm_wgrad(self, wname: str, X, dY, Bsz: int, *, bn: int) -> None:
         """dW[K,N] = X^T dY  (both MN-major, contraction over the batch); written where the gradient lives."""
         G = self.G(wname)
-        nat.gemm_bf16(X, 1, dY, 1, G.shape[0], G.shape[1], Bsz, G, mode=nat.EPI_STORE_F32, bn=bn)
-
-    def gemm_dgrad_pool2(self, ws) -> None:
-        """fc1 dgrad -> ReLU' -> max-pool backward in one kernel: writes ws.dy2 and accumulates the conv2 bias grad."""
-        W = self.S("weights/wd1")
-        nat.gemm_dgrad_pool2(ws.dhid, [W.data_ptr()], W.stride(0), ws.B, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"))
+        nat.gemm_bf16(X, 1, dY, 1, G.shape[0], G.shape[1], Bsz, G, mode=nat.EPI_STORE_F32, bn=bn, tf32=self.tf32)
 
     def step_ptr(self):
         """Device word that advances once per training step (dropout stream, version gates)."""
@@ -277,8 +312,8 @@ class NativeEngine:
 
     _prio_default = "0"  # measured neutral on one GPU (0.1213 vs 0.1207 ms); the ps cluster engine turns it on
 
-    def conv1_fwd(self, ws: "Workspace") -> None:
-        nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, ws.B)
+    def conv1_fwd(self, ws: "Workspace", training: bool = True) -> None:
+        nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, ws.B, tf32=self.tf32)
 
     def _capture_stream(self):
         """Stream the step graph is captured on.  With TFD_PRIO=1 it has the highest priority, so the kernels of the
@@ -306,28 +341,13 @@ class NativeEngine:
         from .models import mlp
         mlp.backward(self, ws)
 
-    _training_apply = False  # set by _sequence: True only when this step ends with an apply ("train" mode)
-
-    def _apply_early(self, var: str) -> None:
-        s = self.shard
-        p = s.piece_of(var)
-        o, n = p.offset, p.numel
-        piece = nat.Piece(0, n, p.cols, s.shadow_ld.get(var, 0), s.shadow_off.get(var, 0))
-        nat.adam_apply_part(s.w[o:], s.m[o:], s.v[o:], s.shadow, [self.grad.data_ptr() + 4 * o], 1, 1.0, n, [piece],
-                            self.lr, s.ctrl[CTRL_T:], 0, 0, False)
-
     def _apply(self) -> None:
         s = self.shard
-        skip = (0, 0)
-        if self.early_adam_var is not None:
-            p = s.piece_of(self.early_adam_var)
-            skip = (p.offset, p.offset + p.numel)
-        nat.adam_apply_part(s.w, s.m, s.v, s.shadow, self.slot_ptrs, 1, 1.0, s.n, s.pieces, self.lr, s.ctrl[CTRL_T:],
-                            skip[0], skip[1], True, None, s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:])
+        nat.adam_apply(s.w, s.m, s.v, s.shadow if not self.tf32 else None, self.slot_ptrs, 1, 1.0, s.n, s.pieces, self.lr,
+                       s.ctrl[CTRL_T:], None, s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:])
 
     def _sequence(self, ws: Workspace, mode: str, keep_prob: float, mask_out=None) -> None:
         training = mode in ("train", "grads")
-        self._training_apply = (mode == "train")
         self._pre_step(ws, training)
         if self.spec.kind == "cnn":
             self._cnn_forward(ws, training, keep_prob, mask_out)
@@ -340,7 +360,8 @@ class NativeEngine:
         if training:
             self._post_backward(ws)
         if not training:
-            nat.head_cols(None, None, 0, ws.dlogits, ws.loss_row, ws.hit, ws.B, 1, None, None, None, ws.scalars)
+            nat.head_cols(None, None, 0, ws.dlogits, ws.loss_row, ws.hit, ws.B, 1, None, None, None, ws.scalars,
+                          tf32=self.tf32)
         if mode == "train":
             self._apply()
 

@@ -1,8 +1,10 @@
 """The reference's CNN (``conv_net``, ``/root/reference/mnist_python_m.py:104-128``) as explicit kernel sequences:
 reshape -> conv5x5(1->32)+bias+ReLU -> pool2 -> conv5x5(32->64)+bias+ReLU -> pool2 -> flatten(3136, NHWC order) ->
 FC1024+ReLU -> dropout -> FC10, the loss of m:205 and the hand-written backward pass TF's autodiff generates at
-m:222.  ``eng`` supplies parameters (``P`` fp32, ``S`` bf16 shadow), gradient destinations (``G``) and the three
-GEMM hooks, so the same sequence runs on one GPU and on a ps/worker cluster (where the hooks address ps shards).
+m:222.  ``eng`` supplies parameters (``P`` fp32, ``S`` what the tensor cores read: the fp32 master on the tf32 arm, a
+bf16 shadow on the bf16 arm), gradient destinations (``G``) and the three GEMM hooks, so the same sequence runs on one
+GPU and on a ps/worker cluster (where the hooks address ps shards and ``G`` may be a staging slot on another GPU:
+every gradient kernel WRITES its result -- fixed-order reductions, no atomics, nothing to zero).
 """
 from __future__ import annotations
 
@@ -12,64 +14,42 @@ from ..ops import native as nat
 
 
 def forward(eng, ws: Workspace, training: bool, keep_prob: float, mask_out=None) -> None:
-    B = ws.B
-    if training:  # accumulators of the atomic epilogues (all tiny): cleared off the critical path
-        main = torch.cuda.current_stream()
-        s2 = eng._side_streams()[1]
-        s2.wait_stream(main)
-        with torch.cuda.stream(s2):
-            nat.zero_multi([eng.G("weights/wc1"), eng.G("biases/bc1"), eng.G("weights/wc2"),
-                            eng.G("biases/bc2")])
-    eng.conv1_fwd(ws)  # (on a ps cluster the pull of wc1/bc1 may be folded into this kernel)
-    nat.conv2_fwd(ws.pool1, eng.S("weights/wc2"), eng.P("biases/bc2"), ws.pool2, ws.am2, B, ref=eng.conv2_ref)
+    B, tf = ws.B, eng.tf32
+    eng.conv1_fwd(ws, training)  # (on a ps cluster this kernel also waits for the parameter version, locally)
+    nat.conv2_fwd(ws.pool1, eng.S("weights/wc2"), eng.P("biases/bc2"), ws.pool2, ws.am2, B, ref=eng.conv2_ref, tf32=tf)
     eng.gemm_fwd("weights/wd1", ws.pool2.view(B, 3136), B, ws.fc1acc, mode=nat.EPI_STORE_F32, bn=64,
                   splits=ws.fc1_splits, split_stride=B * 1024, ld_out=1024)
     nat.head_rows(ws.fc1acc, None, eng.P("biases/bd1"), eng.P("weights/out"), eng.P("biases/out"), ws.y, B,
                   1024, 1024, keep_prob if training else 1.0, eng.dropout_seed, 0, training, ws.hid,
                   ws.dhid if training else None, ws.dlogits, ws.loss_row, ws.hit, mask_out,
                   step_ptr=eng.step_ptr() if training else None, pre_nsplit=ws.fc1_splits,
-                  pre_split_stride=B * 1024)
+                  pre_split_stride=B * 1024, tf32=tf)
 
 
 def backward(eng, ws: Workspace) -> None:
     """Backward as a DAG: the weight-gradient kernels are leaves (nothing downstream reads them before the
-    push/apply), so they run on side streams -- graph branches after capture -- next to the critical path
+    apply), so they run on side streams -- graph branches after capture -- next to the critical path
     head -> fc1 dgrad -> pool2 bwd -> conv2 dgrad -> conv1 wgrad."""
-    B = ws.B
+    B, tf = ws.B, eng.tf32
     main = torch.cuda.current_stream()
     s1, s2 = eng._side_streams()
     s1.wait_stream(main)
     with torch.cuda.stream(s1):
         nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, eng.G("weights/out"),
-                      eng.G("biases/bd1"), eng.G("biases/out"), ws.scalars)
+                      eng.G("biases/bd1"), eng.G("biases/out"), ws.scalars, tf32=tf)
         # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
         eng.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
-    main.wait_stream(s2)  # the zeroed accumulators (d(bc2) is accumulated below)
-    early = eng.early_adam_var == "weights/wd1" and eng._training_apply
-    if getattr(eng, "fuse_dgrad_pool", False):
-        # fc1 dgrad fused with ReLU' and the 2x2 max-pool backward in the GEMM epilogue.  Measured (B=128): 25.6 us
-        # for the fused kernel (it cannot use split-K, so only 49 CTAs) vs 12.4 + 9.4 us for the two kernels below.
-        eng.gemm_dgrad_pool2(ws)
-    else:
-        # fc1 dgrad: dpool2[B,3136] = dhid wd1^T (wd1 read K-major in place), split-K partial planes summed by the
-        # pool2 / ReLU backward kernel
-        eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
-                       split_stride=B * 3136, ld_out=3136)
-        if early:
-            s1.wait_stream(main)  # the old weights have been read; wd1's Adam pass may overwrite them from here on
-        nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, eng.G("biases/bc2"), B, nsplit=ws.dg_splits,
-                      split_stride=B * 3136)
-    if early:
-        # wd1 is 98% of the parameter bytes: its Adam pass may start as soon as its gradient is complete and the
-        # dgrad above has read the old weights (see profiles/ANALYSIS.md; off by default)
-        if getattr(eng, "fuse_dgrad_pool", False):
-            s1.wait_stream(main)
-        with torch.cuda.stream(s1):
-            eng._apply_early("weights/wd1")
+    # fc1 dgrad: dpool2[B,3136] = dhid wd1^T (wd1 read K-major in place), split-K partial planes summed by the
+    # pool2 / ReLU backward kernel
+    eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
+                   split_stride=B * 3136, ld_out=3136)
+    nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, eng.G("biases/bc2"), ws.p2b_scratch, B, nsplit=ws.dg_splits,
+                  split_stride=B * 3136, tf32=tf)
     s2.wait_stream(main)
     with torch.cuda.stream(s2):
-        nat.conv2_wgrad(ws.pool1, ws.dy2, eng.G("weights/wc2"), B, ref=eng.conv2_ref)
-    nat.conv2_dgrad(ws.dy2, eng.S("weights/wc2"), ws.dpool1, B, ref=eng.conv2_ref)
-    nat.conv1_wgrad(ws.x, ws.dpool1, ws.pool1, ws.am1, eng.G("weights/wc1"), eng.G("biases/bc1"), B)
+        nat.conv2_wgrad(ws.pool1, ws.dy2, eng.G("weights/wc2"), ws.c2w_scratch, B, ref=eng.conv2_ref, tf32=tf)
+    nat.conv2_dgrad(ws.dy2, eng.S("weights/wc2"), ws.dpool1, B, ref=eng.conv2_ref, tf32=tf)
+    nat.conv1_wgrad(ws.x, ws.dpool1, ws.pool1, ws.am1, eng.G("weights/wc1"), eng.G("biases/bc1"), ws.c1w_scratch, B,
+                    tf32=tf, nsplit=ws.dp1_splits, split_stride=B * 14 * 14 * 32)
     main.wait_stream(s1)
     main.wait_stream(s2)

@@ -18,6 +18,8 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file_
 _lib: Optional[ctypes.CDLL] = None
 
 EPI_STORE_F32, EPI_ATOMIC_F32, EPI_BIAS_RELU_BF16, EPI_STORE_BF16, EPI_RELUMASK_BF16 = range(5)
+EPI_BIAS_RELU_F32, EPI_RELUMASK_F32 = 6, 7
+DTYPE_BF16, DTYPE_TF32 = 0, 1
 
 #: number of kernel launches issued through this binding (bench.py reports it as gpu_launches)
 launch_count = 0
@@ -99,11 +101,20 @@ def device_info(dev: int = 0) -> dict:
 def gemm_bf16(A, a_mn: int, B, b_mn: int, M: int, N: int, K: int, out, *, mode: int, bn: int = 128, splits: int = 1,
               alpha: float = 1.0, bias=None, relu_mask=None, lda: Optional[int] = None, ldb: Optional[int] = None,
               ld_out: Optional[int] = None, ld_mask: Optional[int] = None, wait_flag=None, wait_value: int = 0,
-              split_stride: int = 0) -> None:
+              split_stride: int = 0, tf32: bool = False) -> None:
+    """D[M,N] = A B on tcgen05.  tf32=False: bf16 operands; tf32=True: fp32 operands read as tf32 (kind::tf32)."""
     lda = lda if lda is not None else A.stride(0)
     ldb = ldb if ldb is not None else B.stride(0)
     ld_out = ld_out if ld_out is not None else out.stride(0)
     ld_mask = ld_mask if ld_mask is not None else (relu_mask.stride(0) if relu_mask is not None else 0)
+    if tf32:
+        assert wait_flag is None
+        _check(lib().tfd_gemm(c_int(DTYPE_TF32), _p(A), c_longlong(lda), c_int(a_mn), _p(B), c_longlong(ldb), c_int(b_mn),
+                              c_int(M), c_int(N), c_int(K), c_int(bn), c_int(splits), c_int(mode), c_float(alpha), _p(out),
+                              c_longlong(ld_out), _p(bias), _p(relu_mask), c_longlong(ld_mask), c_longlong(split_stride),
+                              _stream()), "tfd_gemm(tf32)")
+        _count()
+        return
     _check(lib().tfd_gemm_bf16(_p(A), c_longlong(lda), c_int(a_mn), _p(B), c_longlong(ldb), c_int(b_mn), c_int(M),
                                c_int(N), c_int(K), c_int(bn), c_int(splits), c_int(mode), c_float(alpha), _p(out),
                                c_longlong(ld_out), _p(bias), _p(relu_mask), c_longlong(ld_mask),
@@ -119,18 +130,18 @@ def gemm_bf16_seg(A, a_mn: int, B_ptrs, b_mn: int, M: int, N: int, K: int, out, 
                   ld_out: int, seg_mode: int, seg_rows, out_ptrs=None, wait_flags=None, wait_value: int = 0,
                   wait_value_ptr=None,
                   bn: int = 128, splits: int = 1, alpha: float = 1.0, bias=None, relu_mask=None, ld_mask: int = 0,
-                  split_stride: int = 0) -> None:
+                  split_stride: int = 0, tf32: bool = False) -> None:
     """Sharded GEMM: B_ptrs / out_ptrs / wait_flags are per-shard raw device pointers (ints), possibly peer-mapped."""
     nseg = len(seg_rows) - 1
     BP = (c_void_p * nseg)(*[c_void_p(int(x)) for x in (B_ptrs if B_ptrs is not None else [0] * nseg)])
     OP = (c_void_p * nseg)(*[c_void_p(int(x)) for x in out_ptrs]) if out_ptrs is not None else None
     WF = (c_void_p * nseg)(*[c_void_p(int(x) if x else 0) for x in wait_flags]) if wait_flags is not None else None
     SR = (c_int * (nseg + 1))(*[int(r) for r in seg_rows])
-    _check(lib().tfd_gemm_bf16_seg(_p(A), c_longlong(lda), c_int(a_mn), BP, c_longlong(ldb), c_int(b_mn), c_int(M),
-                                   c_int(N), c_int(K), c_int(bn), c_int(splits), c_int(mode), c_float(alpha), _p(out),
-                                   c_longlong(ld_out), _p(bias), _p(relu_mask), c_longlong(ld_mask),
-                                   c_longlong(split_stride), c_int(seg_mode), c_int(nseg), SR, OP, WF,
-                                   c_uint(wait_value), _p(wait_value_ptr), _stream()), "tfd_gemm_bf16_seg")
+    _check(lib().tfd_gemm_seg(c_int(DTYPE_TF32 if tf32 else DTYPE_BF16), _p(A), c_longlong(lda), c_int(a_mn), BP,
+                              c_longlong(ldb), c_int(b_mn), c_int(M), c_int(N), c_int(K), c_int(bn), c_int(splits),
+                              c_int(mode), c_float(alpha), _p(out), c_longlong(ld_out), _p(bias), _p(relu_mask),
+                              c_longlong(ld_mask), c_longlong(split_stride), c_int(seg_mode), c_int(nseg), SR, OP, WF,
+                              c_uint(wait_value), _p(wait_value_ptr), _stream()), "tfd_gemm_seg")
     _count()
 
 
@@ -167,63 +178,85 @@ def random_normal(out, seed: int, stddev: float = 1.0, elem_offset: int = 0) -> 
     _count()
 
 
-def conv1_fwd(x, w, b, pool_out, argmax, B: int) -> None:
-    _check(lib().tfd_conv1_fwd(_p(x), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), _stream()), "tfd_conv1_fwd")
+def _dt(tf32: bool) -> c_int:
+    return c_int(DTYPE_TF32 if tf32 else DTYPE_BF16)
+
+
+def scratch_floats(kind: str, B: int) -> int:
+    """Size (floats) of the reduction scratch of a deterministic-gradient kernel: 'conv1_wgrad' / 'conv2_wgrad' /
+    'pool2_bwd'.  The caller allocates it zeroed once; the kernel owns it from then on."""
+    fn = getattr(lib(), "tfd_%s_scratch_floats" % kind)
+    fn.restype = c_longlong
+    return int(fn(c_int(B)))
+
+
+def conv1_fwd(x, w, b, pool_out, argmax, B: int, tf32: bool = False, gate_flags=None, want_ptr=None) -> None:
+    """gate_flags: LOCAL version words (ints or tensors) every block waits on (>= *want_ptr) before it reads w / b."""
+    n = len(gate_flags) if gate_flags else 0
+    G = (c_void_p * max(1, n))(*[c_void_p(int(f) if isinstance(f, int) else f.data_ptr()) for f in (gate_flags or [])])
+    _check(lib().tfd_conv1_fwd(_dt(tf32), _p(x), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), G, c_int(n),
+                               _p(want_ptr), _stream()), "tfd_conv1_fwd")
     _count()
 
 
-def conv1_fwd_gated(x, w_peer, b_peer, pool_out, argmax, B: int, gate_w, gate_b, want_ptr) -> None:
-    """conv1 block whose filter/bias are read from the owner shards (peer pointers, ints or tensors) once their
-    version flags have reached ``*want_ptr``: the pull of conv1's parameters inside the step's first kernel."""
-    _check(lib().tfd_conv1_fwd_gated(_p(x), _p(w_peer), _p(b_peer), _p(pool_out), _p(argmax), c_int(B), _p(gate_w),
-                                     _p(gate_b), _p(want_ptr), _stream()), "tfd_conv1_fwd_gated")
+def conv1_wgrad(x, dpool, pool_out, argmax, dw, db, scratch, B: int, tf32: bool = False, nsplit: int = 1,
+                split_stride: int = 0) -> None:
+    _check(lib().tfd_conv1_wgrad(_dt(tf32), _p(x), _p(dpool), c_int(nsplit), c_longlong(split_stride), _p(pool_out),
+                                 _p(argmax), _p(dw), _p(db), _p(scratch), c_int(B), _stream()), "tfd_conv1_wgrad")
     _count()
 
 
-def conv1_wgrad(x, dpool, pool_out, argmax, dw, db, B: int) -> None:
-    _check(lib().tfd_conv1_wgrad(_p(x), _p(dpool), _p(pool_out), _p(argmax), _p(dw), _p(db), c_int(B), _stream()),
-           "tfd_conv1_wgrad")
+def conv2_fwd(inp, w, b, pool_out, argmax, B: int, ref: bool = False, tf32: bool = False) -> None:
+    if ref:
+        _check(lib().tfd_conv2_fwd_ref(_p(inp), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), _stream()), "tfd_conv2_fwd_ref")
+    else:
+        _check(lib().tfd_conv2_fwd(_dt(tf32), _p(inp), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), _stream()),
+               "tfd_conv2_fwd")
     _count()
 
 
-def conv2_fwd(inp, w, b, pool_out, argmax, B: int, ref: bool = False) -> None:
-    fn = lib().tfd_conv2_fwd_ref if ref else lib().tfd_conv2_fwd
-    _check(fn(_p(inp), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), _stream()), "tfd_conv2_fwd")
+def conv2_dgrad(dy, w, dx, B: int, ref: bool = False, tf32: bool = False) -> None:
+    """tf32: dx holds TWO partial planes (B*14*14*32 floats apart) that conv1_wgrad adds."""
+    if ref:
+        _check(lib().tfd_conv2_dgrad_ref(_p(dy), _p(w), _p(dx), c_int(B), _stream()), "tfd_conv2_dgrad_ref")
+    else:
+        _check(lib().tfd_conv2_dgrad(_dt(tf32), _p(dy), _p(w), _p(dx), c_int(B), _stream()), "tfd_conv2_dgrad")
     _count()
 
 
-def conv2_dgrad(dy, w, dx, B: int, ref: bool = False) -> None:
-    fn = lib().tfd_conv2_dgrad_ref if ref else lib().tfd_conv2_dgrad
-    _check(fn(_p(dy), _p(w), _p(dx), c_int(B), _stream()), "tfd_conv2_dgrad")
+def conv2_wgrad(inp, dy, dw, scratch, B: int, ref: bool = False, tf32: bool = False) -> None:
+    """dw is WRITTEN (deterministic plane reduction through `scratch`); the validation kernel (ref) accumulates."""
+    if ref:
+        dw.zero_()
+        _check(lib().tfd_conv2_wgrad_ref(_p(inp), _p(dy), _p(dw), c_int(B), _stream()), "tfd_conv2_wgrad_ref")
+    else:
+        _check(lib().tfd_conv2_wgrad(_dt(tf32), _p(inp), _p(dy), _p(dw), _p(scratch), c_int(B), _stream()),
+               "tfd_conv2_wgrad")
     _count()
 
 
-def conv2_wgrad(inp, dy, dw, B: int, ref: bool = False) -> None:
-    fn = lib().tfd_conv2_wgrad_ref if ref else lib().tfd_conv2_wgrad
-    _check(fn(_p(inp), _p(dy), _p(dw), c_int(B), _stream()), "tfd_conv2_wgrad")
+def pool2_bwd(dpool, pool_out, argmax, dy, db, scratch, B: int, nsplit: int = 1, split_stride: int = 0,
+              tf32: bool = False) -> None:
+    _check(lib().tfd_pool2_bwd(_dt(tf32), _p(dpool), c_int(nsplit), c_longlong(split_stride), _p(pool_out), _p(argmax),
+                               _p(dy), _p(db), _p(scratch), c_int(B), _stream()), "tfd_pool2_bwd")
     _count()
 
 
-def pool2_bwd(dpool, pool_out, argmax, dy, db, B: int, nsplit: int = 1, split_stride: int = 0) -> None:
-    _check(lib().tfd_pool2_bwd(_p(dpool), c_int(nsplit), c_longlong(split_stride), _p(pool_out), _p(argmax), _p(dy), _p(db), c_int(B), _stream()),
-           "tfd_pool2_bwd")
-    _count()
-
-
-def head_rows(pre_f32, hid_bf16, hid_bias, out_w, out_b, labels, B: int, H: int, ld_h: int, keep_prob: float,
+def head_rows(pre_f32, hid_in, hid_bias, out_w, out_b, labels, B: int, H: int, ld_h: int, keep_prob: float,
               seed: int, step: int, training: bool, hid_out, dhid, dlogits, loss_row, hit, keep_mask_out=None,
-              step_ptr=None, pre_nsplit: int = 1, pre_split_stride: int = 0) -> None:
-    _check(lib().tfd_head_rows(_p(pre_f32), c_int(pre_nsplit), c_longlong(pre_split_stride), _p(hid_bf16), _p(hid_bias), _p(out_w), _p(out_b), _p(labels), c_int(B),
-                               c_int(H), c_longlong(ld_h), c_float(keep_prob), c_ulonglong(seed), c_ulonglong(step),
-                               _p(step_ptr), c_int(int(training)), _p(hid_out), _p(dhid), _p(dlogits), _p(loss_row), _p(hit),
+              step_ptr=None, pre_nsplit: int = 1, pre_split_stride: int = 0, tf32: bool = False) -> None:
+    _check(lib().tfd_head_rows(_dt(tf32), _p(pre_f32), c_int(pre_nsplit), c_longlong(pre_split_stride), _p(hid_in),
+                               _p(hid_bias), _p(out_w), _p(out_b), _p(labels), c_int(B), c_int(H), c_longlong(ld_h),
+                               c_float(keep_prob), c_ulonglong(seed), c_ulonglong(step), _p(step_ptr),
+                               c_int(int(training)), _p(hid_out), _p(dhid), _p(dlogits), _p(loss_row), _p(hit),
                                _p(keep_mask_out), _stream()), "tfd_head_rows")
     _count()
 
 
 def head_cols(hid, dhid, ld_h: int, dlogits, loss_row, hit, B: int, H: int, d_out_w, d_hid_bias, d_out_b,
-              scalars) -> None:
-    _check(lib().tfd_head_cols(_p(hid), _p(dhid), c_longlong(ld_h), _p(dlogits), _p(loss_row), _p(hit), c_int(B),
-                               c_int(H), _p(d_out_w), _p(d_hid_bias), _p(d_out_b), _p(scalars), _stream()),
+              scalars, tf32: bool = False) -> None:
+    _check(lib().tfd_head_cols(_dt(tf32), _p(hid), _p(dhid), c_longlong(ld_h), _p(dlogits), _p(loss_row), _p(hit),
+                               c_int(B), c_int(H), _p(d_out_w), _p(d_hid_bias), _p(d_out_b), _p(scalars), _stream()),
            "tfd_head_cols")
     _count()
 
@@ -236,10 +269,13 @@ def zero_multi(tensors) -> None:
     _count()
 
 
-def colsum_bf16(x, ld: int, rows: int, cols: int, out) -> None:
-    _check(lib().tfd_colsum_bf16(_p(x), c_longlong(ld), c_int(rows), c_int(cols), _p(out), _stream()),
-           "tfd_colsum_bf16")
+def colsum(x, ld: int, rows: int, cols: int, out, tf32: bool = False) -> None:
+    _check(lib().tfd_colsum(_dt(tf32), _p(x), c_longlong(ld), c_int(rows), c_int(cols), _p(out), _stream()), "tfd_colsum")
     _count()
+
+
+def colsum_bf16(x, ld: int, rows: int, cols: int, out) -> None:
+    colsum(x, ld, rows, cols, out, False)
 
 
 def adam_apply(w, m, v, shadow, slots_dev, num_slots: int, scale: float, n: int, pieces, lr: float, t_counter,

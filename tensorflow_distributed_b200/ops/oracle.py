@@ -45,33 +45,52 @@ def accuracy(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
     return (logits.argmax(dim=1) == labels.argmax(dim=1)).float().mean()
 
 
+def quantizer(precision: Optional[str]):
+    """Operand quantisation of a tensor-core precision arm as a straight-through function (identity gradient):
+    'bf16' rounds to bfloat16, 'tf32' drops the low 13 mantissa bits (what tcgen05 kind::tf32 reads of an fp32 word),
+    None / 'fp32' is the identity.  Used to derive test tolerances: oracle(quantised operands) - oracle(fp32) is the
+    error a precision arm is ENTITLED to; what a kernel adds on top of it is accumulation order only."""
+    if precision in (None, "fp32"):
+        return lambda t: t
+    if precision == "bf16":
+        rnd = lambda t: t.to(torch.bfloat16).to(t.dtype)  # noqa: E731
+    elif precision == "tf32":
+        rnd = lambda t: (t.contiguous().view(torch.int32) & ~0x1fff).view(torch.float32)  # noqa: E731
+    else:
+        raise ValueError("unknown precision %r" % precision)
+    return lambda t: t + (rnd(t.detach()) - t.detach())
+
+
 def cnn_forward(x: torch.Tensor, p: Dict[str, torch.Tensor], keep_prob: float = 1.0,
-                keep_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """conv_net (m:104-128).  ``x``: [B,784]; returns logits [B,10]."""
+                keep_mask: Optional[torch.Tensor] = None, q=None) -> torch.Tensor:
+    """conv_net (m:104-128).  ``x``: [B,784]; returns logits [B,10].  ``q``: operand quantiser of the tensor-core
+    layers (conv2, fc1); conv1 and the 10-wide output layer run on CUDA cores in fp32 in every arm."""
+    q = q or (lambda t: t)
     h = x.reshape(-1, 28, 28, 1)
     h = torch.relu(conv2d_same_nhwc(h, p["weights/wc1"]) + p["biases/bc1"])
     h = maxpool2x2_nhwc(h)
-    h = torch.relu(conv2d_same_nhwc(h, p["weights/wc2"]) + p["biases/bc2"])
+    h = torch.relu(conv2d_same_nhwc(q(h), q(p["weights/wc2"])) + p["biases/bc2"])
     h = maxpool2x2_nhwc(h)
     h = h.reshape(-1, p["weights/wd1"].shape[0])          # NHWC flatten order (m:120)
-    h = torch.relu(h @ p["weights/wd1"] + p["biases/bd1"])
+    h = torch.relu(q(h) @ q(p["weights/wd1"]) + p["biases/bd1"])
     h = dropout_with_mask(h, keep_mask, keep_prob)
     return h @ p["weights/out"] + p["biases/out"]
 
 
 def mlp_forward(x: torch.Tensor, p: Dict[str, torch.Tensor], keep_prob: float = 1.0,
-                keep_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+                keep_mask: Optional[torch.Tensor] = None, q=None) -> torch.Tensor:
     """784 -> hidden x L (ReLU) -> 10.  Dropout is not part of the MLP."""
+    q = q or (lambda t: t)
     h = x
     i = 1
     while "weights/h%d" % i in p:
-        h = torch.relu(h @ p["weights/h%d" % i] + p["biases/b%d" % i])
+        h = torch.relu(q(h) @ q(p["weights/h%d" % i]) + p["biases/b%d" % i])
         i += 1
     return h @ p["weights/out"] + p["biases/out"]
 
 
-def forward(kind: str, x, p, keep_prob: float = 1.0, keep_mask=None):
-    return (cnn_forward if kind == "cnn" else mlp_forward)(x, p, keep_prob, keep_mask)
+def forward(kind: str, x, p, keep_prob: float = 1.0, keep_mask=None, q=None):
+    return (cnn_forward if kind == "cnn" else mlp_forward)(x, p, keep_prob, keep_mask, q)
 
 
 def dropout_width(kind: str, p: Dict[str, torch.Tensor]) -> int:
@@ -79,11 +98,12 @@ def dropout_width(kind: str, p: Dict[str, torch.Tensor]) -> int:
 
 
 def loss_and_grads(kind: str, x: torch.Tensor, y: torch.Tensor, p: Dict[str, torch.Tensor],
-                   keep_prob: float = 1.0, keep_mask: Optional[torch.Tensor] = None
+                   keep_prob: float = 1.0, keep_mask: Optional[torch.Tensor] = None, precision: Optional[str] = None
                    ) -> Tuple[torch.Tensor, Dict[str, torch.Tensor], torch.Tensor]:
-    """Loss, d(loss)/d(param) for every parameter, and logits (autograd, fp32)."""
+    """Loss, d(loss)/d(param) for every parameter, and logits (autograd, fp32; ``precision`` quantises the operands
+    of the tensor-core layers the way that arm's kernels see them)."""
     leaves = {k: v.detach().clone().requires_grad_(True) for k, v in p.items()}
-    logits = forward(kind, x, leaves, keep_prob, keep_mask)
+    logits = forward(kind, x, leaves, keep_prob, keep_mask, quantizer(precision))
     loss = softmax_xent_mean(logits, y)
     grads = torch.autograd.grad(loss, [leaves[k] for k in leaves])
     return loss.detach(), {k: g for k, g in zip(leaves, grads)}, logits.detach()

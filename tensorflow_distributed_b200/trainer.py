@@ -37,12 +37,13 @@ def run_single(*, model: str = "cnn", learning_rate: float = 0.01, training_iter
                nt: int = 50, val_batch: int = 100, data_dir: str = "MNIST_data/", synthetic: Optional[bool] = None,
                backend: str = "auto", seed: int = 0, hidden_units: int = 100, mlp_layers: int = 1,
                train_dir: str = "", init_stddev: float = 1.0, trace_file: str = "", trace_start: int = 2,
-               trace_steps: int = 3, log: Callable[[str], None] = print) -> dict:
+               trace_steps: int = 3, precision: Optional[str] = None, log: Callable[[str], None] = print) -> dict:
     mnist = data_mod.read_data_sets(data_dir, True, synthetic, seed)
     tracer = StepTracer(trace_file, trace_start, trace_steps, log)
     spec = make_spec(model, hidden_units, mlp_layers)
     start_time = time.time()  # the reference starts its timer before session creation (single:102)
-    eng = make_engine(spec, backend, learning_rate=learning_rate, seed=seed, init_stddev=init_stddev)
+    eng = make_engine(spec, backend, learning_rate=learning_rate, seed=seed, init_stddev=init_stddev,
+                      precision=precision)
     sv = Supervisor(True, spec, train_dir, log=log) if train_dir else None
     if sv is not None:
         def _restore(blob):
@@ -155,7 +156,7 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
         from .engine_native import CTRL_T, NativeEngine
         dev = cl.torch_device_of(device)
         eng = NativeEngine(spec, flags.learning_rate, flags.seed + 31 * flags.task_index, flags.init_stddev,
-                           device=dev if dev != "cpu" else "cuda:0")
+                           device=dev if dev != "cpu" else "cuda:0", precision=flags.precision)
     else:
         eng = OracleEngine(spec, flags.learning_rate, flags.seed, flags.init_stddev, cl.torch_device_of(device)
                            if torch.cuda.is_available() else "cpu")

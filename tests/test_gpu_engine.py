@@ -28,27 +28,45 @@ def _engine(spec, **kw):
     return NativeEngine(spec, **kw)
 
 
-@pytest.mark.parametrize("conv2_ref", [True, False])
+def _frob(a, b):
+    return (a.float() - b.float()).norm().item() / (b.float().norm().item() + 1e-20)
+
+
+ARMS = [("tf32", False), ("bf16", False), ("bf16", True)]  # (precision, conv2 on the CUDA-core validation kernels)
+
+
+def _entitled(g_fp32, g_quant, k):
+    """Error budget of a precision arm for gradient k: what quantising the tensor-core operands alone does to the fp32
+    oracle (oracle.quantizer), times a factor for the second rounding the kernels add (dy operands of the backward
+    GEMMs, bf16-stored activations), plus accumulation-order noise."""
+    return 3.0 * _frob(g_quant[k], g_fp32[k]) + 2e-3
+
+
+@pytest.mark.parametrize("precision,conv2_ref", ARMS)
 @pytest.mark.parametrize("keep_prob", [1.0, 0.75])
-def test_cnn_step_gradients_match_oracle(conv2_ref, keep_prob):
+def test_cnn_step_gradients_match_oracle(precision, conv2_ref, keep_prob):
+    """Whole-step gradients against the PURE fp32 oracle (its weights are not rounded to what the tensor cores see):
+    the tolerance is what the arm's operand quantisation is entitled to, measured on the oracle itself."""
     spec = cnn_spec()
-    eng = _engine(spec, init_stddev=0.05, seed=1, conv2_ref=conv2_ref, use_graphs=False)
+    eng = _engine(spec, init_stddev=0.05, seed=1, conv2_ref=conv2_ref, use_graphs=False, precision=precision)
     x, y = _batch(128, 1)
     loss, grads, mask = eng.loss_and_grads(x, y, keep_prob)
     p = eng.get_params()
-    # the oracle sees the weights the tensor cores saw
-    for k in ("weights/wc2", "weights/wd1"):
-        p[k] = p[k].to(torch.bfloat16).float()
-    oloss, ograds, _ = oracle.loss_and_grads("cnn", x, y, p, keep_prob, None if mask is None else mask.bool().cpu())
-    assert abs(loss - oloss.item()) < 3e-2 * max(1.0, abs(oloss.item()))
-    for k in ograds:
-        assert _rel(grads[k], ograds[k]) < 0.1, k
+    km = None if mask is None else mask.bool().cpu()
+    oloss, g32, _ = oracle.loss_and_grads("cnn", x, y, p, keep_prob, km)
+    _, gq, _ = oracle.loss_and_grads("cnn", x, y, p, keep_prob, km, precision=precision)
+    assert abs(loss - oloss.item()) < (2e-3 if precision == "tf32" else 2e-2) * max(1.0, abs(oloss.item()))
+    for k in g32:
+        assert _frob(grads[k], g32[k]) < _entitled(g32, gq, k), (k, _frob(grads[k], g32[k]), _frob(gq[k], g32[k]))
+        # no single element is far off either (max-abs error relative to the largest gradient of the tensor)
+        assert _rel(grads[k], g32[k]) < 2.0 * _entitled(g32, gq, k) + 1e-2, (k, _rel(grads[k], g32[k]))
 
 
-def test_cnn_training_trajectory_tracks_oracle_and_learns():
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+def test_cnn_training_trajectory_tracks_oracle_and_learns(precision):
     from tensorflow_distributed_b200 import data
     spec = cnn_spec()
-    eng = _engine(spec, init_stddev=0.05, seed=2)
+    eng = _engine(spec, init_stddev=0.05, seed=2, precision=precision)
     ds = data.read_data_sets("", synthetic=True, seed=0)
     first = last = None
     for i in range(30):
@@ -63,9 +81,47 @@ def test_cnn_training_trajectory_tracks_oracle_and_learns():
     assert eng.eval_loss(vx, vy) >= 0.0
 
 
-def test_adam_step_matches_tf_adam_on_engine_grads():
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+def test_twenty_steps_at_the_reference_init_against_the_fp32_oracle(precision):
+    """The regime the reference and bench.py actually run in: every parameter ~ N(0, 1) (m:186-195), so fc1
+    activations are in the hundreds and the first losses in the thousands.  20 training steps (dropout off so both
+    sides see the same function) from the same weights and batches: the loss trajectory and the final weights of each
+    precision arm against the fp32 CPU oracle.  Bounds = a multiple of what the arm's operand quantisation does to the
+    ORACLE's own trajectory (measured here, not guessed)."""
     spec = cnn_spec()
-    eng = _engine(spec, init_stddev=0.05, seed=3, use_graphs=False)
+    eng = _engine(spec, init_stddev=1.0, seed=11, precision=precision)
+    p0 = eng.get_params()
+    batches = [_batch(128, 100 + i) for i in range(20)]
+
+    def run_oracle(prec):
+        params = {k: v.clone() for k, v in p0.items()}
+        adam, losses = oracle.TFAdam(0.01), []
+        for x, y in batches:
+            l, g, _ = oracle.loss_and_grads("cnn", x, y, params, precision=prec)
+            adam.apply(params, g)
+            losses.append(float(l))
+        return losses, params
+
+    l32, w32 = run_oracle(None)
+    lq, wq = run_oracle(precision)
+    le = [eng.train_step(x, y, 1.0, fetch_loss=True) for x, y in batches]
+    we = eng.get_params()
+    rel_loss = max(abs(a - b) / max(abs(b), 1.0) for a, b in zip(le, l32))
+    rel_loss_q = max(abs(a - b) / max(abs(b), 1.0) for a, b in zip(lq, l32))
+    upd = lambda w, k: w[k] - p0[k]  # noqa: E731  (20 Adam steps move a weight by at most 0.2: compare the UPDATE)
+    print("precision %s: max rel loss error %.3e (oracle-with-quantised-operands: %.3e)" % (precision, rel_loss, rel_loss_q))
+    assert le[0] > 100.0 and all(torch.isfinite(torch.tensor(le)))
+    assert rel_loss < 3.0 * rel_loss_q + (5e-3 if precision == "tf32" else 2e-2)
+    for k in w32:
+        e, eq = _frob(upd(we, k), upd(w32, k)), _frob(upd(wq, k), upd(w32, k))
+        print("  %-12s update error vs fp32 oracle %.3e (entitled %.3e)" % (k, e, eq))
+        assert e < 3.0 * eq + 5e-2, (k, e, eq)
+
+
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+def test_adam_step_matches_tf_adam_on_engine_grads(precision):
+    spec = cnn_spec()
+    eng = _engine(spec, init_stddev=0.05, seed=3, use_graphs=False, precision=precision)
     x, y = _batch(128, 3)
     p0 = eng.get_params()
     eng.train_step(x, y, 1.0)
@@ -76,40 +132,43 @@ def test_adam_step_matches_tf_adam_on_engine_grads():
     adam.apply(ref, g)
     for k in ref:
         assert torch.allclose(p1[k], ref[k], atol=2e-5, rtol=1e-4), k
-    # the published bf16 shadow is the rounded master copy
-    assert torch.equal(eng.S("weights/wd1").cpu(), p1["weights/wd1"].to(torch.bfloat16))
+    if precision == "bf16":  # the published bf16 shadow is the rounded master copy
+        assert torch.equal(eng.S("weights/wd1").cpu(), p1["weights/wd1"].to(torch.bfloat16))
+    else:                    # tf32: no shadow at all, the tensor cores read the master
+        assert eng.S("weights/wd1").data_ptr() == eng.P("weights/wd1").data_ptr()
 
 
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
 @pytest.mark.parametrize("hidden,layers", [(100, 1), (256, 3)])
-def test_mlp_step_gradients_match_oracle(hidden, layers):
+def test_mlp_step_gradients_match_oracle(hidden, layers, precision):
     spec = mlp_spec(hidden, layers)
-    eng = _engine(spec, init_stddev=0.05, seed=4, use_graphs=False)
+    eng = _engine(spec, init_stddev=0.05, seed=4, use_graphs=False, precision=precision)
     x, y = _batch(128, 4)
     loss, grads, _ = eng.loss_and_grads(x, y, 1.0)
     p = eng.get_params()
-    for k in p:
-        if k.startswith("weights/h"):
-            p[k] = p[k].to(torch.bfloat16).float()
-    oloss, ograds, _ = oracle.loss_and_grads("mlp", x.to(torch.bfloat16).float(), y, p)
-    assert abs(loss - oloss.item()) < 3e-2 * max(1.0, abs(oloss.item()))
-    for k in ograds:
-        assert _rel(grads[k], ograds[k]) < 0.1, k
+    oloss, g32, _ = oracle.loss_and_grads("mlp", x, y, p)
+    _, gq, _ = oracle.loss_and_grads("mlp", x, y, p, precision=precision)
+    assert abs(loss - oloss.item()) < (2e-3 if precision == "tf32" else 2e-2) * max(1.0, abs(oloss.item()))
+    for k in g32:
+        assert _frob(grads[k], g32[k]) < _entitled(g32, gq, k), (k, _frob(grads[k], g32[k]), _frob(gq[k], g32[k]))
 
 
-def test_graph_replay_equals_eager():
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+def test_graph_replay_equals_eager_bit_for_bit(precision):
+    """Every reduction of the step has a fixed order (split-K planes, per-block partials summed by the last block,
+    the conv2 wgrad plane reduction), so replaying the captured graph and launching the kernels one by one give the
+    same bits."""
     spec = cnn_spec()
     x, y = _batch(128, 5)
     outs = []
     for graphs in (False, True):
-        eng = _engine(spec, init_stddev=0.05, seed=5, use_graphs=graphs)
-        for _ in range(4):
+        eng = _engine(spec, init_stddev=0.05, seed=5, use_graphs=graphs, precision=precision)
+        for _ in range(5):
             eng.train_step(x, y, 0.75)
-        outs.append(eng.get_params())
-    for k in outs[0]:
-        # atomics make the split-K sums order-dependent: equal up to fp32 reassociation noise
-        # (Adam's m/sqrt(v) turns a sign flip of a near-zero gradient into a full-size update: compare in the mean)
-        d = (outs[0][k] - outs[1][k]).abs()
-        assert d.mean().item() < 1e-4 and (d > 2e-2).float().mean().item() < 1e-3, k
+        outs.append((eng.get_params(), eng.get_adam_state()))
+    for k in outs[0][0]:
+        assert torch.equal(outs[0][0][k], outs[1][0][k]), k
+        assert torch.equal(outs[0][1]["m"][k], outs[1][1]["m"][k]), k
 
 
 def test_run_single_on_gpu_prints_reference_lines():
@@ -121,33 +180,19 @@ def test_run_single_on_gpu_prints_reference_lines():
     assert out["mean_accuracy"] > 0.5
 
 
-def test_early_adam_launch_matches_single_launch():
-    """Adam split into an early launch for wd1 and a finalising launch for the rest gives the same update."""
-    spec = cnn_spec()
-    x, y = _batch(128, 6)
-    outs = []
-    for early in (False, True):
-        eng = _engine(spec, init_stddev=0.05, seed=6, use_graphs=False, early_adam=early)
-        eng.train_step(x, y, 1.0)
-        eng.train_step(x, y, 1.0)
-        outs.append((eng.get_params(), eng.global_step, eng.get_adam_state()["t"]))
-    assert outs[0][1] == outs[1][1] == 2 and outs[0][2] == outs[1][2] == 2
-    for k in outs[0][0]:
-        d = (outs[0][0][k] - outs[1][0][k]).abs()
-        assert d.mean().item() < 1e-4 and (d > 2e-2).float().mean().item() < 1e-3, k
-
-
-def test_checkpoint_resume_gives_the_same_next_step(tmp_path):
-    """save -> (process would die here) -> restore into a fresh engine -> identical next step."""
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+def test_checkpoint_resume_gives_the_same_next_step(tmp_path, precision):
+    """save -> (process would die here) -> restore into a fresh engine -> identical next step (bit for
+    bit: the reductions are deterministic)."""
     from tensorflow_distributed_b200 import checkpoint
     spec = cnn_spec()
     x, y = _batch(128, 7)
-    a = _engine(spec, init_stddev=0.05, seed=7, use_graphs=False)
+    a = _engine(spec, init_stddev=0.05, seed=7, use_graphs=False, precision=precision)
     for _ in range(3):
         a.train_step(x, y, 1.0)
     path = checkpoint.save(str(tmp_path), spec, a.global_step, a.get_params(), a.get_adam_state())
     blob = checkpoint.load(checkpoint.latest_checkpoint(str(tmp_path)), spec)
-    b = _engine(spec, init_stddev=0.05, seed=99, use_graphs=False)  # different init: everything must come from the file
+    b = _engine(spec, init_stddev=0.05, seed=99, use_graphs=False, precision=precision)  # everything comes from the file
     b.set_params(blob["variables"])
     b.set_adam_state(blob["adam"])
     b.global_step = blob["global_step"]
@@ -156,13 +201,10 @@ def test_checkpoint_resume_gives_the_same_next_step(tmp_path):
     b.train_step(x, y, 1.0)
     pa, pb = a.get_params(), b.get_params()
     for k in pa:
-        d = (pa[k] - pb[k]).abs()
-        assert d.mean().item() < 1e-5 and (d > 2e-2).float().mean().item() < 1e-3, k
+        assert torch.equal(pa[k], pb[k]), k
     assert a.global_step == b.global_step == 4
 
 
-@pytest.mark.skipif(os.environ.get("TFD_TEST_PREDICT", "0") != "1",
-                    reason="predict_proba on the native engine: opt in with TFD_TEST_PREDICT=1 (added after the GPU budget ended)")
 def test_native_predict_proba_matches_the_oracle():
     import numpy as np
     spec = cnn_spec()

@@ -120,40 +120,111 @@ def test_gemm_epilogues_bias_relu_and_relumask_and_padded_ld(nat):
 
 
 # ------------------------------------------------------------------------------------------------
+# tf32 arm: fp32 operands in memory, tcgen05 kind::tf32.  Reference = fp32 matmul of the tf32-truncated operands
+# (the tensor core drops the low 13 mantissa bits), so what is left is accumulation order.
+def tf32_trunc(x):
+    return (x.contiguous().view(torch.int32) & ~0x1fff).view(torch.float32)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("M,N,K,bn,splits", [(128, 1024, 3136, 64, 8), (100, 72, 200, 64, 1), (256, 512, 128, 256, 1),
+                                             (3136, 1024, 128, 128, 1)])
+def test_gemm_tf32_all_major_combinations(nat, a_mn, b_mn, M, N, K, bn, splits):
+    if a_mn == 1 and M % 4:
+        M = (M + 3) // 4 * 4  # leading dimension of an MN-major fp32 operand must keep 16-byte rows
+    torch.manual_seed(7)
+    A = torch.randn(M, K, device=DEV)
+    Bm = torch.randn(K, N, device=DEV)
+    ref = tf32_trunc(A) @ tf32_trunc(Bm)
+    ref64 = (tf32_trunc(A).double() @ tf32_trunc(Bm).double()).float()
+    As = A.t().contiguous() if a_mn else A                # a_mn: stored [K, M]
+    Bs = Bm if b_mn else Bm.t().contiguous()              # b_mn=0: stored [N, K]
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        out = torch.full((max(1, splits), M, N), 7.0, device=DEV)
+        nat.gemm_bf16(As, a_mn, Bs, b_mn, M, N, K, out, mode=nat.EPI_STORE_F32, bn=bn, splits=splits,
+                      split_stride=M * N, ld_out=N, tf32=True)
+        torch.cuda.synchronize()
+        got = out.sum(0)
+        assert rel_err(got, ref64) < 2e-5, (a_mn, b_mn)
+        # and it is tf32, not bf16 and not fp32: against the untruncated fp32 product the error is ~1e-3, not ~1e-2
+        full = (A.double() @ Bm.double()).float()
+        assert rel_err(got, full) < 4e-3
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def test_gemm_tf32_epilogues_bias_relu_and_relumask_f32(nat):
+    torch.manual_seed(8)
+    M, N, K, ld = 128, 100, 784, 104
+    A = torch.randn(M, K, device=DEV)
+    W = torch.zeros(K, ld, device=DEV)
+    W[:, :N] = torch.randn(K, N, device=DEV)
+    bias = torch.randn(N, device=DEV)
+    ref = torch.relu((tf32_trunc(A).double() @ tf32_trunc(W[:, :N]).double()).float() + bias)
+    out = torch.full((M, ld), 7.0, device=DEV)
+    nat.gemm_bf16(A, 0, W, 1, M, N, K, out, mode=nat.EPI_BIAS_RELU_F32, bn=64, bias=bias, tf32=True)
+    torch.cuda.synchronize()
+    assert rel_err(out[:, :N], ref) < 2e-5
+    assert torch.all(out[:, N:] == 7.0)
+    dy = torch.zeros(M, ld, device=DEV)
+    dy[:, :N] = torch.randn(M, N, device=DEV)
+    act = torch.randn(M, K, device=DEV)
+    ref2 = (tf32_trunc(dy[:, :N]).double() @ tf32_trunc(W[:, :N]).double().t()).float() * (act > 0)
+    out2 = torch.zeros(M, K, device=DEV)
+    nat.gemm_bf16(dy, 0, W, 0, M, K, N, out2, mode=nat.EPI_RELUMASK_F32, bn=64, relu_mask=act, tf32=True)
+    torch.cuda.synchronize()
+    assert rel_err(out2, ref2) < 2e-5
+
+
+# ------------------------------------------------------------------------------------------------
 def _conv1_ref(x, w, b):
     y = torch.relu(oracle.conv2d_same_nhwc(x.reshape(-1, 28, 28, 1), w) + b)
     return oracle.maxpool2x2_nhwc(y), y
 
 
+def _scratch(nat, kind, B):
+    return torch.zeros(nat.scratch_floats(kind, B), device=DEV)
+
+
+@pytest.mark.parametrize("tf32", [False, True])
 @pytest.mark.parametrize("B", [128, 5])
-def test_conv1_fwd_and_wgrad(nat, B):
+def test_conv1_fwd_and_wgrad(nat, B, tf32):
     torch.manual_seed(5)
+    adt = torch.float32 if tf32 else torch.bfloat16
     x = torch.rand(B, 784, device=DEV)
     w = torch.randn(5, 5, 1, 32, device=DEV)
     b = torch.randn(32, device=DEV)
-    pool = torch.empty(B, 14, 14, 32, device=DEV, dtype=torch.bfloat16)
+    pool = torch.empty(B, 14, 14, 32, device=DEV, dtype=adt)
     am = torch.empty(B, 14, 14, 32, device=DEV, dtype=torch.uint8)
-    nat.conv1_fwd(x, w, b, pool, am, B)
+    nat.conv1_fwd(x, w, b, pool, am, B, tf32=tf32)
     torch.cuda.synchronize()
     ref, pre = _conv1_ref(x, w, b)
-    assert rel_err(pool, ref) < 1e-2
+    assert rel_err(pool, ref) < (1e-5 if tf32 else 1e-2)
     assert int(am.max()) <= 3
-    # backward: oracle gradient of sum(pool * dpool) w.r.t. w and b
+    # backward: oracle gradient of sum(pool * dpool) w.r.t. w and b; dpool arrives as two partial planes
     dpool = torch.randn(B, 14, 14, 32, device=DEV)
+    planes = torch.stack([0.25 * dpool, 0.75 * dpool])
     wl, bl = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
     r2, _ = _conv1_ref(x, wl, bl)
     (r2 * dpool).sum().backward()
-    dw = torch.zeros(25, 32, device=DEV)
-    db = torch.zeros(32, device=DEV)
-    nat.conv1_wgrad(x, dpool, pool, am, dw, db, B)
-    torch.cuda.synchronize()
-    assert rel_err(dw, wl.grad.reshape(25, 32)) < 2e-3
-    assert rel_err(db, bl.grad) < 2e-3
+    scratch = _scratch(nat, "conv1_wgrad", B)
+    res = []
+    for _ in range(2):  # written, not accumulated; a second launch on the same scratch gives the same bits
+        dw = torch.full((25, 32), 7.0, device=DEV)
+        db = torch.full((32,), 7.0, device=DEV)
+        nat.conv1_wgrad(x, planes, pool, am, dw, db, scratch, B, tf32=tf32, nsplit=2, split_stride=dpool.numel())
+        torch.cuda.synchronize()
+        res.append((dw, db))
+    assert rel_err(res[0][0], wl.grad.reshape(25, 32)) < 2e-3
+    assert rel_err(res[0][1], bl.grad) < 2e-3
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
 
 
-def test_conv1_fwd_gated_equals_plain_once_the_version_is_there(nat):
-    """The gated form (parameters read from the owner shard inside the kernel after its version flag has reached
-    the worker's step counter) computes exactly what the plain form computes; flags already satisfied here."""
+def test_conv1_fwd_gated_on_local_flags_equals_plain(nat):
+    """The gated form (every block first waits until the shards' version words in LOCAL memory have reached the
+    worker's step counter) computes exactly what the plain form computes; the flags are already satisfied here."""
     B = 37
     torch.manual_seed(8)
     x = torch.rand(B, 784, device=DEV)
@@ -164,9 +235,9 @@ def test_conv1_fwd_gated_equals_plain_once_the_version_is_there(nat):
         pool = torch.zeros(B, 14, 14, 32, device=DEV, dtype=torch.bfloat16)
         am = torch.zeros(B, 14, 14, 32, device=DEV, dtype=torch.uint8)
         if gated:
-            flags = torch.tensor([7, 9], dtype=torch.int32, device=DEV)  # versions of the w shard and the b shard
+            flags = torch.tensor([7, 9, 8], dtype=torch.int32, device=DEV)  # versions of three shards
             want = torch.tensor([7], dtype=torch.int32, device=DEV)
-            nat.conv1_fwd_gated(x, w, b, pool, am, B, flags[0:], flags[1:], want)
+            nat.conv1_fwd(x, w, b, pool, am, B, gate_flags=[flags[0:], flags[1:], flags[2:]], want_ptr=want)
         else:
             nat.conv1_fwd(x, w, b, pool, am, B)
         torch.cuda.synchronize()
@@ -174,103 +245,128 @@ def test_conv1_fwd_gated_equals_plain_once_the_version_is_there(nat):
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
 
 
-def _conv2_inputs(B, seed):
+def _conv2_inputs(B, seed, tf32=False):
     torch.manual_seed(seed)
-    inp = bf(torch.rand(B, 14, 14, 32, device=DEV))
-    w = bf(torch.randn(5, 5, 32, 64, device=DEV) * 0.1)
+    q = tf32_trunc if tf32 else (lambda t: bf(t))
+    inp = q(torch.rand(B, 14, 14, 32, device=DEV))
+    w = q(torch.randn(5, 5, 32, 64, device=DEV) * 0.1)
     b = torch.randn(64, device=DEV) * 0.1
     return inp, w, b
 
 
-@pytest.mark.parametrize("ref_kernel", [True, False])
-@pytest.mark.parametrize("B", [128, 6])
-def test_conv2_fwd(nat, B, ref_kernel):
-    inp, w, b = _conv2_inputs(B, 6)
-    pool = torch.zeros(B, 7, 7, 64, device=DEV, dtype=torch.bfloat16)
+CONV2_ARMS = [("bf16", True), ("bf16", False), ("tf32", False)]  # (precision, CUDA-core validation kernel)
+
+
+@pytest.mark.parametrize("arm,ref_kernel", CONV2_ARMS)
+@pytest.mark.parametrize("B", [128, 6, 75])
+def test_conv2_fwd(nat, B, arm, ref_kernel):
+    tf32 = arm == "tf32"
+    inp, w, b = _conv2_inputs(B, 6, tf32)
+    pool = torch.zeros(B, 7, 7, 64, device=DEV, dtype=torch.float32 if tf32 else torch.bfloat16)
     am = torch.zeros(B, 7, 7, 64, device=DEV, dtype=torch.uint8)
-    nat.conv2_fwd(inp, w.reshape(800, 64), b, pool, am, B, ref=ref_kernel)
+    nat.conv2_fwd(inp, w.reshape(800, 64), b, pool, am, B, ref=ref_kernel, tf32=tf32)
     torch.cuda.synchronize()
-    pre = torch.relu(oracle.conv2d_same_nhwc(inp.float(), w.float()) + b)
+    pre = torch.relu(oracle.conv2d_same_nhwc(inp.double(), w.double()).float() + b)
     ref = oracle.maxpool2x2_nhwc(pre)
-    assert rel_err(pool, ref) < 1e-2
+    assert rel_err(pool, ref) < (2e-5 if tf32 else 1e-2)
     # argmax points at a maximal element of its window
     win = pre.reshape(B, 7, 2, 7, 2, 64).permute(0, 1, 3, 5, 2, 4).reshape(B, 7, 7, 64, 4)
     picked = torch.gather(win, 4, am.long().unsqueeze(-1)).squeeze(-1)
-    assert (picked - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
+    assert (picked - ref).abs().max().item() <= (1e-4 if tf32 else 2e-2) * ref.abs().max().item()
 
 
-@pytest.mark.parametrize("ref_kernel", [True, False])
-@pytest.mark.parametrize("B", [128, 6])
-def test_conv2_dgrad(nat, B, ref_kernel):
-    inp, w, b = _conv2_inputs(B, 7)
-    dy = bf(torch.randn(B, 14, 14, 64, device=DEV))
-    xin = inp.float().requires_grad_(True)
-    (oracle.conv2d_same_nhwc(xin, w.float()) * dy.float()).sum().backward()
-    dx = torch.zeros(B, 14, 14, 32, device=DEV)
-    nat.conv2_dgrad(dy, w.reshape(800, 64), dx, B, ref=ref_kernel)
+@pytest.mark.parametrize("arm,ref_kernel", CONV2_ARMS)
+@pytest.mark.parametrize("B", [128, 6, 75])
+def test_conv2_dgrad(nat, B, arm, ref_kernel):
+    tf32 = arm == "tf32"
+    inp, w, b = _conv2_inputs(B, 7, tf32)
+    dy = torch.randn(B, 14, 14, 64, device=DEV)
+    dy = tf32_trunc(dy) if tf32 else bf(dy)
+    xin = inp.double().requires_grad_(True)
+    (oracle.conv2d_same_nhwc(xin, w.double()) * dy.double()).sum().backward()
+    nplanes = 2 if tf32 else 1
+    dx = torch.full((nplanes, B, 14, 14, 32), 7.0, device=DEV)
+    nat.conv2_dgrad(dy, w.reshape(800, 64), dx, B, ref=ref_kernel, tf32=tf32)
     torch.cuda.synchronize()
-    assert rel_err(dx, xin.grad) < 2e-3
+    assert rel_err(dx.sum(0), xin.grad.float()) < (2e-5 if tf32 else 2e-3)
 
 
-@pytest.mark.parametrize("ref_kernel", [True, False])
-@pytest.mark.parametrize("B", [128, 6])
-def test_conv2_wgrad(nat, B, ref_kernel):
-    inp, w, b = _conv2_inputs(B, 8)
-    dy = bf(torch.randn(B, 14, 14, 64, device=DEV))
-    wl = w.float().requires_grad_(True)
-    (oracle.conv2d_same_nhwc(inp.float(), wl) * dy.float()).sum().backward()
-    dw = torch.zeros(800, 64, device=DEV)
-    nat.conv2_wgrad(inp, dy, dw, B, ref=ref_kernel)
-    torch.cuda.synchronize()
-    assert rel_err(dw, wl.grad.reshape(800, 64)) < 2e-3
+@pytest.mark.parametrize("arm,ref_kernel", CONV2_ARMS)
+@pytest.mark.parametrize("B", [128, 6, 75])
+def test_conv2_wgrad(nat, B, arm, ref_kernel):
+    tf32 = arm == "tf32"
+    inp, w, b = _conv2_inputs(B, 8, tf32)
+    dy = torch.randn(B, 14, 14, 64, device=DEV)
+    dy = tf32_trunc(dy) if tf32 else bf(dy)
+    wl = w.double().requires_grad_(True)
+    (oracle.conv2d_same_nhwc(inp.double(), wl) * dy.double()).sum().backward()
+    scratch = _scratch(nat, "conv2_wgrad", B)
+    res = []
+    for _ in range(2):  # written (not accumulated) in a fixed order: two launches on one scratch agree bit for bit
+        dw = torch.full((800, 64), 7.0, device=DEV)
+        nat.conv2_wgrad(inp, dy, dw, scratch, B, ref=ref_kernel, tf32=tf32)
+        torch.cuda.synchronize()
+        res.append(dw)
+    assert rel_err(res[0], wl.grad.float().reshape(800, 64)) < (2e-5 if tf32 else 2e-3)
+    if not ref_kernel:
+        assert torch.equal(res[0], res[1])
 
 
-def test_pool2_bwd(nat):
+@pytest.mark.parametrize("tf32", [False, True])
+def test_pool2_bwd(nat, tf32):
     torch.manual_seed(9)
     B = 16
+    adt = torch.float32 if tf32 else torch.bfloat16
     pre = torch.randn(B, 14, 14, 64, device=DEV)
     act = torch.relu(pre).requires_grad_(True)
     pooled = oracle.maxpool2x2_nhwc(act)
     dpool = torch.randn(B, 7, 7, 64, device=DEV)
     win = act.detach().reshape(B, 7, 2, 7, 2, 64).permute(0, 1, 3, 5, 2, 4).reshape(B, 7, 7, 64, 4)
     am = win.argmax(dim=4).to(torch.uint8)
-    pool_bf = bf(pooled.detach())
-    dy = torch.empty(B, 14, 14, 64, device=DEV, dtype=torch.bfloat16)
-    db = torch.zeros(64, device=DEV)
+    pool_bf = pooled.detach().to(adt)
+    dy = torch.empty(B, 14, 14, 64, device=DEV, dtype=adt)
+    db = torch.full((64,), 7.0, device=DEV)
     parts = torch.stack([0.5 * dpool, 0.25 * dpool, 0.25 * dpool])
-    nat.pool2_bwd(parts, pool_bf, am, dy, db, B, nsplit=3, split_stride=dpool.numel())
+    scratch = _scratch(nat, "pool2_bwd", B)
+    nat.pool2_bwd(parts, pool_bf, am, dy, db, scratch, B, nsplit=3, split_stride=dpool.numel(), tf32=tf32)
     torch.cuda.synchronize()
+    db1 = db.clone()
+    nat.pool2_bwd(parts, pool_bf, am, dy, db, scratch, B, nsplit=3, split_stride=dpool.numel(), tf32=tf32)
+    torch.cuda.synchronize()
+    assert torch.equal(db, db1)  # written in a fixed order, not accumulated
     g = dpool * (pooled.detach() > 0)
     ref = torch.zeros(B, 7, 7, 64, 4, device=DEV).scatter_(4, am.long().unsqueeze(-1), g.unsqueeze(-1))
     ref = ref.reshape(B, 7, 7, 64, 2, 2).permute(0, 1, 4, 2, 5, 3).reshape(B, 14, 14, 64)
-    assert rel_err(dy, ref) < 1e-2
+    assert rel_err(dy, ref) < (1e-6 if tf32 else 1e-2)
     assert rel_err(db, g.sum(dim=(0, 1, 2))) < 1e-3
 
 
 # ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tf32", [False, True])
 @pytest.mark.parametrize("keep_prob", [1.0, 0.75])
-def test_head_cnn_mode_matches_oracle(nat, keep_prob):
+def test_head_cnn_mode_matches_oracle(nat, keep_prob, tf32):
     torch.manual_seed(10)
     B, H = 128, 1024
+    adt = torch.float32 if tf32 else torch.bfloat16
     pre = torch.randn(B, H, device=DEV) * 3
     bias = torch.randn(H, device=DEV)
     ow = torch.randn(H, 10, device=DEV) * 0.1
     ob = torch.randn(10, device=DEV)
     y = torch.eye(10, device=DEV)[torch.randint(0, 10, (B,), device=DEV)]
-    hid = torch.empty(B, H, device=DEV, dtype=torch.bfloat16)
-    dhid = torch.empty(B, H, device=DEV, dtype=torch.bfloat16)
+    hid = torch.empty(B, H, device=DEV, dtype=adt)
+    dhid = torch.empty(B, H, device=DEV, dtype=adt)
     dl = torch.empty(B, 10, device=DEV)
     lr_ = torch.empty(B, device=DEV)
     hit = torch.empty(B, device=DEV, dtype=torch.uint8)
     mask = torch.ones(B, H, device=DEV, dtype=torch.uint8)
     pre2 = torch.stack([0.25 * pre, 0.75 * pre])  # two split-K partial planes
     nat.head_rows(pre2, None, bias, ow, ob, y, B, H, H, keep_prob, 123, 5, True, hid, dhid, dl, lr_, hit, mask,
-                  pre_nsplit=2, pre_split_stride=B * H)
+                  pre_nsplit=2, pre_split_stride=B * H, tf32=tf32)
     dow = torch.empty(H, 10, device=DEV)
     dhb = torch.empty(H, device=DEV)
     dob = torch.empty(10, device=DEV)
     sc = torch.empty(2, device=DEV)
-    nat.head_cols(hid, dhid, H, dl, lr_, hit, B, H, dow, dhb, dob, sc)
+    nat.head_cols(hid, dhid, H, dl, lr_, hit, B, H, dow, dhb, dob, sc, tf32=tf32)
     torch.cuda.synchronize()
     if keep_prob < 1:
         frac = mask.float().mean().item()
@@ -284,11 +380,12 @@ def test_head_cnn_mode_matches_oracle(nat, keep_prob):
     loss.backward()
     assert abs(sc[0].item() - loss.item()) < 2e-2 * max(1.0, abs(loss.item()))
     assert abs(sc[1].item() - oracle.accuracy(logits, y).item()) < 2.0 / B
-    assert rel_err(hid, h) < 1e-2
-    assert rel_err(dhid, prel.grad) < 2e-2
-    assert rel_err(dow, owl.grad) < 2e-2
-    assert rel_err(dob, obl.grad) < 1e-2
-    assert rel_err(dhb, bl.grad) < 2e-2
+    tol = 1e-4 if tf32 else 2e-2  # the tf32 arm keeps fp32 activations: only summation order differs
+    assert rel_err(hid, h) < (1e-6 if tf32 else 1e-2)
+    assert rel_err(dhid, prel.grad) < tol
+    assert rel_err(dow, owl.grad) < tol
+    assert rel_err(dob, obl.grad) < (1e-4 if tf32 else 1e-2)
+    assert rel_err(dhb, bl.grad) < tol
 
 
 def test_head_mlp_mode_and_eval(nat):
@@ -411,28 +508,30 @@ def test_gemm_segmented_operands_single_gpu(nat):
     assert rel_err(dplanes.sum(0), dy.float() @ W.float().t()) < 2e-3
 
 
-@pytest.mark.parametrize("B", [128, 40])
-def test_gemm_dgrad_fused_with_pool2_backward(nat, B):
-    """fc1 dgrad -> ReLU' -> max-pool backward in the GEMM epilogue vs the unfused PyTorch formulation."""
-    torch.manual_seed(14)
-    dhid = bf(torch.randn(B, 1024, device=DEV))
-    W = bf(torch.randn(3136, 1024, device=DEV) * 0.05)
-    pre = torch.randn(B, 14, 14, 64, device=DEV)
-    act = torch.relu(pre)
-    pooled = oracle.maxpool2x2_nhwc(act)
-    win = act.reshape(B, 7, 2, 7, 2, 64).permute(0, 1, 3, 5, 2, 4).reshape(B, 7, 7, 64, 4)
-    am = win.argmax(dim=4).to(torch.uint8)
-    pool_bf = bf(pooled)
-    dy = torch.full((B, 14, 14, 64), 9.0, device=DEV, dtype=torch.bfloat16)
-    db = torch.zeros(64, device=DEV)
-    nat.gemm_dgrad_pool2(dhid, [W.data_ptr()], 1024, B, pool_bf, am, dy, db)
+def test_gemm_tf32_segmented_operands_single_gpu(nat):
+    """The same three sharded paths on the tf32 arm (fp32 shards: what a tf32 worker reads from the owners' masters)."""
+    torch.manual_seed(16)
+    B_, Kin, H = 128, 3136, 1024
+    bounds = [0, 1152, 2176, 3136]
+    x, W, dy = torch.randn(B_, Kin, device=DEV), torch.randn(Kin, H, device=DEV), torch.randn(B_, H, device=DEV)
+    pieces = [W[bounds[i]:bounds[i + 1]].clone() for i in range(3)]
+    planes = torch.zeros(4, B_, H, device=DEV)
+    nat.gemm_bf16_seg(x, 0, [p.data_ptr() for p in pieces], 1, B_, H, Kin, planes, mode=nat.EPI_STORE_F32, lda=Kin,
+                      ldb=H, ld_out=H, seg_mode=nat.SEG_B_K, seg_rows=bounds, bn=64, splits=4, split_stride=B_ * H,
+                      tf32=True)
+    dplanes = torch.zeros(2, B_, Kin, device=DEV)
+    nat.gemm_bf16_seg(dy, 0, [p.data_ptr() for p in pieces], 0, B_, Kin, H, dplanes, mode=nat.EPI_STORE_F32, lda=H,
+                      ldb=H, ld_out=Kin, seg_mode=nat.SEG_B_N, seg_rows=bounds, bn=64, splits=2, split_stride=B_ * Kin,
+                      tf32=True)
+    slots = [torch.zeros(bounds[i + 1] - bounds[i], H, device=DEV) for i in range(3)]
+    nat.gemm_bf16_seg(x, 1, [dy.data_ptr(), 0, 0], 1, Kin, H, B_, None, mode=nat.EPI_STORE_F32, lda=Kin, ldb=H,
+                      ld_out=H, seg_mode=nat.SEG_OUT_M, seg_rows=bounds, out_ptrs=[t.data_ptr() for t in slots], bn=128,
+                      tf32=True)
     torch.cuda.synchronize()
-    dpool = (dhid.float() @ W.float().t()).reshape(B, 7, 7, 64)
-    g = dpool * (pool_bf.float() > 0)
-    ref = torch.zeros(B, 7, 7, 64, 4, device=DEV).scatter_(4, am.long().unsqueeze(-1), g.unsqueeze(-1))
-    ref = ref.reshape(B, 7, 7, 64, 2, 2).permute(0, 1, 4, 2, 5, 3).reshape(B, 14, 14, 64)
-    assert rel_err(dy, ref) < 1e-2
-    assert rel_err(db, g.sum(dim=(0, 1, 2))) < 2e-3
+    xd, Wd, dyd = tf32_trunc(x).double(), tf32_trunc(W).double(), tf32_trunc(dy).double()
+    assert rel_err(torch.cat(slots, 0), (xd.t() @ dyd).float()) < 2e-5
+    assert rel_err(planes.sum(0), (xd @ Wd).float()) < 2e-5
+    assert rel_err(dplanes.sum(0), (dyd @ Wd.t()).float()) < 2e-5
 
 
 def test_backup_workers_decide_and_masked_apply(nat):
