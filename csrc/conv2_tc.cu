@@ -92,71 +92,75 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   grid_dep_wait();
   grid_dep_launch();
 
+  // Producer and MMA warps run their loops with ALL lanes (warp-uniform control flow and addresses, so the shared-memory
+  // descriptors live in uniform registers); only the TMA / MMA / commit instructions themselves sit under elect_one().
+  // With the loops under `if (lane == 0)` the compiler had to move five registers to the uniform file around every
+  // MMA (21 instructions per UTCHMMA), which -- not the tensor pipe -- bounded the kernel.
   if (warp == 0) {
-    if (lane == 0) {
-      // the first input boxes go out before the 100 KB filter so the first MMAs are not queued behind it
-      int stage = 0;
-      uint32_t phase = 0;
-      bool filter_sent = false;
-      for (int tile = tile0; tile < num_tiles; tile += tstride) {
-        const int n = tile >> 1, ht = tile & 1;
-        for (int kw = 0; kw < 5; ++kw) {
-          mbar_wait(&a_empty[stage], phase ^ 1);
+    // the first input boxes go out before the 100 KB filter so the first MMAs are not queued behind it
+    int stage = 0;
+    uint32_t phase = 0;
+    bool filter_sent = false;
+    for (int tile = tile0; tile < num_tiles; tile += tstride) {
+      const int n = tile >> 1, ht = tile & 1;
+      for (int kw = 0; kw < 5; ++kw) {
+        mbar_wait(&a_empty[stage], phase ^ 1);
+        if (elect_one()) {
           mbar_arrive_expect_tx(&a_full[stage], C::kBoxBytes);
           // tf32 dgrad reads only this CTA's half of dy's channels (the K split)
           tma_load_4d(abuf + stage * C::kBoxBytes, &tmA, &a_full[stage], (TF && !kFwd) ? half * 32 : 0,
                       kFwd ? kw - 2 : 2 - kw, 8 * ht - 2, n);
-          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
-          if (!filter_sent) { load_filter(filt, &tmW, filt_full, TF ? half * 32 : 0); filter_sent = true; }
+          if (!filter_sent) load_filter(filt, &tmW, filt_full, TF ? half * 32 : 0);
         }
+        __syncwarp();
+        filter_sent = true;
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = TF ? make_idesc_tf32(128, C::kN, 0, kFwd ? 1 : 0) : make_idesc_bf16(128, C::kN, 0, kFwd ? 1 : 0);
-      mbar_wait(filt_full, 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = tile0; tile < num_tiles; tile += tstride, ++it) {
-        const int buf = it & 1;
-        mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+    constexpr uint32_t idesc = TF ? make_idesc_tf32(128, C::kN, 0, kFwd ? 1 : 0) : make_idesc_bf16(128, C::kN, 0, kFwd ? 1 : 0);
+    // descriptor templates: everything but the start address is fixed per operand
+    const uint64_t da0 = (TF || !kFwd) ? make_smem_desc(smem_u32(abuf), 16, 1024, kSwz128)
+                                       : make_smem_desc(smem_u32(abuf), 16, 512, kSwz64);
+    const uint64_t db0 = TF ? (kFwd ? make_smem_desc(smem_u32(filt), 4096, 512, kSwz128B32)
+                                    : make_smem_desc(smem_u32(filt), 16, 1024, kSwz128))
+                            : (kFwd ? make_smem_desc(smem_u32(filt), 4096, 1024, kSwz128)
+                                    : make_smem_desc(smem_u32(filt), 16, 1024, kSwz128));
+    // bytes between consecutive MMAs' K slices inside a filter tap tile: MN-major B steps by k-rows, K-major by 32 B
+    constexpr uint32_t kBStep = kFwd ? (TF ? 1024u : 2048u) : 32u;
+    mbar_wait(filt_full, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tstride, ++it) {
+      const int buf = it & 1;
+      mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + buf * C::kN;
+      for (int kw = 0; kw < 5; ++kw) {
+        mbar_wait(&a_full[stage], phase);
         tc_fence_after();
-        const uint32_t tacc = tmem_base + buf * C::kN;
-        for (int kw = 0; kw < 5; ++kw) {
-          mbar_wait(&a_full[stage], phase);
-          tc_fence_after();
-          const uint32_t sbox = smem_u32(abuf + stage * C::kBoxBytes);
+        if (elect_one()) {
+          const uint64_t da_s = desc_advance(da0, (uint32_t)(stage * C::kBoxBytes));
+          const uint64_t db_s = desc_advance(db0, (uint32_t)(kw * 4096));
 #pragma unroll
           for (int kh = 0; kh < 5; ++kh) {
             // forward: output row hh reads box row hh+kh.  dgrad: dy row hh+2-kh -> box row hh+4-kh.
-            const uint32_t sa = sbox + (kFwd ? kh : 4 - kh) * 16 * C::kRowBytes;
-            const uint32_t sw = smem_u32(filt + (kh * 5 + kw) * 4096);
+            // A: [128 px][K slice] K-major (32 B per MMA inside the row).  B: filter tap (kh,kw) at tap*4096.
 #pragma unroll
             for (int ks = 0; ks < C::kKSteps; ++ks) {
-              uint64_t da, db;
-              const bool acc = (kw > 0 || kh > 0 || ks > 0);
-              if (TF) {
-                da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);             // [128 px][32 ch fp32]  K-major
-                if (kFwd) db = make_smem_desc(sw + ks * 1024, 4096, 512, kSwz128B32);  // [32 ci][32 co]  MN-major
-                else      db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);        // [32 ci][32 co]  K-major (co = K)
-                umma_tf32(tacc, da, db, idesc, acc ? 1u : 0u);
-              } else {
-                if (kFwd) {
-                  da = make_smem_desc(sa + ks * 32, 16, 512, kSwz64);         // [128 px][32 ci]  K-major, 64 B rows
-                  db = make_smem_desc(sw + ks * 2048, 4096, 1024, kSwz128);   // [32 ci][64 co]   MN-major (co contiguous)
-                } else {
-                  da = make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);       // [128 px][64 co]  K-major, 128 B rows
-                  db = make_smem_desc(sw + ks * 32, 16, 1024, kSwz128);       // [32 ci][64 co]   K-major  (co = K)
-                }
-                umma_bf16(tacc, da, db, idesc, acc ? 1u : 0u);
-              }
+              const uint64_t da = desc_advance(da_s, (uint32_t)((kFwd ? kh : 4 - kh) * 16 * C::kRowBytes + ks * 32));
+              const uint64_t db = desc_advance(db_s, (uint32_t)(kh * 5 * 4096) + ks * kBStep);
+              const uint32_t acc = (kw > 0 || kh > 0 || ks > 0) ? 1u : 0u;
+              if (TF) umma_tf32(tacc, da, db, idesc, acc);
+              else    umma_bf16(tacc, da, db, idesc, acc);
             }
           }
           umma_commit(&a_empty[stage]);
-          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          if (kw == 4) umma_commit(&acc_full[buf]);
         }
-        umma_commit(&acc_full[buf]);
+        __syncwarp();
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else {
@@ -295,13 +299,13 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
   grid_dep_launch();
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int nb = tile / 7, hp = tile % 7;
-        uint8_t* st = smem + stage * C::kStageBytes;
-        mbar_wait(&empty[stage], phase ^ 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int nb = tile / 7, hp = tile % 7;
+      uint8_t* st = smem + stage * C::kStageBytes;
+      mbar_wait(&empty[stage], phase ^ 1);
+      if (elect_one()) {
         mbar_arrive_expect_tx(&full[stage], C::kDyTile + ntap * C::kInTile);
         tma_load_4d(st, &tmDy, &full[stage], 0, 0, 2 * hp, nb * 4);
         if (TF) tma_load_4d(st + 16384, &tmDy, &full[stage], 32, 0, 2 * hp, nb * 4);  // channels 32..63
@@ -309,39 +313,43 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
           const int tap = g * 4 + tl, kh = tap / 5, kw = tap % 5;
           tma_load_4d(st + C::kDyTile + tl * C::kInTile, &tmIn, &full[stage], 0, kw - 2, 2 * hp + kh - 2, nb * 4);
         }
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == C::kStages) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = TF ? make_idesc_tf32(128, 64, 1, 1) : make_idesc_bf16(128, 64, 1, 1);
-      int stage = 0, it = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        mbar_wait(&full[stage], phase);
-        tc_fence_after();
-        const uint32_t sdy = smem_u32(smem + stage * C::kStageBytes);
-        const uint32_t sa = sdy + C::kDyTile;
+    constexpr uint32_t idesc = TF ? make_idesc_tf32(128, 64, 1, 1) : make_idesc_bf16(128, 64, 1, 1);
+    // descriptor templates (start address = stage 0): A = tap tiles stacked along M, B = the dy tile
+    const uint64_t db0 = TF ? make_smem_desc(smem_u32(smem), 16384, 512, kSwz128B32)          // N chunks = co halves
+                            : make_smem_desc(smem_u32(smem), 8192, 1024, kSwz128);
+    const uint64_t da0 = TF ? make_smem_desc(smem_u32(smem) + C::kDyTile, C::kInTile, 512, kSwz128B32)  // M chunks = taps
+                            : make_smem_desc(smem_u32(smem) + C::kDyTile, 8192, 512, kSwz64);
+    int stage = 0, it = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t da_s = desc_advance(da0, (uint32_t)(stage * C::kStageBytes));
+        const uint64_t db_s = desc_advance(db0, (uint32_t)(stage * C::kStageBytes));
         if (TF) {
 #pragma unroll
-          for (int ks = 0; ks < 16; ++ks) {  // 8 pixels (1024 B of every 128 B-wide tile) per MMA
-            const uint64_t da = make_smem_desc(sa + ks * 1024, C::kInTile, 512, kSwz128B32);   // M chunks = taps
-            const uint64_t dbb = make_smem_desc(sdy + ks * 1024, 16384, 512, kSwz128B32);       // N chunks = co halves
-            umma_tf32(tmem_base, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
-          }
+          for (int ks = 0; ks < 16; ++ks)  // 8 pixels (1024 B of every 128 B-wide tile) per MMA
+            umma_tf32(tmem_base, desc_advance(da_s, ks * 1024), desc_advance(db_s, ks * 1024), idesc,
+                      (it > 0 || ks > 0) ? 1u : 0u);
         } else {
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint64_t da = make_smem_desc(sa + ks * 1024, 8192, 512, kSwz64);     // 16 px = two 512 B atoms
-            const uint64_t dbb = make_smem_desc(sdy + ks * 2048, 8192, 1024, kSwz128);  // 16 px = two 1024 B atoms
-            umma_bf16(tmem_base, da, dbb, idesc, (it > 0 || ks > 0) ? 1u : 0u);
-          }
+          for (int ks = 0; ks < 8; ++ks)   // 16 pixels: two 512 B atoms of A (64 B rows), two 1024 B atoms of B
+            umma_bf16(tmem_base, desc_advance(da_s, ks * 1024), desc_advance(db_s, ks * 2048), idesc,
+                      (it > 0 || ks > 0) ? 1u : 0u);
         }
         umma_commit(&empty[stage]);
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
-      umma_commit(acc_full);
+      __syncwarp();
+      if (++stage == C::kStages) { stage = 0; phase ^= 1; }
     }
+    if (elect_one()) umma_commit(acc_full);
+    __syncwarp();
   } else {
     // ---- epilogue warps: partial plane -> group rendezvous -> fixed-order slice reduction ----
     const int q = warp & 3;
@@ -360,17 +368,16 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
 #pragma unroll
       for (int i = 0; i < 16; i += 4) __stcg(reinterpret_cast<float4*>(o + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
     }
-    __threadfence();
-    asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps
+    asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps: all partial stores are issued
     if (et == 0) {
+      __threadfence();  // one fence for the CTA (cumulative over the stores ordered before the barrier)
       // monotonic counter: this launch's arrivals fill one block of `chunks` counts
       const unsigned old = atomicAdd(&counters[g], 1u);
       const unsigned target = (old / (unsigned)chunks + 1u) * (unsigned)chunks;
       unsigned long long t0 = globaltimer_ns();
       unsigned itn = 0;
       while ((int)(*reinterpret_cast<volatile unsigned*>(&counters[g]) - target) < 0) {
-        __nanosleep(64);
-        if ((++itn & 0x3ff) == 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) {
+        if ((++itn & 0x3fff) == 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) {
           printf("tfd: conv2 wgrad group %d rendezvous timed out\n", g);
           __trap();
         }
@@ -378,13 +385,27 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_con
       __threadfence();
     }
     asm volatile("bar.sync 1, 128;" ::: "memory");
+    // this CTA finalises a slice of the group's rows: float4 outputs, all planes' loads in flight, added in plane order
     const int rows_valid = ntap * 32;                               // rows of this group that exist in dW
     const int per = (rows_valid + chunks - 1) / chunks;             // rows this CTA finalises
     const int r0 = blockIdx.x * per, r1 = min(rows_valid, r0 + per);
-    for (int idx = et + r0 * 64; idx < r1 * 64; idx += 128) {
-      float sacc = 0.f;
-      for (int c = 0; c < chunks; ++c) sacc += __ldcg(planes + (size_t)c * 8192 + idx);  // plane order: deterministic
-      dw[(size_t)g * 8192 + idx] = sacc;  // (g*4 + tap_local)*32*64 + ci*64 + co  ==  g*8192 + idx
+    const float4* planes4 = reinterpret_cast<const float4*>(planes);
+    float4* dw4 = reinterpret_cast<float4*>(dw + (size_t)g * 8192);  // (g*4 + tap_local)*32*64 + ci*64 + co == g*8192 + idx
+    for (int i4 = et + r0 * 16; i4 < r1 * 16; i4 += 128) {
+      float4 sacc = make_float4(0.f, 0.f, 0.f, 0.f);
+      int c = 0;
+      for (; c + 8 <= chunks; c += 8) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldcg(planes4 + (size_t)(c + u) * 2048 + i4);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { sacc.x += v[u].x; sacc.y += v[u].y; sacc.z += v[u].z; sacc.w += v[u].w; }
+      }
+      for (; c < chunks; ++c) {
+        const float4 v = __ldcg(planes4 + (size_t)c * 2048 + i4);
+        sacc.x += v.x; sacc.y += v.y; sacc.z += v.z; sacc.w += v.w;
+      }
+      dw4[i4] = sacc;
     }
   }
   tc_fence_before();

@@ -40,11 +40,15 @@ template <> __device__ __forceinline__ float from_f<float>(float v) { return v; 
 // is never reset, so a kernel can sit in a CUDA graph and be replayed.
 __device__ __forceinline__ bool last_block_arrives(unsigned* counter, unsigned nblocks) {
   __shared__ unsigned s_last;
-  __threadfence();
+  __syncthreads();  // every thread's partial results are ordered before thread 0's fence (cumulativity does the rest:
+                    // ONE fence per block -- a fence in every thread made these kernels membar-bound)
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned last = (atomicAdd(counter, 1u) % nblocks == nblocks - 1u) ? 1u : 0u;
+    if (last) __threadfence();
+    s_last = last;
+  }
   __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) % nblocks == nblocks - 1u) ? 1u : 0u;
-  __syncthreads();
-  if (s_last) __threadfence();
   return s_last != 0;
 }
 
@@ -154,99 +158,124 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
 }
 
 // conv1 filter gradient: pool/ReLU backward folded in (only the arg-max position of each 2x2 window carries
-// gradient).  One block per PAIR of images, 16 warps: warp = (image of the pair, pixel group), lane = channel.
-// dpool arrives as nsplit partial planes (the tf32 conv2 dgrad splits its K over two CTAs) that are added here in
-// plane order.  Reduction without atomics: warps -> shared memory (fixed order) -> one partial [26][32] per block in
-// `scratch` -> the last block to finish sums the blocks' partials in block order and writes dw / db (which may be
-// staging slots on another GPU).  scratch = 16 counter words + ceil(B/2) * 832 floats, zeroed once by the caller.
+// gradient).  One block of 32 warps per image: warp = pixel group, lane = channel, so a thread touches at most 7 of
+// the 196 pooled pixels and all its global loads are in flight at once (the kernel is load-latency bound: the
+// round-1 shape with 13 pixels per thread took 12 us).  dpool arrives as nsplit partial planes (the tf32 conv2 dgrad
+// splits its K over two CTAs) that are added here in plane order.  Reduction without atomics: warps -> shared memory
+// in four fixed passes -> one partial [26][32] per image in `scratch` -> the last block to finish sums the images'
+// partials in a fixed order and writes dw / db (which may be staging slots on another GPU).
+// scratch = 16 counter words + B * 832 floats, zeroed once by the caller.
 template <typename T>
-__global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
-                                                          int nsplit, long long split_stride, const T* __restrict__ pool,
-                                                          const unsigned char* __restrict__ amax, float* __restrict__ dw,
-                                                          float* __restrict__ db, float* __restrict__ scratch, int B) {
+__global__ void __launch_bounds__(1024) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
+                                                           int nsplit, long long split_stride, const T* __restrict__ pool,
+                                                           const unsigned char* __restrict__ amax, float* __restrict__ dw,
+                                                           float* __restrict__ db, float* __restrict__ scratch, int B) {
   grid_dep_wait();
   grid_dep_launch();
-  __shared__ float img[2][32][33];
-  __shared__ float red[8][26][32];
-  const int n0 = blockIdx.x * 2;
-  for (int i = threadIdx.x; i < 2 * 32 * 32; i += blockDim.x) {
-    const int im = i >> 10, r = ((i >> 5) & 31) - 2, c = (i & 31) - 2;
-    const int n = n0 + im;
-    img[im][(i >> 5) & 31][i & 31] = (n < B && r >= 0 && r < 28 && c >= 0 && c < 28) ? x[(long long)n * 784 + r * 28 + c] : 0.f;
-  }
-  __syncthreads();
-  const int c = threadIdx.x & 31, wrp = threadIdx.x >> 5, im = wrp >> 3, grp = wrp & 7;
-  const int n = n0 + im;
-  float acc[25];
+  __shared__ float img[32][33];
+  __shared__ __align__(16) float red[8][26][32];
+  const int n = blockIdx.x;
+  const int c = threadIdx.x & 31, grp = threadIdx.x >> 5;
+  // this thread's pixels: grp, grp+32, ...; all their loads are issued before anything else
+  float gq[7];
+  int aq[7];
 #pragma unroll
-  for (int t = 0; t < 25; ++t) acc[t] = 0.f;
-  float accb = 0.f;
-  // 196 pixels / 8 groups = at most 25 per thread: issue all their global loads first (the loop below would otherwise
-  // sit on one dependent load chain per pixel), then do the shared-memory / FMA work
-  float gq[25];
-  int aq[25];
-#pragma unroll
-  for (int it = 0; it < 25; ++it) {
-    const int pix = grp + it * 8;
+  for (int it = 0; it < 7; ++it) {
+    const int pix = grp + it * 32;
     gq[it] = 0.f;
     aq[it] = 0;
-    if (pix < 196 && n < B) {
+    if (pix < 196) {
       const long long idx = ((long long)n * 196 + pix) * 32 + c;
       float g = dpool[idx];
-      for (int sp = 1; sp < nsplit; ++sp) g += dpool[sp * split_stride + idx];
+      if (nsplit > 1) g += dpool[split_stride + idx];
+      for (int sp = 2; sp < nsplit; ++sp) g += dpool[sp * split_stride + idx];
       gq[it] = (to_f(pool[idx]) > 0.f) ? g : 0.f;
       aq[it] = amax[idx];
     }
   }
-#pragma unroll
-  for (int it = 0; it < 25; ++it) {
-    const int pix = grp + it * 8;
-    if (pix >= 196) break;
-    const int ph = pix / 14, pw = pix % 14;
-    const float g = gq[it];
-    const int h = 2 * ph + (aq[it] >> 1), wq = 2 * pw + (aq[it] & 1);
-    accb += g;
-#pragma unroll
-    for (int kh = 0; kh < 5; ++kh)
-#pragma unroll
-      for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(g, img[im][h + kh][wq + kw], acc[kh * 5 + kw]);
-  }
-  // image 1's warps deposit, image 0's warps add on top: a fixed order
-  if (im == 1) {
-#pragma unroll
-    for (int t = 0; t < 25; ++t) red[grp][t][c] = acc[t];
-    red[grp][25][c] = accb;
+  {
+    const int i = threadIdx.x;  // 32 x 32 padded image, one element per thread
+    const int r = (i >> 5) - 2, cc = (i & 31) - 2;
+    img[i >> 5][i & 31] = (r >= 0 && r < 28 && cc >= 0 && cc < 28) ? x[(long long)n * 784 + r * 28 + cc] : 0.f;
   }
   __syncthreads();
-  if (im == 0) {
+  float acc[25];
 #pragma unroll
-    for (int t = 0; t < 25; ++t) red[grp][t][c] += acc[t];
-    red[grp][25][c] += accb;
+  for (int t = 0; t < 25; ++t) acc[t] = 0.f;
+  float accb = 0.f;
+#pragma unroll
+  for (int it = 0; it < 7; ++it) {
+    const int pix = grp + it * 32;
+    if (pix < 196) {
+      const int ph = pix / 14, pw = pix % 14;
+      const float g = gq[it];
+      const int h = 2 * ph + (aq[it] >> 1), wq = 2 * pw + (aq[it] & 1);
+      accb += g;
+#pragma unroll
+      for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(g, img[h + kh][wq + kw], acc[kh * 5 + kw]);
+    }
   }
-  __syncthreads();
+  // 32 warps -> 8 rows of `red` in four passes (pass k: warps 8k..8k+7), a fixed order
+#pragma unroll 1
+  for (int pass = 0; pass < 4; ++pass) {
+    if ((grp >> 3) == pass) {
+      const int row = grp & 7;
+      if (pass == 0) {
+#pragma unroll
+        for (int t = 0; t < 25; ++t) red[row][t][c] = acc[t];
+        red[row][25][c] = accb;
+      } else {
+#pragma unroll
+        for (int t = 0; t < 25; ++t) red[row][t][c] += acc[t];
+        red[row][25][c] += accb;
+      }
+    }
+    __syncthreads();
+  }
   unsigned* counter = reinterpret_cast<unsigned*>(scratch);
   float* parts = scratch + 16;
-  for (int i = threadIdx.x; i < 26 * 32; i += blockDim.x) {
-    const int t = i >> 5, cc = i & 31;
+  if (threadIdx.x < 832) {
+    const int i = threadIdx.x, t = i >> 5, cc = i & 31;
     float s = 0.f;
 #pragma unroll
     for (int g8 = 0; g8 < 8; ++g8) s += red[g8][t][cc];
     __stcg(parts + (size_t)blockIdx.x * 832 + i, s);
   }
   if (!last_block_arrives(counter, gridDim.x)) return;
-  for (int i = threadIdx.x; i < 26 * 32; i += blockDim.x) {
-    float s = 0.f;
-    int bk = 0;
-    for (; bk + 8 <= (int)gridDim.x; bk += 8) {
-      float v[8];
+  // final sum over the images' partials: 208 float4 outputs x 4 interleaved groups of images, each summed in image
+  // order with 8 loads in flight, then the four group sums are added in group order
+  float4* red4 = reinterpret_cast<float4*>(&red[0][0][0]);  // [4][208]
+  const int o4 = threadIdx.x % 208, grp4 = threadIdx.x / 208;
+  if (grp4 < 4) {
+    const float4* p4 = reinterpret_cast<const float4*>(parts) + o4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    int bk = grp4;
+    for (; bk + 28 < (int)gridDim.x; bk += 32) {
+      float4 v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = __ldcg(parts + (size_t)(bk + u) * 832 + i);
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(p4 + (size_t)(bk + 4 * u) * 208);
 #pragma unroll
-      for (int u = 0; u < 8; ++u) s += v[u];
+      for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
     }
-    for (; bk < (int)gridDim.x; ++bk) s += __ldcg(parts + (size_t)bk * 832 + i);
-    if (i < 800) dw[i] = s;
-    else db[i - 800] = s;
+    for (; bk < (int)gridDim.x; bk += 4) {
+      const float4 v = __ldcg(p4 + (size_t)bk * 208);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    red4[grp4 * 208 + o4] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < 208) {
+    float4 s = red4[threadIdx.x];
+#pragma unroll
+    for (int g4 = 1; g4 < 4; ++g4) {
+      const float4 v = red4[g4 * 208 + threadIdx.x];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    const int i = threadIdx.x * 4;
+    if (i < 800) *reinterpret_cast<float4*>(dw + i) = s;
+    else *reinterpret_cast<float4*>(db + (i - 800)) = s;
   }
 }
 
@@ -302,13 +331,39 @@ __global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict_
     __stcg(parts + (size_t)blockIdx.x * 64 + threadIdx.x,
            red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192]);
   if (!last_block_arrives(counter, gridDim.x)) return;
-  // 4 row groups x 64 channels: each thread sums every 4th block's partial, then the four are added in order
-  float s = 0.f;
-  for (int bk = pl; bk < (int)gridDim.x; bk += 4) s += __ldcg(parts + (size_t)bk * 64 + c);
-  red[threadIdx.x] = s;
+  // 16 float4 channel groups x 16 interleaved groups of blocks: each thread sums every 16th block's partial in block
+  // order with 8 loads in flight; the 16 group sums are then added in group order
+  __shared__ float4 red4[16][16];
+  {
+    const int c4 = threadIdx.x & 15, bg = threadIdx.x >> 4;
+    const float4* p4 = reinterpret_cast<const float4*>(parts) + c4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    int bk = bg;
+    for (; bk + 112 < (int)gridDim.x; bk += 128) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(p4 + (size_t)(bk + 16 * u) * 16);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+    }
+    for (; bk < (int)gridDim.x; bk += 16) {
+      const float4 v = __ldcg(p4 + (size_t)bk * 16);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    red4[bg][c4] = s;
+  }
   __syncthreads();
-  if (threadIdx.x < 64) db[threadIdx.x] = red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192];
+  if (threadIdx.x < 16) {
+    float4 s = red4[0][threadIdx.x];
+#pragma unroll
+    for (int bg = 1; bg < 16; ++bg) {
+      const float4 v = red4[bg][threadIdx.x];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    *reinterpret_cast<float4*>(db + threadIdx.x * 4) = s;
+  }
 }
+
 
 // ------------------------------------------------------------------------------------------------
 // head: rows phase
@@ -648,7 +703,7 @@ extern "C" int tfd_conv1_fwd(int dtype, const float* x, const float* w, const fl
   return 0;
 }
 
-extern "C" long long tfd_conv1_wgrad_scratch_floats(int B) { return 16 + (long long)((B + 1) / 2) * 832; }
+extern "C" long long tfd_conv1_wgrad_scratch_floats(int B) { return 16 + (long long)B * 832; }
 extern "C" long long tfd_pool2_bwd_scratch_floats(int B) { return 16 + (((long long)B * 49 + 15) / 16) * 64; }
 
 extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, int nsplit, long long split_stride,
@@ -656,12 +711,12 @@ extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, in
                                int B, void* stream) {
   TFD_ACT_CHECK("conv1_wgrad");
   TFD_REQUIRE(scratch != nullptr && nsplit >= 1, "conv1_wgrad: scratch missing or nsplit %d < 1", nsplit);
-  const dim3 grid((B + 1) / 2);
+  const dim3 grid(B);
   if (dtype == TFD_DTYPE_TF32)
-    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<float>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
+    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<float>, grid, dim3(1024), 0, ST(stream), x, dpool, nsplit, split_stride,
                               (const float*)pool_out, argmax, dw, db, scratch, B));
   else
-    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<bf16>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
+    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<bf16>, grid, dim3(1024), 0, ST(stream), x, dpool, nsplit, split_stride,
                               (const bf16*)pool_out, argmax, dw, db, scratch, B));
   TFD_LAUNCH_CHECK();
   return 0;

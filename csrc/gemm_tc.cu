@@ -139,28 +139,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   grid_dep_wait();    // prologue above overlapped the previous kernel's tail; from here on we touch global memory
   grid_dep_launch();
 
+  // Producer and MMA warps run their loops with all 32 lanes (warp-uniform control flow, addresses and descriptors:
+  // they stay in uniform registers); only the TMA / MMA / commit instructions sit under elect_one().  Loops under
+  // `if (lane == 0)` made the compiler shuttle five registers to the uniform file around every UTCHMMA.
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      int gated = -1;  // last shard whose version flag this producer has already seen
-      const uint32_t want = sg.wait_value + (sg.wait_value_ptr ? *sg.wait_value_ptr : 0u);
-      // dgrad: the whole N tile comes from one shard
-      int seg_n = 0, nrow0 = n0;
-      if (sg.mode == TFD_SEG_B_N) {
-        seg_n = find_seg(sg, n0);
-        nrow0 = n0 - sg.bound[seg_n];
-        if (sg.wait_flag[seg_n]) spin_until_ge(sg.wait_flag[seg_n], want, "gemm pull gate (N)");
-      } else if (sg.mode != TFD_SEG_B_K && sg.wait_flag[0]) {
-        spin_until_ge(sg.wait_flag[0], want, "gemm pull gate");
+    int stage = 0;
+    uint32_t phase = 0;
+    int gated = -1;  // last shard whose version flag this producer has already seen
+    const uint32_t want = sg.wait_value + (sg.wait_value_ptr ? *sg.wait_value_ptr : 0u);
+    // dgrad: the whole N tile comes from one shard
+    int seg_n = 0, nrow0 = n0;
+    if (sg.mode == TFD_SEG_B_N) {
+      seg_n = find_seg(sg, n0);
+      nrow0 = n0 - sg.bound[seg_n];
+      if (sg.wait_flag[seg_n]) spin_until_ge(sg.wait_flag[seg_n], want, "gemm pull gate (N)");
+    } else if (sg.mode != TFD_SEG_B_K && sg.wait_flag[0]) {
+      spin_until_ge(sg.wait_flag[0], want, "gemm pull gate");
+    }
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      uint8_t* sa = smem + stage * C::kStageBytes;
+      uint8_t* sb = sa + BM * 128;
+      const int k0 = kb * BK;
+      int s = 0, krow = k0;
+      if (B_MN != 0 && sg.mode == TFD_SEG_B_K) {
+        s = find_seg(sg, k0);
+        krow = k0 - sg.bound[s];
+        if (s != gated) {
+          if (sg.wait_flag[s]) spin_until_ge(sg.wait_flag[s], want, "gemm pull gate (K)");
+          gated = s;
+        }
       }
-      for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sa = smem + stage * C::kStageBytes;
-        uint8_t* sb = sa + BM * 128;
+      if (elect_one()) {
         mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
-        const int k0 = kb * BK;
         if (A_MN == 0) {
           tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);            // box [128 rows(m), BK k]
         } else {
@@ -169,50 +181,46 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tma_load_2d(sa + c * E::kMnBoxBytes, &tmA, &full_bar[stage], m0 + c * E::kMnW, k0);
         }
         if (B_MN == 0) {
-          tma_load_2d(sb, &tmBs.m[seg_n], &full_bar[stage], k0, nrow0);  // box [BN rows(n), 64 k]
+          tma_load_2d(sb, &tmBs.m[seg_n], &full_bar[stage], k0, nrow0);  // box [BN rows(n), BK k]
         } else {
-          int s = 0, krow = k0;
-          if (sg.mode == TFD_SEG_B_K) {
-            s = find_seg(sg, k0);
-            krow = k0 - sg.bound[s];
-            if (s != gated) {
-              if (sg.wait_flag[s]) spin_until_ge(sg.wait_flag[s], want, "gemm pull gate (K)");
-              gated = s;
-            }
-          }
 #pragma unroll
           for (int c = 0; c < BN / E::kMnW; ++c)
             tma_load_2d(sb + c * E::kMnBoxBytes, &tmBs.m[s], &full_bar[stage], n0 + c * E::kMnW, krow);
         }
-        if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == nstages) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = TF ? make_idesc_tf32(BM, BN, A_MN, B_MN) : make_idesc_bf16(BM, BN, A_MN, B_MN);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
-        const uint32_t sb = sa + BM * 128;
+    constexpr uint32_t idesc = TF ? make_idesc_tf32(BM, BN, A_MN, B_MN) : make_idesc_bf16(BM, BN, A_MN, B_MN);
+    // descriptor templates at stage 0; per stage / per MMA only the start address moves.
+    // K-major: one MMA's K = 32 B inside the 128 B swizzle row.  MN-major: its k-rows are E::kMnKStep bytes further
+    // down the box (bf16: 16 rows = two 1024 B atoms; tf32: 8 rows = two 512 B atoms).
+    const uint32_t s0 = smem_u32(smem);
+    const uint64_t da0 = A_MN ? make_smem_desc(s0, E::kMnBoxBytes, E::kMnSbo, E::kMnSwz) : make_smem_desc(s0, 16, 1024, kSwz128);
+    const uint64_t db0 = B_MN ? make_smem_desc(s0 + BM * 128, E::kMnBoxBytes, E::kMnSbo, E::kMnSwz)
+                              : make_smem_desc(s0 + BM * 128, 16, 1024, kSwz128);
+    constexpr uint32_t kAStep = A_MN ? E::kMnKStep : 32, kBStep = B_MN ? E::kMnKStep : 32;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t da_s = desc_advance(da0, (uint32_t)(stage * C::kStageBytes));
+        const uint64_t db_s = desc_advance(db0, (uint32_t)(stage * C::kStageBytes));
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
-          // K-major: one MMA's K = 32 B inside the 128 B swizzle row.  MN-major: its k-rows are E::kMnKStep bytes
-          // further down the box (bf16: 16 rows = two 1024 B atoms; tf32: 8 rows = two 512 B atoms).
-          const uint64_t da = A_MN ? make_smem_desc(sa + ks * E::kMnKStep, E::kMnBoxBytes, E::kMnSbo, E::kMnSwz)
-                                   : make_smem_desc(sa + ks * 32, 16, 1024, kSwz128);
-          const uint64_t db = B_MN ? make_smem_desc(sb + ks * E::kMnKStep, E::kMnBoxBytes, E::kMnSbo, E::kMnSwz)
-                                   : make_smem_desc(sb + ks * 32, 16, 1024, kSwz128);
+          const uint64_t da = desc_advance(da_s, ks * kAStep), db = desc_advance(db_s, ks * kBStep);
           if (TF) umma_tf32(tmem_base, da, db, idesc, (kb > kb_begin || ks > 0) ? 1u : 0u);
           else    umma_bf16(tmem_base, da, db, idesc, (kb > kb_begin || ks > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
-        if (++stage == nstages) { stage = 0; phase ^= 1; }
+        if (kb == kb_end - 1) umma_commit(tmem_full_bar);
       }
-      umma_commit(tmem_full_bar);
+      __syncwarp();
+      if (++stage == nstages) { stage = 0; phase ^= 1; }
     }
   } else {
     // ===== epilogue: warps 2..5 own TMEM lane quadrants (warp % 4) =====
@@ -429,6 +437,9 @@ int launch(const CUtensorMap& tmA, const TmapArray& tmBs, const GemmParams& p, c
   GemmParams q = p;
   const int per_split = (p.kblocks + p.splits - 1) / p.splits;
   q.stages = per_split < C::kStages ? per_split : C::kStages;
+  // short K loops (wgrad: K = batch): two stages are enough and keep the CTA at ~69 KB so three fit on an SM and one
+  // CTA's store drain overlaps another's loads (tf32 has 4 K blocks for K = 128 where bf16 has 2)
+  if (per_split <= 4 && q.stages > 2) q.stages = 2;
   static const int cap_kb = [] {  // tuning knob: cap the pipeline so two CTAs (of this or another kernel) share an SM
     const char* e = getenv("TFD_GEMM_SMEM_KB");
     return e ? atoi(e) : 0;

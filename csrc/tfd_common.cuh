@@ -198,6 +198,9 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
   return d;
 }
 
+// the same descriptor with its start address moved by `bytes` (a multiple of 16; the result stays below 256 KB)
+__device__ __forceinline__ uint64_t desc_advance(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
+
 // kind::f16, A/B bf16, D fp32.  a_mn / b_mn: 1 = MN-major operand, 0 = K-major.
 __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn, int b_mn) {
   return (1u << 4)                    // c_format  = F32

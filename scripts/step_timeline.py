@@ -28,7 +28,7 @@ if world > 1:  # under torchrun: colocated ps shards, one rank per GPU; rank 0 p
     eng = GpuClusterEngine(SPEC, Topology.make(world, os.environ.get("TFD_LAYOUT", "colocated")), rank,
                            "cuda:%d" % local, init_stddev=STD, pull_mode=os.environ.get("TFD_PULL", "auto"))
 else:
-    eng = NativeEngine(SPEC, init_stddev=STD)
+    eng = NativeEngine(SPEC, init_stddev=STD, precision=os.environ.get("TFD_PRECISION", "tf32"))
 rng = np.random.RandomState(rank)
 x = rng.rand(128, 784).astype(np.float32)
 y = np.eye(10, dtype=np.float32)[rng.randint(0, 10, size=128)]

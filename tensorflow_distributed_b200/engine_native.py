@@ -310,7 +310,7 @@ class NativeEngine:
         from .models import cnn
         cnn.forward(self, ws, training, keep_prob, mask_out)
 
-    _prio_default = "0"  # measured neutral on one GPU (0.1213 vs 0.1207 ms); the ps cluster engine turns it on
+    _prio_default = "1"  # critical path (conv2 dgrad) ahead of the weight-gradient branches when both are ready
 
     def conv1_fwd(self, ws: "Workspace", training: bool = True) -> None:
         nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, ws.B, tf32=self.tf32)
