@@ -37,9 +37,26 @@ struct AdamArgs {
   int qlen;
   const unsigned* shutdown;     // non-zero: leave without applying (the ps is being released)
   int slots_bf16;               // gradient slots hold bf16 (halves the push bytes); accumulation stays fp32
-  long long skip_begin, skip_end;  // elements [skip_begin, skip_end) are left alone (updated by an earlier launch)
-  int finalize;                 // 1: bump t / global_step and publish the version; 0: partial launch of this step
   const unsigned* mask_ptr;     // backup workers: bit w set = slot w contributes to this update (decided by decide_kernel)
+  // ---- colocated strict-sync step: the rendezvous kernels folded into this one ----
+  unsigned* signal_arrive[TFD_MAX_SEG];  // every shard's arrival counter (peer pointers): this rank's worker signals
+  int n_signal;                          //   "my gradients are in your slot" from block 0 before anybody waits
+  unsigned* local_step;                  // this rank's worker step word, advanced by the last block
+};
+
+// Publish table: what the owner shard stores into every worker's parameter mirror (peer memory) right after the
+// update, so that a worker's next step reads its small parameters from LOCAL memory and waits on a LOCAL version word.
+struct PubPiece {
+  long long f32_off;   // byte offset of the variable's fp32 mirror inside a worker heap, or -1
+  long long b16_off;   // byte offset of its bf16 mirror (bf16 arm, tensor-core operands), or -1
+  int ld16;            // leading dimension of the bf16 mirror (elements)
+  int pad;
+};
+struct PubTable {
+  PubPiece pc[kMaxPieces];        // parallel to the PieceTable
+  unsigned char* base[TFD_MAX_SLOTS];  // every worker's heap base (peer-mapped; the own rank's is local)
+  unsigned* wver[TFD_MAX_SLOTS];       // every worker's LOCAL version word for this shard
+  int nworkers;                        // 0: nothing is published (single GPU, legacy pull protocol)
 };
 
 // four gradient values at element index i of a staging slot (fp32 or bf16 storage)
@@ -50,9 +67,17 @@ __device__ __forceinline__ float4 load_grad4(const float* slot, long long i, int
                      __uint_as_float(r.y & 0xffff0000u));
 }
 
-__global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __grid_constant__ PieceTable pt) {
+__global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __grid_constant__ PieceTable pt,
+                                                         const __grid_constant__ PubTable pub) {
   grid_dep_wait();
   grid_dep_launch();
+  // Colocated strict sync: this rank's worker half signals "my gradients are in your slots" to every shard from here
+  // (the gradient kernels of this step ran earlier in the same stream and stored straight into the owners' slots), so
+  // no stand-alone push kernel exists.  One thread per shard: the NVLink round trips of the releases overlap.
+  if (blockIdx.x == 0 && (int)threadIdx.x < a.n_signal) {
+    __threadfence_system();
+    red_add_release_sys_u32(a.signal_arrive[threadIdx.x], 1u);
+  }
   // Every thread derives the step index and lr_t itself (one broadcast load + a few SFU ops): no block barrier
   // and no serial prologue in front of the streaming loop.  Only one thread per block waits for the arrivals.
   const unsigned t = a.t_counter[0] + 1;  // this update's 1-based index
@@ -98,9 +123,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   const float lr_t = a.lr * sqrtf(om_b2t) / om_b1t;
   // Two float4 groups per thread per iteration, one block-stride apart (every warp instruction touches 512
   // contiguous bytes); all eight streaming loads are issued before the first use (memory-level parallelism).
-  // index space = the arena minus the skipped range (already updated by the early launch of this step)
-  const long long skip4 = (a.skip_end - a.skip_begin) >> 2, skipb4 = a.skip_begin >> 2;
-  const long long n4 = (a.n >> 2) - skip4;
+  const long long n4 = a.n >> 2;
   const long long stride4 = (long long)gridDim.x * blockDim.x;
   int first = 0;
   if (a.mask_ptr) first = __ffs(use_mask) - 1;
@@ -109,7 +132,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   int cur = 0;  // cached piece index for the shadow lookup
   for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += 2 * stride4) {
     const long long j0 = i4, j1 = i4 + stride4;
-    long long idx[2] = {(j0 < skipb4 ? j0 : j0 + skip4) << 2, (j1 < skipb4 ? j1 : j1 + skip4) << 2};
+    long long idx[2] = {j0 << 2, j1 << 2};
     const bool ok0 = true, ok1 = j1 < n4;
     if (!ok1) idx[1] = idx[0];
     float4 w4[2], m4[2], v4[2], g4[2];
@@ -146,27 +169,50 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
       __stcs(reinterpret_cast<float4*>(a.w + i), make_float4(wv[0], wv[1], wv[2], wv[3]));
       __stcs(reinterpret_cast<float4*>(a.m + i), make_float4(mv[0], mv[1], mv[2], mv[3]));
       __stcs(reinterpret_cast<float4*>(a.v + i), make_float4(vv[0], vv[1], vv[2], vv[3]));
-      if (a.shadow) {
+      if (a.shadow || pub.nworkers > 0) {
         // pieces are 64-element aligned in the arena, so one float4 lies in one piece; a thread's indices grow
         // monotonically, so the piece found last time is almost always still the right one
         if (!(i >= pt.p[cur].arena_off && i < pt.p[cur].arena_off + pt.p[cur].numel)) {
           for (int q = 0; q < pt.n; ++q)
             if (i >= pt.p[q].arena_off && i < pt.p[q].arena_off + pt.p[q].numel) { cur = q; break; }
         }
-        {
-          const tfd_piece_t& pc = pt.p[cur];
-          if (i >= pc.arena_off && i < pc.arena_off + pc.numel) {
-            if (pc.ld_shadow > 0) {
-              const long long e0 = i - pc.arena_off;
-              if (pc.ld_shadow == pc.cols) {
-                *reinterpret_cast<uint2*>(a.shadow + pc.shadow_off + e0) =
-                    make_uint2(pack_bf16x2(wv[0], wv[1]), pack_bf16x2(wv[2], wv[3]));
-              } else {
+        const tfd_piece_t& pc = pt.p[cur];
+        if (i >= pc.arena_off && i < pc.arena_off + pc.numel) {
+          const long long e0 = i - pc.arena_off;
+          const uint2 packed = make_uint2(pack_bf16x2(wv[0], wv[1]), pack_bf16x2(wv[2], wv[3]));
+          if (a.shadow && pc.ld_shadow > 0) {
+            if (pc.ld_shadow == pc.cols) {
+              *reinterpret_cast<uint2*>(a.shadow + pc.shadow_off + e0) = packed;
+            } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const long long e = e0 + j;
-                  if (e < pc.numel)
-                    a.shadow[pc.shadow_off + (e / pc.cols) * pc.ld_shadow + (e % pc.cols)] = __float2bfloat16(wv[j]);
+              for (int j = 0; j < 4; ++j) {
+                const long long e = e0 + j;
+                if (e < pc.numel)
+                  a.shadow[pc.shadow_off + (e / pc.cols) * pc.ld_shadow + (e % pc.cols)] = __float2bfloat16(wv[j]);
+              }
+            }
+          }
+          // every worker's mirror of a small variable gets the new values now (peer stores; mirrors are padded to
+          // whole float4 groups, so the tail of a 10-element bias needs no special case)
+          if (pub.nworkers > 0) {
+            const PubPiece& pp = pub.pc[cur];
+            if (pp.f32_off >= 0) {
+              const float4 o4 = make_float4(wv[0], wv[1], wv[2], wv[3]);
+              for (int wk = 0; wk < pub.nworkers; ++wk)
+                *reinterpret_cast<float4*>(pub.base[wk] + pp.f32_off + 4 * e0) = o4;
+            }
+            if (pp.b16_off >= 0) {
+              if (pp.ld16 == pc.cols) {
+                for (int wk = 0; wk < pub.nworkers; ++wk)
+                  *reinterpret_cast<uint2*>(pub.base[wk] + pp.b16_off + 2 * e0) = packed;
+              } else {
+                for (int wk = 0; wk < pub.nworkers; ++wk) {
+                  bf16* d = reinterpret_cast<bf16*>(pub.base[wk] + pp.b16_off);
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    const long long e = e0 + j;
+                    if (e < pc.numel) d[(e / pc.cols) * pp.ld16 + (e % pc.cols)] = __float2bfloat16(wv[j]);
+                  }
                 }
               }
             }
@@ -175,19 +221,30 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
       }
     }
   }
-  // publish: last block bumps the counters and releases the new parameter version
-  __threadfence();
+  // publish: last block bumps the counters and releases the new parameter version.  One fence per block (the
+  // barrier orders every thread's stores before it; system scope because mirrors live on other GPUs).
   __syncthreads();
+  __shared__ unsigned s_last;
   if (threadIdx.x == 0) {
+    if (pub.nworkers > 0) __threadfence_system(); else __threadfence();
     const unsigned done = atomicAdd(&a.t_counter[1], 1u);
-    if (done == gridDim.x - 1) {
+    s_last = (done == gridDim.x - 1) ? 1u : 0u;
+    if (s_last) {
       a.t_counter[1] = 0;
-      if (!a.finalize) return;
       a.t_counter[0] = t;
       if (a.queue) a.queue[(t - 1) % (unsigned)a.qlen] = 0;
       if (a.global_step) *a.global_step = *a.global_step + 1;
+      if (a.local_step) *a.local_step = *a.local_step + 1;
       __threadfence_system();
       if (a.version_flag) st_release_sys_u32(a.version_flag, t);
+    }
+  }
+  if (pub.nworkers > 0) {
+    __syncthreads();
+    // one thread per worker: the release stores' round trips overlap
+    if (s_last && (int)threadIdx.x < pub.nworkers) {
+      __threadfence_system();
+      st_release_sys_u32(pub.wver[threadIdx.x], t);
     }
   }
 }
@@ -318,10 +375,9 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
                        float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
                        float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                        unsigned* version_flag, unsigned* global_step, unsigned* queue, int qlen,
-                       const unsigned* shutdown, int slots_bf16, long long skip_begin, long long skip_end, int finalize,
-                       const unsigned* mask_ptr, void* stream) {
-  TFD_REQUIRE(n % 4 == 0 && skip_begin % 4 == 0 && skip_end % 4 == 0 && skip_begin <= skip_end && skip_end <= n,
-              "adam: arena length %lld / skip range [%lld,%lld) must be multiples of 4 and nested", n, skip_begin, skip_end);
+                       const unsigned* shutdown, int slots_bf16, const unsigned* mask_ptr, const tfd_pub_t* pubspec,
+                       void* stream) {
+  TFD_REQUIRE(n % 4 == 0, "adam: arena length %lld must be a multiple of 4", n);
   TFD_REQUIRE(num_pieces <= kMaxPieces, "adam: too many pieces (%d)", num_pieces);
   TFD_REQUIRE(num_slots >= 1, "adam: need at least one gradient slot");
   PieceTable pt;
@@ -329,23 +385,38 @@ static int adam_launch(float* w, float* m, float* v, void* shadow, const float* 
   for (int i = 0; i < num_pieces; ++i) pt.p[i] = pieces[i];
   TFD_REQUIRE(num_slots <= TFD_MAX_SLOTS, "adam: at most %d gradient slots", TFD_MAX_SLOTS);
   AdamArgs a;
+  memset(&a, 0, sizeof(a));
   a.w = w; a.m = m; a.v = v; a.shadow = static_cast<bf16*>(shadow);
   for (int i = 0; i < TFD_MAX_SLOTS; ++i) a.slots[i] = i < num_slots ? slots[i] : nullptr;
   a.num_slots = num_slots; a.scale = scale; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
   a.t_counter = t_counter; a.wait_counter = wait_counter; a.version_flag = version_flag; a.global_step = global_step;
   a.queue = queue; a.qlen = qlen; a.shutdown = shutdown; a.slots_bf16 = slots_bf16;
-  a.skip_begin = skip_begin; a.skip_end = skip_end; a.finalize = finalize; a.mask_ptr = mask_ptr;
-  long long blocks = ((n - (skip_end - skip_begin)) / 8 + 255) / 256;
+  a.mask_ptr = mask_ptr;
+  PubTable pub;
+  memset(&pub, 0, sizeof(pub));
+  for (int i = 0; i < kMaxPieces; ++i) pub.pc[i].f32_off = pub.pc[i].b16_off = -1;
+  if (pubspec) {
+    TFD_REQUIRE(pubspec->nworkers >= 0 && pubspec->nworkers <= TFD_MAX_SLOTS && pubspec->n_signal >= 0 &&
+                    pubspec->n_signal <= TFD_MAX_SEG,
+                "adam: publish spec with %d workers / %d signals", pubspec->nworkers, pubspec->n_signal);
+    pub.nworkers = pubspec->nworkers;
+    for (int i = 0; i < pubspec->nworkers; ++i) {
+      pub.base[i] = static_cast<unsigned char*>(pubspec->worker_base[i]);
+      pub.wver[i] = pubspec->worker_version[i];
+    }
+    for (int i = 0; i < num_pieces && pubspec->pieces; ++i) {
+      pub.pc[i].f32_off = pubspec->pieces[i].f32_off;
+      pub.pc[i].b16_off = pubspec->pieces[i].b16_off;
+      pub.pc[i].ld16 = pubspec->pieces[i].ld16;
+    }
+    a.n_signal = pubspec->n_signal;
+    for (int i = 0; i < pubspec->n_signal; ++i) a.signal_arrive[i] = pubspec->signal_arrive[i];
+    a.local_step = pubspec->local_step;
+  }
+  long long blocks = (n / 8 + 255) / 256;
   if (blocks < 1) blocks = 1;
-  // finalize == 0: the early launch runs next to tcgen05 kernels; two blocks per SM leave them the registers
-  static const long long early_cap = [] {
-    const char* e = getenv("TFD_EARLY_ADAM_BLOCKS");  // tuning knob: how many SM slots the overlapped pass may take
-    const long long v = e ? atoll(e) : 0;
-    return v > 0 ? v : 148LL * 2;
-  }();
-  const long long cap = finalize ? 148 * 3 : early_cap;
-  if (blocks > cap) blocks = cap;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
-  TFD_CUDA_CHECK(tfd_launch(adam_apply_kernel, dim3((unsigned)blocks), dim3(256), 0, ST(stream), a, pt));
+  if (blocks > 148 * 3) blocks = 148 * 3;  // one resident wave (80 registers -> 3 blocks of 256 per SM)
+  TFD_CUDA_CHECK(tfd_launch(adam_apply_kernel, dim3((unsigned)blocks), dim3(256), 0, ST(stream), a, pt, pub));
   TFD_LAUNCH_CHECK();
   return 0;
 }
@@ -355,21 +426,58 @@ extern "C" int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const 
                               float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, 0, 0, 1, nullptr, stream);
+                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, nullptr, nullptr,
+                     stream);
 }
 
-/* Partial form: update only part of the arena now and the rest later in the same step, so the Adam pass over a big
- * tensor can start as soon as ITS gradient is complete and run under the rest of the backward pass.
- *   early launch:  base pointers offset to the tensor, n = its length, finalize = 0   (uses t+1, publishes nothing)
- *   last launch:   whole arena, [skip_begin, skip_end) = the range already done, finalize = 1 */
-extern "C" int tfd_adam_apply_part(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
-                                   float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr,
-                                   float beta1, float beta2, float eps, unsigned* t_counter,
-                                   const unsigned* wait_counter, unsigned* version_flag, unsigned* global_step,
-                                   long long skip_begin, long long skip_end, int finalize, void* stream) {
+// tfd_adam_apply for a strict-sync ps/worker cluster: on top of the update, the kernel (a) sends this rank's own
+// "gradients delivered" signals before it waits (colocated ranks), (b) stores the new values of the small variables
+// into every worker's mirror and (c) releases every worker's LOCAL version word -- see tfd_pub_t in the header.
+extern "C" int tfd_adam_apply_pub(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
+                                  float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr,
+                                  float beta1, float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
+                                  unsigned* version_flag, unsigned* global_step, const tfd_pub_t* pub, void* stream) {
   return adam_launch(w, m, v, shadow, slots, num_slots, scale, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, skip_begin,
-                     skip_end, finalize, nullptr, stream);
+                     wait_counter, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, nullptr, pub, stream);
+}
+
+// Worker-side signal of the same protocol when the worker GPU hosts no shard (dedicated ps GPUs): one tiny block adds 1
+// (release, system scope) to every shard's arrival counter and advances the worker's step word.
+__global__ void signal_kernel(const __grid_constant__ PushTable t, unsigned* local_step) {
+  grid_dep_wait();
+  if ((int)threadIdx.x < t.narrive) {
+    __threadfence_system();
+    red_add_release_sys_u32(t.arrive[threadIdx.x], 1u);
+  }
+  if (threadIdx.x == 0 && local_step) *local_step = *local_step + 1;
+}
+
+extern "C" int tfd_signal_arrive(unsigned* const* arrive, int narrive, unsigned* local_step, void* stream) {
+  TFD_REQUIRE(narrive >= 1 && narrive <= kMaxSegs, "signal: bad shard count %d", narrive);
+  PushTable t;
+  memset(&t, 0, sizeof(t));
+  t.narrive = narrive;
+  for (int i = 0; i < narrive; ++i) t.arrive[i] = arrive[i];
+  TFD_CUDA_CHECK(tfd_launch(signal_kernel, dim3(1), dim3(32), 0, ST(stream), t, local_step));
+  TFD_LAUNCH_CHECK();
+  return 0;
+}
+
+// Stand-alone wait on a list of (local) version words: the MLP's step has no conv1 to fold the wait into.
+__global__ void gate_kernel(const __grid_constant__ PullTable t, const unsigned* want_ptr) {
+  grid_dep_wait();
+  if ((int)threadIdx.x < t.nseg) spin_until_ge(t.seg[threadIdx.x].version, *want_ptr, "gate: parameter version");
+}
+
+extern "C" int tfd_gate_flags(const unsigned* const* flags, int n, const unsigned* want_ptr, void* stream) {
+  TFD_REQUIRE(n >= 1 && n <= kMaxSegs && want_ptr, "gate: bad flag count %d", n);
+  PullTable t;
+  memset(&t, 0, sizeof(t));
+  t.nseg = n;
+  for (int i = 0; i < n; ++i) t.seg[i].version = flags[i];
+  TFD_CUDA_CHECK(tfd_launch(gate_kernel, dim3(1), dim3(32), 0, ST(stream), t, want_ptr));
+  TFD_LAUNCH_CHECK();
+  return 0;
 }
 
 // Backup workers (replicas_to_aggregate R < workers N; m:62-65, SyncReplicasOptimizer's stale-gradient drop): every
@@ -407,7 +515,7 @@ extern "C" int tfd_adam_apply_backup(float* w, float* m, float* v, void* shadow,
   decide_kernel<<<1, 32, 0, ST(stream)>>>(stamps, num_slots, replicas_to_aggregate, t_counter, mask_word, shutdown);
   TFD_LAUNCH_CHECK();
   return adam_launch(w, m, v, shadow, slots, num_slots, 1.0f, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     nullptr, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, 0, 0, 1, mask_word, stream);
+                     nullptr, version_flag, global_step, nullptr, 0, nullptr, g_next_slots_bf16, mask_word, nullptr, stream);
 }
 
 extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
@@ -416,7 +524,7 @@ extern "C" int tfd_adam_serve(float* w, float* m, float* v, void* shadow, const 
                               unsigned* version_flag, unsigned* global_step, void* stream) {
   TFD_REQUIRE(queue != nullptr && qlen >= num_slots, "adam_serve: ring of %d cells cannot hold %d workers", qlen, num_slots);
   return adam_launch(w, m, v, shadow, slots, num_slots, 1.0f, n, pieces, num_pieces, lr, beta1, beta2, eps, t_counter,
-                     nullptr, version_flag, global_step, queue, qlen, shutdown, g_next_slots_bf16, 0, 0, 1, nullptr, stream);
+                     nullptr, version_flag, global_step, queue, qlen, shutdown, g_next_slots_bf16, nullptr, nullptr, stream);
 }
 
 /* Multi-segment push: segs[i] = {src, dst, n}; after every segment is written the last block adds 1 to each

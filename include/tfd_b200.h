@@ -210,14 +210,41 @@ int tfd_adam_apply(float* w, float* m, float* v, void* shadow, const float* cons
                    float eps, unsigned* t_counter, const unsigned* wait_counter, unsigned* version_flag,
                    unsigned* global_step, void* stream);
 
-/* tfd_adam_apply in two launches per step: an early one over one big tensor (finalize = 0; pass w/m/v/slots already
- * offset to the tensor, pieces with arena_off relative to that base) and a last one over the whole arena that skips
- * [skip_begin, skip_end) and finalises (bumps t / global_step, publishes the version). */
-int tfd_adam_apply_part(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots,
-                        float scale, long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1,
-                        float beta2, float eps, unsigned* t_counter, const unsigned* wait_counter,
-                        unsigned* version_flag, unsigned* global_step, long long skip_begin, long long skip_end,
-                        int finalize, void* stream);
+/* ---- strict-sync cluster step without stand-alone rendezvous kernels ----
+ * The reference's workers block in a token dequeue after pushing their gradients (m:279-299).  Here the hand-off is
+ * folded into kernels that run anyway.  Every worker owns, in its own peer-mapped heap, a mirror of the small
+ * variables and one version word per shard.  tfd_adam_apply_pub is tfd_adam_apply plus:
+ *   signal_arrive[n_signal]: block 0 first adds 1 (release, system scope) to these arrival counters -- the signal of
+ *       the worker that lives on the same GPU as this shard (its gradient kernels ran earlier in this stream and
+ *       stored straight into the owners' slots); local_step (optional) is that worker's step word, advanced at the end;
+ *   pieces[i] (parallel to the tfd_piece_t array): where variable i's values go inside EVERY worker's heap
+ *       (byte offsets; fp32 mirror and/or bf16 mirror; -1 = not mirrored; mirrors are padded to 16 bytes);
+ *   worker_base[nworkers] / worker_version[nworkers]: heap base and this shard's version word of every worker.
+ * After the update the last block stores version = t into every worker_version word (release): the worker's next
+ * step polls LOCAL memory (tfd_conv1_fwd gate list / tfd_gate_flags / the GEMM's wait_flags). */
+typedef struct {
+  long long f32_off;
+  long long b16_off;
+  int ld16;
+  int pad;
+} tfd_pub_piece_t;
+typedef struct {
+  const tfd_pub_piece_t* pieces;              /* num_pieces entries, or NULL                       */
+  void* worker_base[8];                       /* TFD_MAX_SLOTS                                     */
+  unsigned* worker_version[8];
+  int nworkers;
+  int n_signal;
+  unsigned* signal_arrive[8];                 /* TFD_MAX_SEG                                       */
+  unsigned* local_step;
+} tfd_pub_t;
+int tfd_adam_apply_pub(float* w, float* m, float* v, void* shadow, const float* const* slots, int num_slots, float scale,
+                       long long n, const tfd_piece_t* pieces, int num_pieces, float lr, float beta1, float beta2,
+                       float eps, unsigned* t_counter, const unsigned* wait_counter, unsigned* version_flag,
+                       unsigned* global_step, const tfd_pub_t* pub, void* stream);
+/* The same signal from a worker GPU that hosts no shard (dedicated ps GPUs): one tiny block. */
+int tfd_signal_arrive(unsigned* const* arrive, int narrive, unsigned* local_step, void* stream);
+/* Stand-alone wait until every (local) flag has reached *want_ptr (the MLP step has no conv1 to fold it into). */
+int tfd_gate_flags(const unsigned* const* flags, int n, const unsigned* want_ptr, void* stream);
 
 /* Storage type of the gradient staging slots used by tfd_adam_apply / tfd_adam_serve / tfd_push_multi[_async] from
  * now on in this process: 0 = fp32 (default), 1 = bf16 (halves the bytes a push moves over NVLink; the shard still

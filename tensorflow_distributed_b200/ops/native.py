@@ -34,6 +34,34 @@ class Piece(ctypes.Structure):
                 ("shadow_off", c_longlong)]
 
 
+class PubPiece(ctypes.Structure):
+    """tfd_pub_piece_t: where a variable's new values go inside every worker's heap (byte offsets, -1 = not mirrored)."""
+    _fields_ = [("f32_off", c_longlong), ("b16_off", c_longlong), ("ld16", c_int), ("pad", c_int)]
+
+
+class PubSpec(ctypes.Structure):
+    """tfd_pub_t: publish / signal spec of tfd_adam_apply_pub (strict-sync cluster step without rendezvous kernels)."""
+    _fields_ = [("pieces", ctypes.POINTER(PubPiece)), ("worker_base", c_void_p * 8), ("worker_version", c_void_p * 8),
+                ("nworkers", c_int), ("n_signal", c_int), ("signal_arrive", c_void_p * 8), ("local_step", c_void_p)]
+
+
+def make_pub(pieces, worker_bases, worker_versions, signal_arrive=(), local_step=None) -> PubSpec:
+    """pieces: list of (f32_off, b16_off, ld16) parallel to the shard's Piece list.  The returned struct keeps the
+    piece array alive through an attribute."""
+    spec = PubSpec()
+    arr = (PubPiece * max(1, len(pieces)))(*[PubPiece(int(a), int(b), int(c), 0) for a, b, c in pieces])
+    spec._keep = arr
+    spec.pieces = ctypes.cast(arr, ctypes.POINTER(PubPiece))
+    spec.nworkers = len(worker_bases)
+    for i, (b, v) in enumerate(zip(worker_bases, worker_versions)):
+        spec.worker_base[i], spec.worker_version[i] = int(b), int(v)
+    spec.n_signal = len(signal_arrive)
+    for i, a in enumerate(signal_arrive):
+        spec.signal_arrive[i] = int(a)
+    spec.local_step = int(local_step) if local_step else None
+    return spec
+
+
 class NvlsPiece(ctypes.Structure):
     """tfd_nvls_piece_t: the rows of one variable a shard owns, with their places in the symmetric arenas."""
     _fields_ = [("owner_off", c_longlong), ("numel", c_longlong), ("cols", c_int), ("ld_shadow", c_int),
@@ -280,26 +308,33 @@ def colsum_bf16(x, ld: int, rows: int, cols: int, out) -> None:
 
 def adam_apply(w, m, v, shadow, slots_dev, num_slots: int, scale: float, n: int, pieces, lr: float, t_counter,
                wait_counter=None, version_flag=None, global_step=None, beta1: float = 0.9, beta2: float = 0.999,
-               eps: float = 1e-8) -> None:
+               eps: float = 1e-8, pub: Optional[PubSpec] = None) -> None:
     arr = (Piece * max(1, len(pieces)))(*pieces)
     slots = (c_void_p * num_slots)(*[c_void_p(int(x)) for x in slots_dev[:num_slots]])  # host array of device pointers
-    _check(lib().tfd_adam_apply(_p(w), _p(m), _p(v), _p(shadow), slots, c_int(num_slots), c_float(scale),
-                                c_longlong(n), arr, c_int(len(pieces)), c_float(lr), c_float(beta1), c_float(beta2),
-                                c_float(eps), _p(t_counter), _p(wait_counter), _p(version_flag), _p(global_step),
-                                _stream()), "tfd_adam_apply")
+    if pub is None:
+        _check(lib().tfd_adam_apply(_p(w), _p(m), _p(v), _p(shadow), slots, c_int(num_slots), c_float(scale),
+                                    c_longlong(n), arr, c_int(len(pieces)), c_float(lr), c_float(beta1), c_float(beta2),
+                                    c_float(eps), _p(t_counter), _p(wait_counter), _p(version_flag), _p(global_step),
+                                    _stream()), "tfd_adam_apply")
+    else:
+        _check(lib().tfd_adam_apply_pub(_p(w), _p(m), _p(v), _p(shadow), slots, c_int(num_slots), c_float(scale),
+                                        c_longlong(n), arr, c_int(len(pieces)), c_float(lr), c_float(beta1),
+                                        c_float(beta2), c_float(eps), _p(t_counter), _p(wait_counter), _p(version_flag),
+                                        _p(global_step), ctypes.byref(pub), _stream()), "tfd_adam_apply_pub")
     _count()
 
 
-def adam_apply_part(w, m, v, shadow, slots, num_slots: int, scale: float, n: int, pieces, lr: float, t_counter,
-                    skip_begin: int, skip_end: int, finalize: bool, wait_counter=None, version_flag=None,
-                    global_step=None, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8) -> None:
-    arr = (Piece * max(1, len(pieces)))(*pieces)
-    sl = (c_void_p * num_slots)(*[c_void_p(int(x)) for x in slots[:num_slots]])
-    _check(lib().tfd_adam_apply_part(_p(w), _p(m), _p(v), _p(shadow), sl, c_int(num_slots), c_float(scale), c_longlong(n),
-                                     arr, c_int(len(pieces)), c_float(lr), c_float(beta1), c_float(beta2), c_float(eps),
-                                     _p(t_counter), _p(wait_counter), _p(version_flag), _p(global_step),
-                                     c_longlong(skip_begin), c_longlong(skip_end), c_int(int(finalize)), _stream()),
-           "tfd_adam_apply_part")
+def signal_arrive(arrive, local_step=None) -> None:
+    """Worker without a shard on its GPU: add 1 (release) to every shard's arrival counter, advance the step word."""
+    A = (c_void_p * len(arrive))(*[c_void_p(int(x)) for x in arrive])
+    _check(lib().tfd_signal_arrive(A, c_int(len(arrive)), _p(local_step), _stream()), "tfd_signal_arrive")
+    _count()
+
+
+def gate_flags(flags, want_ptr) -> None:
+    """Wait (on the device) until every flag word has reached *want_ptr."""
+    F = (c_void_p * len(flags))(*[c_void_p(int(f) if isinstance(f, int) else f.data_ptr()) for f in flags])
+    _check(lib().tfd_gate_flags(F, c_int(len(flags)), _p(want_ptr), _stream()), "tfd_gate_flags")
     _count()
 
 

@@ -29,7 +29,7 @@ import torch
 import torch.distributed as dist
 
 from ..engine_native import (CTRL_ARRIVE, CTRL_GSTEP, CTRL_T, CTRL_VERSION, NativeEngine, ShardState, Workspace,
-                             needs_shadow, _pad8)
+                             needs_shadow, tc_operand, _pad8)
 from ..models.spec import ModelSpec
 from ..ops import native as nat
 from .placement import Placement
@@ -42,6 +42,8 @@ WCTRL_TAG_CUR, WCTRL_TAG_NEXT = 10, 11  # backup workers: tag of my last push / 
 CTRL_DONE = 56                     # async: shard 0 holds one 'worker finished' word per worker (56..63)
 WCTRL_MYTICKET = 48                # async: worker-local, one word per shard: version that serves my last push
 DIRECT_THRESHOLD = 1 << 18         # tensors at least this big are consumed in place over NVLink, never mirrored
+WCTRL_VER = 64                     # worker-local: version word of shard s at WCTRL_VER + s, stored by the owner shard
+CTRL_WORDS = 128
 
 
 @dataclass
@@ -89,19 +91,39 @@ def _al(n: int, a: int = 1024) -> int:
     return (n + a - 1) // a * a
 
 
+def direct_vars(spec: ModelSpec):
+    """Tensor-core weights big enough to be consumed in place over NVLink (fused pull / push), never mirrored."""
+    return {v.name for v in spec.variables if tc_operand(spec, v.name) and v.numel >= DIRECT_THRESHOLD}
+
+
 class HeapLayout:
-    """Byte offsets inside one rank's peer-mapped allocation.  Identical arithmetic on every rank."""
+    """Byte offsets inside one rank's peer-mapped allocation.  Identical arithmetic on every rank.
+
+    ``[ctrl | mirrors | w | m | v | shadow | slots]``.  The mirror region has the SAME offsets on every rank (it only
+    depends on the model): one fp32 mirror per small variable and, on the bf16 arm, a bf16 mirror of the small
+    tensor-core weights.  The owner shards store into the workers' mirrors from inside their Adam kernel."""
 
     def __init__(self, spec: ModelSpec, placement: Placement, shard: Optional[int], num_workers: int,
-                 grad_bytes: int = 4):
+                 grad_bytes: int = 4, precision: str = "bf16"):
         self.grad_bytes = grad_bytes
         off = 0
         self.ctrl = off; off += 1024
+        direct = direct_vars(spec)
+        self.mw: Dict[str, int] = {}
+        self.ms: Dict[str, int] = {}
+        for v in spec.variables:
+            if v.name in direct:
+                continue
+            self.mw[v.name] = off; off += _al((v.numel + 3) // 4 * 16, 256)
+            if needs_shadow(spec, v.name, precision):
+                rows = v.numel // v.cols
+                self.ms[v.name] = off; off += _al(rows * _pad8(v.cols) * 2 + 16, 256)
+        off = _al(off)
         self.n = self.shadow_n = 0
         self.w = self.m = self.v = self.shadow = self.slots = off
         if shard is not None:
             self.n = placement.shard_sizes[shard]
-            _, _, _, self.shadow_n = ShardState.layout(spec, placement, shard)
+            _, _, _, self.shadow_n = ShardState.layout(spec, placement, shard, precision)
             self.w = off; off += _al(self.n * 4)
             self.m = off; off += _al(self.n * 4)
             self.v = off; off += _al(self.n * 4)
@@ -126,7 +148,7 @@ class GpuClusterEngine(NativeEngine):
     def __init__(self, spec: ModelSpec, topo: Topology, rank: int, device, learning_rate: float = 0.01,
                  seed: int = 0, init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False,
                  async_mode: bool = False, pull_mode: str = "auto", prefetch_max_numel: int = 8 << 20,
-                 grad_dtype: str = "fp32", replicas_to_aggregate: int = 0):
+                 grad_dtype: str = "fp32", replicas_to_aggregate: int = 0, precision: Optional[str] = None):
         # backup workers: sync mode that aggregates only the first R of N gradients per update and drops stale ones
         self.R = replicas_to_aggregate if 0 < replicas_to_aggregate < topo.num_workers else topo.num_workers
         self.backup = (not async_mode) and self.R < topo.num_workers
@@ -145,10 +167,16 @@ class GpuClusterEngine(NativeEngine):
             # tickets unconditionally -- which is also the reference's topology (separate ps processes).
             raise ValueError("async replicas need dedicated ps GPUs (layout='dedicated')")
         self.async_mode = async_mode
+        # Strict sync with fp32 slots runs the protocol WITHOUT stand-alone rendezvous kernels: gradients are written
+        # straight into the owners' slots by the kernels that produce them, the arrival signal and the parameter
+        # publish live inside the shard's Adam kernel, and workers wait on version words in their own memory.
+        # Async, backup-worker and bf16-slot modes keep the pull / push kernels.
+        self.v2 = (not async_mode) and (not self.backup) and grad_dtype == "fp32"
         if not dist.is_initialized():
             raise RuntimeError("GpuClusterEngine needs torch.distributed (bootstrap only) to be initialised")
         nat.lib()
         self.spec, self.topo, self.rank = spec, topo, rank
+        self._set_precision(precision, conv2_ref)
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
         nat.set_device(self.device.index or 0)
@@ -164,8 +192,8 @@ class GpuClusterEngine(NativeEngine):
         self.num_workers = topo.num_workers
         S = topo.num_shards
         self.placement = Placement(spec, S)
-        self.layouts = [HeapLayout(spec, self.placement, topo.shard_of(r), topo.num_workers, self.grad_bytes)
-                        for r in range(topo.world)]
+        self.layouts = [HeapLayout(spec, self.placement, topo.shard_of(r), topo.num_workers, self.grad_bytes,
+                                   self.precision) for r in range(topo.world)]
         nat.set_slot_dtype(self.grad_dtype == "bf16")
         # ---- symmetric heap: allocate, exchange the 64-byte cudaIpc handles, map every ps rank's heap ----
         self.mc_base = 0  # multicast (NVLS) alias of the heap; only the experimental symmetric-memory heap has one
@@ -189,20 +217,21 @@ class GpuClusterEngine(NativeEngine):
             handles: List[Optional[bytes]] = [None] * topo.world
             dist.all_gather_object(handles, handle)
             self.peer_base = {rank: self.heap_ptr}
-            for r in topo.ps_ranks:
-                if r != rank:
+            for r in range(topo.world):  # every heap: workers read the shards', shards write the workers' mirrors
+                if r != rank and (r in topo.ps_ranks or (self.is_ps and self.v2)):
                     self.peer_base[r] = nat.ipc_open(handles[r])
                     self._opened.append(self.peer_base[r])
         L = self.layouts[rank]
-        self.ctrl = nat.tensor_from_ptr(self.heap_ptr + L.ctrl, 64, torch.int32, self.device)
+        self.ctrl = nat.tensor_from_ptr(self.heap_ptr + L.ctrl, CTRL_WORDS, torch.int32, self.device)
         # ---- ps role ----
         self.shard = None
-        self._shard_layouts = [ShardState.layout(spec, self.placement, s) for s in range(S)]
+        self._shard_layouts = [ShardState.layout(spec, self.placement, s, self.precision) for s in range(S)]
         if self.is_ps:
             offs = {"w": L.w, "m": L.m, "v": L.v, "shadow": L.shadow, "ctrl": L.ctrl}
             self.shard = ShardState(spec, self.placement, self.my_shard, self.device,
                                     alloc=lambda name, numel, dtype: nat.tensor_from_ptr(
-                                        self.heap_ptr + offs[name], numel, dtype, self.device))
+                                        self.heap_ptr + offs[name], numel, dtype, self.device),
+                                    precision=self.precision)
             self.slot_ptrs = [self.heap_ptr + L.slot(w) for w in range(topo.num_workers)]
             self.shard.init_variables(seed, init_stddev)
         # ---- worker role ----
@@ -213,13 +242,15 @@ class GpuClusterEngine(NativeEngine):
         # takes two latency-bound NVLink reads off the critical path (2 GPUs: 154.9 vs 157.7 us/step;
         # 1 ps + 7 workers: 222 vs 317 us/step).  "auto" therefore prefetches matrices up to prefetch_max_numel
         # elements and fuses the pull of everything bigger; "fused" / "prefetch" force one strategy.
-        self.direct = {v.name for v in spec.variables if needs_shadow(spec, v.name) and v.numel >= DIRECT_THRESHOLD}
+        self.direct = direct_vars(spec)
         self.prefetched = {n for n in self.direct
                            if pull_mode in ("prefetch", "auto") and spec.by_name()[n].numel <= prefetch_max_numel}
         if self.is_worker:
             self._build_worker_tables()
+        self._pub = self._build_pub() if (self.is_ps and self.v2) else None
         torch.cuda.synchronize(self.device)
         dist.barrier()  # X6: everybody waits until every shard has been initialised
+        self._publish_host(0)
 
     # ---- addressing helpers ----------------------------------------------------------------
     def _ps_rank(self, shard: int) -> int:
@@ -233,66 +264,140 @@ class GpuClusterEngine(NativeEngine):
         r = self._ps_rank(shard)
         return self.peer_base[r] + self.layouts[r].w + 4 * elem_off
 
-    def _shadow_ptr(self, shard: int, var: str) -> int:
+    def _tc_ptr(self, shard: int, var: str) -> int:
+        """What the tensor cores read of `var` on its owner shard: the bf16 shadow, or (tf32 arm) the fp32 master."""
         r = self._ps_rank(shard)
+        if self.tf32:
+            (p,) = [q for q in self.placement.pieces[var] if q.shard == shard]
+            return self.peer_base[r] + self.layouts[r].w + 4 * p.offset
         return self.peer_base[r] + self.layouts[r].shadow + 2 * self._shard_layouts[shard][1][var]
+
+    def _tc_ld(self, cols: int) -> int:
+        return cols if self.tf32 else _pad8(cols)
 
     def _slot_ptr(self, shard: int, elem_off: int) -> int:
         r = self._ps_rank(shard)
         return self.peer_base[r] + self.layouts[r].slot(self.my_worker) + self.grad_bytes * elem_off
 
+    def _wver_ptr(self, rank: int, shard: int) -> int:
+        """Version word of `shard` in the heap of worker rank `rank` (the owner stores it, the worker polls it)."""
+        return self.peer_base[rank] + self.layouts[rank].ctrl + 4 * (WCTRL_VER + shard)
+
     def _build_worker_tables(self) -> None:
         dev = self.device
+        L = self.layouts[self.rank]
+        S = self.topo.num_shards
+        tcdt = torch.float32 if self.tf32 else torch.bfloat16
+        esz = 4 if self.tf32 else 2
         self.mirror_w: Dict[str, torch.Tensor] = {}
         self.mirror_s: Dict[str, torch.Tensor] = {}
         self.local_g: Dict[str, torch.Tensor] = {}
         pull, push = [], []
         seen_shards = set()
+        # version word a consumer waits on for shard s: v2 -- my own copy, stored by the owner; legacy -- the owner's
+        ver_of = (lambda s: self._wver_ptr(self.rank, s)) if self.v2 else (lambda s: self._ctrl_ptr(s, CTRL_VERSION))
+        self._gate = [self._wver_ptr(self.rank, s) for s in range(S)]
         for v in self.spec.variables:
             if v.name in self.direct:
                 continue
             (p,) = self.placement.pieces[v.name]  # small tensors live whole on one shard
             rows, cols = p.row_end - p.row_start, p.cols
+            if self.v2:
+                # parameters: mirror inside my heap, written by the owner's Adam kernel.  gradients: the kernels write
+                # straight into my slot on the owner GPU (a torch view over peer-mapped memory)
+                self.mirror_w[v.name] = nat.tensor_from_ptr(self.heap_ptr + L.mw[v.name], p.numel, torch.float32,
+                                                            dev).view(rows, cols)
+                self.local_g[v.name] = nat.tensor_from_ptr(self._slot_ptr(p.shard, p.offset), p.numel, torch.float32,
+                                                           dev).view(rows, cols)
+                if needs_shadow(self.spec, v.name, self.precision):
+                    ld = _pad8(cols)
+                    self.mirror_s[v.name] = nat.tensor_from_ptr(self.heap_ptr + L.ms[v.name], rows * ld, torch.bfloat16,
+                                                                dev).view(rows, ld)
+                continue
             self.mirror_w[v.name] = torch.zeros(rows, cols, dtype=torch.float32, device=dev)
             self.local_g[v.name] = torch.zeros(rows, cols, dtype=torch.float32, device=dev)
-            ver = self._ctrl_ptr(p.shard, CTRL_VERSION)
+            ver = ver_of(p.shard)
             pull.append((self._w_ptr(p.shard, p.offset), self.mirror_w[v.name].data_ptr(), p.numel, ver, p.shard))
             push.append((self.local_g[v.name].data_ptr(), self._slot_ptr(p.shard, p.offset), p.numel))
             seen_shards.add(p.shard)
-            if needs_shadow(self.spec, v.name):
+            if needs_shadow(self.spec, v.name, self.precision):
                 ld = _pad8(cols)
                 self.mirror_s[v.name] = torch.zeros(rows, ld, dtype=torch.bfloat16, device=dev)
-                pull.append((self._shadow_ptr(p.shard, v.name), self.mirror_s[v.name].data_ptr(), rows * ld // 2, ver, p.shard))
-        for s in range(self.topo.num_shards):  # wait for EVERY shard's version (its slots are then free again)
-            if s not in seen_shards:
-                pull.append((self._w_ptr(s, 0), self.ctrl.data_ptr() + 4 * 60, 0, self._ctrl_ptr(s, CTRL_VERSION), s))
+                pull.append((self._tc_ptr(p.shard, v.name), self.mirror_s[v.name].data_ptr(), rows * ld // 2, ver, p.shard))
+        if not self.v2:
+            for s in range(S):  # wait for EVERY shard's version (its slots are then free again)
+                if s not in seen_shards:
+                    pull.append((self._w_ptr(s, 0), self.ctrl.data_ptr() + 4 * 60, 0, ver_of(s), s))
         self._pull, self._push = pull, push
-        self._arrive = [self._ctrl_ptr(s, CTRL_ARRIVE) for s in range(self.topo.num_shards)]
+        self._arrive = [self._ctrl_ptr(s, CTRL_ARRIVE) for s in range(S)]
         # per direct variable: shard pieces in row order
         self._direct_info = {}
         self._prefetch = []
         for name in self.direct:
             pcs = sorted(self.placement.pieces[name], key=lambda q: q.row_start)
+            ld = self._tc_ld(pcs[0].cols)
             if name in self.prefetched:
-                ld = _pad8(pcs[0].cols)
-                self.mirror_s[name] = torch.zeros(pcs[-1].row_end, ld, dtype=torch.bfloat16, device=dev)
+                self.mirror_s[name] = torch.zeros(pcs[-1].row_end, ld, dtype=tcdt, device=dev)
                 for q in pcs:
-                    self._prefetch.append((self._shadow_ptr(q.shard, name),
-                                           self.mirror_s[name].data_ptr() + 2 * q.row_start * ld,
-                                           (q.row_end - q.row_start) * ld // 2, self._ctrl_ptr(q.shard, CTRL_VERSION),
-                                           q.shard))
+                    self._prefetch.append((self._tc_ptr(q.shard, name),
+                                           self.mirror_s[name].data_ptr() + esz * q.row_start * ld,
+                                           (q.row_end - q.row_start) * ld * esz // 4, ver_of(q.shard), q.shard))
             self._direct_info[name] = {
-                "rows": [q.row_start for q in pcs] + [pcs[-1].row_end], "cols": pcs[0].cols, "ld": _pad8(pcs[0].cols),
-                "shadow": [self._shadow_ptr(q.shard, name) for q in pcs],
+                "rows": [q.row_start for q in pcs] + [pcs[-1].row_end], "cols": pcs[0].cols, "ld": ld,
+                "shadow": [self._tc_ptr(q.shard, name) for q in pcs],
                 "slot": [self._slot_ptr(q.shard, q.offset) for q in pcs],
-                "ver": None if (self.async_mode or self.backup) else [self._ctrl_ptr(q.shard, CTRL_VERSION) for q in pcs]}
+                "ver": None if (self.async_mode or self.backup) else [ver_of(q.shard) for q in pcs]}
+
+    def _build_pub(self):
+        """What my shard's Adam kernel publishes: the new values of every small variable I own go into EVERY worker's
+        mirror (same offsets in every heap), then every worker's version word for my shard is released; on a
+        colocated rank the kernel also sends this rank's own arrival signals first."""
+        L = self.layouts[self.rank]
+        pieces = []
+        for p in self.placement.shard_pieces(self.my_shard):
+            if p.var in self.direct:
+                pieces.append((-1, -1, 0))
+            else:
+                pieces.append((L.mw[p.var], L.ms.get(p.var, -1), _pad8(p.cols)))
+        wr = self.topo.worker_ranks
+        return nat.make_pub(pieces, [self.peer_base[r] for r in wr], [self._wver_ptr(r, self.my_shard) for r in wr],
+                            signal_arrive=self._arrive if self.is_worker else (),
+                            local_step=(self.ctrl.data_ptr() + 4 * WCTRL_STEP) if self.is_worker else None)
+
+    def _publish_host(self, version: Optional[int] = None) -> None:
+        """Initialisation / restore: every shard copies its small variables into every worker's mirror and sets every
+        worker's version word for itself, from the host (steady state is done by the Adam kernel).  Collective."""
+        if not self.v2:
+            return
+        if self.is_ps:
+            s = self.shard
+            if version is None:
+                version = int(s.ctrl[CTRL_VERSION].item())
+            for r in self.topo.worker_ranks:
+                Lr = self.layouts[r]
+                for p in self.placement.shard_pieces(self.my_shard):
+                    if p.var in self.direct:
+                        continue
+                    nat.tensor_from_ptr(self.peer_base[r] + Lr.mw[p.var], p.numel, torch.float32, self.device).copy_(
+                        s.w[p.offset:p.offset + p.numel])
+                    if p.var in Lr.ms:
+                        rows, ld = p.row_end - p.row_start, _pad8(p.cols)
+                        nat.tensor_from_ptr(self.peer_base[r] + Lr.ms[p.var], rows * ld, torch.bfloat16,
+                                            self.device).copy_(s.shadow_view(p.var).reshape(-1))
+                nat.tensor_from_ptr(self._wver_ptr(r, self.my_shard), 1, torch.int32, self.device).fill_(int(version))
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
 
     # ---- parameter / gradient views used by the kernel sequences -----------------------------
     def P(self, name: str) -> torch.Tensor:
         return self.mirror_w[name]
 
     def S(self, name: str) -> torch.Tensor:
-        return self.mirror_s[name]
+        """What the tensor cores read locally: a bf16 mirror, a prefetched copy of a big matrix, or (tf32 arm, small
+        tensor-core weights such as wc2) the fp32 mirror itself."""
+        if name in self.mirror_s:
+            return self.mirror_s[name]
+        return self.mirror_w[name]
 
     def G(self, name: str) -> torch.Tensor:
         return self.local_g[name]
@@ -310,7 +415,7 @@ class GpuClusterEngine(NativeEngine):
         nat.gemm_bf16_seg(A, 0, d["shadow"], 1, M, d["cols"], d["rows"][-1], out, mode=mode, lda=A.stride(0),
                           ldb=d["ld"], ld_out=ld_out if ld_out is not None else out.stride(0), seg_mode=nat.SEG_B_K,
                           seg_rows=d["rows"], wait_flags=d["ver"], wait_value_ptr=self.step_ptr(), bn=bn,
-                          splits=splits, split_stride=split_stride, bias=bias)
+                          splits=splits, split_stride=split_stride, bias=bias, tf32=self.tf32)
 
     def gemm_dgrad(self, wname, dY, M, out, *, mode, bn, splits=1, split_stride=0, relu_mask=None, ld_out=None):
         if wname in self.prefetched:
@@ -323,17 +428,7 @@ class GpuClusterEngine(NativeEngine):
                           ldb=d["ld"], ld_out=ld_out if ld_out is not None else out.stride(0), seg_mode=nat.SEG_B_N,
                           seg_rows=d["rows"], wait_flags=d["ver"], wait_value_ptr=self.step_ptr(), bn=bn,
                           splits=splits, split_stride=split_stride, relu_mask=relu_mask,
-                          ld_mask=relu_mask.stride(0) if relu_mask is not None else 0)
-
-    def gemm_dgrad_pool2(self, ws) -> None:
-        name = "weights/wd1"
-        if name in self.prefetched or name not in self.direct:
-            if name in self.prefetched:
-                self._join_prefetch()
-            return super().gemm_dgrad_pool2(ws)
-        d = self._direct_info[name]
-        nat.gemm_dgrad_pool2(ws.dhid, d["shadow"], d["ld"], ws.B, ws.pool2, ws.am2, ws.dy2, self.G("biases/bc2"),
-                             seg_rows=d["rows"], wait_flags=d["ver"], wait_value_ptr=self.step_ptr())
+                          ld_mask=relu_mask.stride(0) if relu_mask is not None else 0, tf32=self.tf32)
 
     def gemm_wgrad(self, wname, X, dY, Bsz, *, bn):
         if wname not in self.direct:
@@ -343,44 +438,29 @@ class GpuClusterEngine(NativeEngine):
         nat.gemm_bf16_seg(X, 1, [dY.data_ptr()] + [0] * (nseg - 1), 1, d["rows"][-1], d["cols"], Bsz, None,
                           mode=nat.EPI_STORE_BF16 if self.grad_dtype == "bf16" else nat.EPI_STORE_F32, lda=X.stride(0),
                           ldb=dY.stride(0), ld_out=d["cols"], seg_mode=nat.SEG_OUT_M, seg_rows=d["rows"],
-                          out_ptrs=d["slot"], bn=bn)
+                          out_ptrs=d["slot"], bn=bn, tf32=self.tf32)
 
     # ---- step pieces -----------------------------------------------------------------------
-    @property
-    def fold_pull(self) -> bool:
-        """CNN, plain sync mode: conv1 reads its filter/bias straight from the owner shards (gated on their version
-        flags inside the kernel) and the copy of the other small tensors runs next to it on a side branch, joined
-        before conv2 -- instead of a pull kernel in front of the whole step.  TFD_FOLD_PULL=1 turns it on."""
-        return (self.spec.kind == "cnn" and not self.async_mode and not self.backup
-                and os.environ.get("TFD_FOLD_PULL", "0") == "1")
-
-    def conv1_fwd(self, ws) -> None:
-        if not self.fold_pull:
-            return super().conv1_fwd(ws)
-        (pw,), (pb,) = self.placement.pieces["weights/wc1"], self.placement.pieces["biases/bc1"]
-        nat.conv1_fwd_gated(ws.x, self._w_ptr(pw.shard, pw.offset), self._w_ptr(pb.shard, pb.offset), ws.pool1, ws.am1,
-                            ws.B, self._ctrl_ptr(pw.shard, CTRL_VERSION), self._ctrl_ptr(pb.shard, CTRL_VERSION),
-                            self.step_ptr())
-        if getattr(self, "_sp_pending", False):  # everything after conv1 reads the mirrors
-            torch.cuda.current_stream().wait_stream(self._sp_stream)
-            self._sp_pending = False
+    def conv1_fwd(self, ws, training: bool = True) -> None:
+        if not self.v2:
+            return super().conv1_fwd(ws, training)
+        # the step's first kernel waits -- on version words in THIS GPU's memory -- until every shard has applied the
+        # update this step builds on (which also means my slots have been consumed and may be overwritten)
+        nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, ws.B, tf32=self.tf32,
+                      gate_flags=self._gate, want_ptr=self.step_ptr())
 
     def _pre_step(self, ws, training: bool) -> None:
-        """Pull (X1): small tensors are copied once the owning shard's version has caught up with this
-        worker's step counter; the same kernel thereby waits for every shard (slots are free to overwrite)."""
+        """Pull (X1).  v2: nothing to copy -- the owners have already stored the small parameters into my mirror; only
+        the wait remains, folded into conv1 (CNN) or a one-block gate kernel (MLP).  Legacy modes: small tensors are
+        copied once the owning shard's version has caught up with this worker's step counter; the same kernel thereby
+        waits for every shard (slots are free to overwrite)."""
         if self._prefetch:
             self._launch_prefetch(training)
-        p = self._pull
-        if self.fold_pull:
-            main = torch.cuda.current_stream()
-            if not hasattr(self, "_sp_stream"):
-                self._sp_stream = torch.cuda.Stream(device=self.device)
-            self._sp_stream.wait_stream(main)
-            with torch.cuda.stream(self._sp_stream):
-                nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
-                               want_ptr=self.step_ptr())
-            self._sp_pending = True
+        if self.v2:
+            if self.spec.kind != "cnn":
+                nat.gate_flags(self._gate, self.step_ptr())
             return
+        p = self._pull
         if self.backup and not training:
             # evaluation after training: my last push may carry a tag the ps will never apply (it has already done
             # its train_steps updates), so read whatever is published now
@@ -427,7 +507,13 @@ class GpuClusterEngine(NativeEngine):
             self._pf_pending = False
 
     def _post_backward(self, ws) -> None:
-        """Push (X2): small gradients into this worker's slots, then arrive += 1 on every shard."""
+        """Push (X2): small gradients into this worker's slots, then arrive += 1 on every shard.  v2: the gradient
+        kernels have already written the slots; a colocated rank signals from inside its Adam kernel, a worker on a
+        GPU without a shard with one tiny block."""
+        if self.v2:
+            if not self.is_ps:
+                nat.signal_arrive(self._arrive, self.ctrl[WCTRL_STEP:])
+            return
         p = self._push
         if self.backup:
             S = self.topo.num_shards
@@ -452,18 +538,18 @@ class GpuClusterEngine(NativeEngine):
             return
         s = self.shard
         if self.backup:  # first R of N gradients stamped for this update, averaged; stale stamps never match
-            nat.adam_apply_backup(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, self.R, s.n, s.pieces,
+            nat.adam_apply_backup(s.w, s.m, s.v, None if self.tf32 else s.shadow, self.slot_ptrs, self.num_workers, self.R, s.n, s.pieces,
                                   self.lr, s.ctrl[CTRL_T:], s.ctrl[CTRL_STAMP:], s.ctrl[CTRL_MASK:],
                                   s.ctrl[CTRL_SHUTDOWN:], s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:])
             return
         if self.async_mode:  # one arriving gradient, in ticket order, scale 1 (apply-on-arrival)
-            nat.adam_serve(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, s.n, s.pieces, self.lr,
+            nat.adam_serve(s.w, s.m, s.v, None if self.tf32 else s.shadow, self.slot_ptrs, self.num_workers, s.n, s.pieces, self.lr,
                            s.ctrl[CTRL_T:], s.ctrl[CTRL_RING:], RING_LEN, s.ctrl[CTRL_SHUTDOWN:], s.ctrl[CTRL_VERSION:],
                            s.ctrl[CTRL_GSTEP:])
             return
-        nat.adam_apply(s.w, s.m, s.v, s.shadow, self.slot_ptrs, self.num_workers, 1.0 / self.num_workers, s.n,
-                       s.pieces, self.lr, s.ctrl[CTRL_T:], s.ctrl[CTRL_ARRIVE:], s.ctrl[CTRL_VERSION:],
-                       s.ctrl[CTRL_GSTEP:])
+        nat.adam_apply(s.w, s.m, s.v, None if self.tf32 else s.shadow, self.slot_ptrs, self.num_workers,
+                       1.0 / self.num_workers, s.n, s.pieces, self.lr, s.ctrl[CTRL_T:], s.ctrl[CTRL_ARRIVE:],
+                       s.ctrl[CTRL_VERSION:], s.ctrl[CTRL_GSTEP:], pub=self._pub)
 
     def _sequence(self, ws, mode: str, keep_prob: float, mask_out=None) -> None:
         if self.is_worker:
@@ -475,7 +561,7 @@ class GpuClusterEngine(NativeEngine):
     # ---- public API ------------------------------------------------------------------------
     def workspace(self, B: int) -> Workspace:
         if B not in self.ws:
-            self.ws[B] = Workspace(self.spec, B if self.is_worker else 1, self.device)
+            self.ws[B] = Workspace(self.spec, B if self.is_worker else 1, self.device, self.precision)
             self.ws[B].B = B if self.is_worker else 1
         return self.ws[B]
 
@@ -489,7 +575,7 @@ class GpuClusterEngine(NativeEngine):
         return int(t.item())
 
     def describe(self) -> str:
-        return self.topo.describe() + (" async" if self.async_mode else " sync") + \
+        return self.topo.describe() + " " + self.precision + (" async" if self.async_mode else " sync") + \
             (" R=%d-of-%d" % (self.R, self.num_workers) if self.backup else "") + \
             (" bf16-grad-push" if self.grad_dtype == "bf16" else "")
 
@@ -546,6 +632,7 @@ class GpuClusterEngine(NativeEngine):
             s.publish_shadow()
         torch.cuda.synchronize(self.device)
         dist.barrier()
+        self._publish_host()
 
     def shutdown(self) -> None:
         torch.cuda.synchronize(self.device)
@@ -559,7 +646,7 @@ class GpuClusterEngine(NativeEngine):
         topo = Topology.make(world, a.layout, a.ps)
         return cls(spec, topo, rank, device, learning_rate=0.01, seed=0, init_stddev=a.init_stddev,
                    async_mode=getattr(a, "async_mode", False), pull_mode=getattr(a, "pull", "auto"),
-                   grad_dtype=getattr(a, "grad_dtype", "fp32"))
+                   grad_dtype=getattr(a, "grad_dtype", "fp32"), precision=getattr(a, "precision", None))
 
     # ---- restore / release helpers used by the cluster program -------------------------------
     def set_adam_state(self, sd: dict) -> None:
@@ -584,6 +671,7 @@ class GpuClusterEngine(NativeEngine):
             self.ctrl[WCTRL_STEP] = int(sd["t"])
         torch.cuda.synchronize(self.device)
         dist.barrier()
+        self._publish_host(int(sd["t"]))
 
     def set_global_step(self, step: int) -> None:
         if self.is_ps:
@@ -662,7 +750,7 @@ def _gpu_task(flags, topo: Topology, rank: int, device, mnist, log) -> dict:
     else:
         eng = GpuClusterEngine(spec, topo, rank, device, learning_rate=flags.learning_rate, seed=flags.seed,
                                init_stddev=flags.init_stddev, async_mode=not flags.sync_replicas,
-                               grad_dtype=flags.grad_dtype,
+                               grad_dtype=flags.grad_dtype, precision=flags.precision,
                                replicas_to_aggregate=R if topo.layout == "dedicated" else 0)
     if flags.log_device_placement and (is_chief or not is_worker):
         log(eng.placement.table())

@@ -100,6 +100,7 @@ class NvlsClusterEngine(NativeEngine):
         nat.lib()
         import torch.distributed._symmetric_memory as symm
         self.spec, self.topo, self.rank = spec, topo, rank
+        self._set_precision("bf16")  # the multicast transport publishes bf16 shadows; tf32 stays on the peer transport
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
         nat.set_device(self.device.index or 0)

@@ -22,26 +22,29 @@ needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_c
 
 
 @needs2
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
 @pytest.mark.parametrize("layout,model,pull", [("colocated", "cnn", "fused"), ("colocated", "cnn", "prefetch"),
                                                ("dedicated", "cnn", "auto"), ("colocated", "mlp", "fused"),
                                                ("colocated", "mlp", "prefetch")])
-def test_two_gpu_sync_ps(layout, model, pull):
-    out = _torchrun(2, ["--layout", layout, "--model", model, "--pull", pull], 29611)
-    assert "OK" in out and "FAIL" not in out
+def test_two_gpu_sync_ps(layout, model, pull, precision):
+    out = _torchrun(2, ["--layout", layout, "--model", model, "--pull", pull, "--precision", precision], 29611)
+    assert "OK" in out and "FAIL" not in out and precision in out
 
 
 @needs2
 def test_two_gpu_fused_pull_is_bit_identical_to_copy_then_gemm():
     """the pull-fused GEMM (weight tiles TMA-loaded from the owner GPUs inside the kernel) against
-    copy-then-unfused (the shadow copied to a local mirror first, same GEMM on local memory).  The MLP path has no
-    floating-point atomics, so after 12 synchronous steps parameters and Adam slots must agree bit for bit."""
+    copy-then-unfused (the weights copied to a local mirror first, same GEMM on local memory).  No kernel of either
+    model uses floating-point atomics, so after 12 synchronous steps parameters and Adam slots must agree bit for
+    bit -- for the MLP and for the CNN."""
     import re
-    digests = []
-    for pull in ("fused", "prefetch"):
-        out = _torchrun(2, ["--layout", "colocated", "--model", "mlp", "--pull", pull, "--digest"], 29617)
-        assert "OK" in out and "FAIL" not in out
-        digests.append(re.search(r"DIGEST ([0-9a-f]{64})", out).group(1))
-    assert digests[0] == digests[1]
+    for model in ("mlp", "cnn"):
+        digests = []
+        for pull in ("fused", "prefetch"):
+            out = _torchrun(2, ["--layout", "colocated", "--model", model, "--pull", pull, "--digest"], 29617)
+            assert "OK" in out and "FAIL" not in out
+            digests.append(re.search(r"DIGEST ([0-9a-f]{64})", out).group(1))
+        assert digests[0] == digests[1], model
 
 
 @needs2
