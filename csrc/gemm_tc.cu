@@ -516,8 +516,8 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
   TFD_REQUIRE(seg_mode != TFD_SEG_B_K || b_mn == 1, "gemm: TFD_SEG_B_K needs B stored [K,N]");
   TFD_REQUIRE(seg_mode != TFD_SEG_B_N || b_mn == 0, "gemm: TFD_SEG_B_N needs B stored [N,K]");
   TFD_REQUIRE(!tf || mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32 || mode == TFD_EPI_BIAS_RELU_F32 ||
-                  mode == TFD_EPI_RELUMASK_F32,
-              "gemm: tf32 operands go with fp32 outputs (epilogue %d writes bf16)", mode);
+                  mode == TFD_EPI_RELUMASK_F32 || mode == TFD_EPI_STORE_BF16,
+              "gemm: tf32 operands go with fp32 outputs or a plain bf16 store (bf16 gradient slots); epilogue %d", mode);
   TFD_REQUIRE(seg_mode != TFD_SEG_OUT_M || mode == TFD_EPI_STORE_F32 || mode == TFD_EPI_ATOMIC_F32 ||
                   mode == TFD_EPI_STORE_BF16,
               "gemm: TFD_SEG_OUT_M needs a plain store epilogue (fp32, fp32 atomic or bf16)");

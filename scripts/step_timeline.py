@@ -26,7 +26,8 @@ if world > 1:  # under torchrun: colocated ps shards, one rank per GPU; rank 0 p
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local))
     eng = GpuClusterEngine(SPEC, Topology.make(world, os.environ.get("TFD_LAYOUT", "colocated")), rank,
-                           "cuda:%d" % local, init_stddev=STD, pull_mode=os.environ.get("TFD_PULL", "auto"))
+                           "cuda:%d" % local, init_stddev=STD, pull_mode=os.environ.get("TFD_PULL", "auto"),
+                           precision=os.environ.get("TFD_PRECISION", "tf32"))
 else:
     eng = NativeEngine(SPEC, init_stddev=STD, precision=os.environ.get("TFD_PRECISION", "tf32"))
 rng = np.random.RandomState(rank)
