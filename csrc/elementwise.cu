@@ -158,30 +158,32 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
 }
 
 // conv1 filter gradient: pool/ReLU backward folded in (only the arg-max position of each 2x2 window carries
-// gradient).  One block of 32 warps per image: warp = pixel group, lane = channel, so a thread touches at most 7 of
-// the 196 pooled pixels and all its global loads are in flight at once (the kernel is load-latency bound: the
-// round-1 shape with 13 pixels per thread took 12 us).  dpool arrives as nsplit partial planes (the tf32 conv2 dgrad
+// gradient).  One block of 16 warps per image: warp = pixel group, lane = channel; a thread touches at most 13 of the
+// 196 pooled pixels and all its global loads are in flight at once.  512 threads x <= 64 registers and 31 KB of shared
+// memory leave room for a conv2 wgrad CTA (192 threads, ~194 KB) on the same SM: the two weight-gradient kernels of
+// the backward tail overlap instead of queueing (a 1024-thread shape owned the whole register file).  dpool arrives as nsplit partial planes (the tf32 conv2 dgrad
 // splits its K over two CTAs) that are added here in plane order.  Reduction without atomics: warps -> shared memory
 // in four fixed passes -> one partial [26][32] per image in `scratch` -> the last block to finish sums the images'
 // partials in a fixed order and writes dw / db (which may be staging slots on another GPU).
 // scratch = 16 counter words + B * 832 floats, zeroed once by the caller.
 template <typename T>
-__global__ void __launch_bounds__(1024) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
-                                                           int nsplit, long long split_stride, const T* __restrict__ pool,
-                                                           const unsigned char* __restrict__ amax, float* __restrict__ dw,
-                                                           float* __restrict__ db, float* __restrict__ scratch, int B) {
+__global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
+                                                          int nsplit, long long split_stride, const T* __restrict__ pool,
+                                                          const unsigned char* __restrict__ amax, float* __restrict__ dw,
+                                                          float* __restrict__ db, float* __restrict__ scratch, int B) {
   grid_dep_wait();
   grid_dep_launch();
   __shared__ float img[32][33];
   __shared__ __align__(16) float red[8][26][32];
   const int n = blockIdx.x;
-  const int c = threadIdx.x & 31, grp = threadIdx.x >> 5;
-  // this thread's pixels: grp, grp+32, ...; all their loads are issued before anything else
-  float gq[7];
-  int aq[7];
+  const int c = threadIdx.x & 31, grp = threadIdx.x >> 5;  // 16 pixel groups
+  // this thread's pixels: grp, grp+16, ...; all their loads are issued before anything else
+  constexpr int kPix = 13;  // ceil(196 / 16)
+  float gq[kPix];
+  int aq[kPix];
 #pragma unroll
-  for (int it = 0; it < 7; ++it) {
-    const int pix = grp + it * 32;
+  for (int it = 0; it < kPix; ++it) {
+    const int pix = grp + it * 16;
     gq[it] = 0.f;
     aq[it] = 0;
     if (pix < 196) {
@@ -193,8 +195,7 @@ __global__ void __launch_bounds__(1024) conv1_wgrad_kernel(const float* __restri
       aq[it] = amax[idx];
     }
   }
-  {
-    const int i = threadIdx.x;  // 32 x 32 padded image, one element per thread
+  for (int i = threadIdx.x; i < 32 * 32; i += 512) {  // 32 x 32 zero-padded image
     const int r = (i >> 5) - 2, cc = (i & 31) - 2;
     img[i >> 5][i & 31] = (r >= 0 && r < 28 && cc >= 0 && cc < 28) ? x[(long long)n * 784 + r * 28 + cc] : 0.f;
   }
@@ -204,8 +205,8 @@ __global__ void __launch_bounds__(1024) conv1_wgrad_kernel(const float* __restri
   for (int t = 0; t < 25; ++t) acc[t] = 0.f;
   float accb = 0.f;
 #pragma unroll
-  for (int it = 0; it < 7; ++it) {
-    const int pix = grp + it * 32;
+  for (int it = 0; it < kPix; ++it) {
+    const int pix = grp + it * 16;
     if (pix < 196) {
       const int ph = pix / 14, pw = pix % 14;
       const float g = gq[it];
@@ -217,9 +218,9 @@ __global__ void __launch_bounds__(1024) conv1_wgrad_kernel(const float* __restri
         for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(g, img[h + kh][wq + kw], acc[kh * 5 + kw]);
     }
   }
-  // 32 warps -> 8 rows of `red` in four passes (pass k: warps 8k..8k+7), a fixed order
+  // 16 warps -> 8 rows of `red` in two passes (pass k: warps 8k..8k+7), a fixed order
 #pragma unroll 1
-  for (int pass = 0; pass < 4; ++pass) {
+  for (int pass = 0; pass < 2; ++pass) {
     if ((grp >> 3) == pass) {
       const int row = grp & 7;
       if (pass == 0) {
@@ -236,30 +237,31 @@ __global__ void __launch_bounds__(1024) conv1_wgrad_kernel(const float* __restri
   }
   unsigned* counter = reinterpret_cast<unsigned*>(scratch);
   float* parts = scratch + 16;
-  if (threadIdx.x < 832) {
-    const int i = threadIdx.x, t = i >> 5, cc = i & 31;
+  for (int i = threadIdx.x; i < 832; i += 512) {
+    const int t = i >> 5, cc = i & 31;
     float s = 0.f;
 #pragma unroll
     for (int g8 = 0; g8 < 8; ++g8) s += red[g8][t][cc];
     __stcg(parts + (size_t)blockIdx.x * 832 + i, s);
   }
   if (!last_block_arrives(counter, gridDim.x)) return;
-  // final sum over the images' partials: 208 float4 outputs x 4 interleaved groups of images, each summed in image
-  // order with 8 loads in flight, then the four group sums are added in group order
-  float4* red4 = reinterpret_cast<float4*>(&red[0][0][0]);  // [4][208]
+  // final sum over the images' partials: 208 float4 outputs x 2 interleaved groups of images, each summed in image
+  // order with 16 loads in flight, then the group sums are added in group order
+  float4* red4 = reinterpret_cast<float4*>(&red[0][0][0]);  // [4][208] (groups 2, 3 stay zero)
   const int o4 = threadIdx.x % 208, grp4 = threadIdx.x / 208;
-  if (grp4 < 4) {
+  if (threadIdx.x < 416) red4[(grp4 + 2) * 208 + o4] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (grp4 < 2) {
     const float4* p4 = reinterpret_cast<const float4*>(parts) + o4;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     int bk = grp4;
-    for (; bk + 28 < (int)gridDim.x; bk += 32) {
-      float4 v[8];
+    for (; bk + 30 < (int)gridDim.x; bk += 32) {
+      float4 v[16];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = __ldcg(p4 + (size_t)(bk + 4 * u) * 208);
+      for (int u = 0; u < 16; ++u) v[u] = __ldcg(p4 + (size_t)(bk + 2 * u) * 208);
 #pragma unroll
-      for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+      for (int u = 0; u < 16; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
     }
-    for (; bk < (int)gridDim.x; bk += 4) {
+    for (; bk < (int)gridDim.x; bk += 2) {
       const float4 v = __ldcg(p4 + (size_t)bk * 208);
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }
@@ -712,11 +714,14 @@ extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, in
   TFD_ACT_CHECK("conv1_wgrad");
   TFD_REQUIRE(scratch != nullptr && nsplit >= 1, "conv1_wgrad: scratch missing or nsplit %d < 1", nsplit);
   const dim3 grid(B);
+  // runs next to the conv2 wgrad CTAs (one per SM, ~194 KB of shared memory): ask for the same carve-out
+  tfd_prefer_max_carveout(reinterpret_cast<const void*>(conv1_wgrad_kernel<float>));
+  tfd_prefer_max_carveout(reinterpret_cast<const void*>(conv1_wgrad_kernel<bf16>));
   if (dtype == TFD_DTYPE_TF32)
-    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<float>, grid, dim3(1024), 0, ST(stream), x, dpool, nsplit, split_stride,
+    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<float>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
                               (const float*)pool_out, argmax, dw, db, scratch, B));
   else
-    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<bf16>, grid, dim3(1024), 0, ST(stream), x, dpool, nsplit, split_stride,
+    TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<bf16>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
                               (const bf16*)pool_out, argmax, dw, db, scratch, B));
   TFD_LAUNCH_CHECK();
   return 0;

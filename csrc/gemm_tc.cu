@@ -62,9 +62,6 @@ struct GemmParams {
   const __nv_bfloat16* mask;    // relu mask source (same shape as out), or null
   long long ld_mask;
   long long split_stride;       // STORE_F32 split-K: plane z at out_f32 + z*split_stride
-  // TFD_EPI_POOL2_BWD: the dgrad of fc1 flows straight through ReLU + 2x2 max-pool backward of the conv2 block
-  const unsigned char* amax;    // [M, 7,7,64] arg-max position of every pooled element
-  float* dbias;                 // [64] += sum of the surviving gradient (conv2 bias gradient)
 };
 
 // Element-type dependent tile constants.  A pipeline stage always holds BM x 128 B of A and BN x 128 B of B: 64 bf16 or
@@ -275,54 +272,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       }
-    } else if (p.mode == TFD_EPI_POOL2_BWD) {
-      // BN == 64 == the channels of ONE pooled pixel: column tile n0 is pixel n0/64.  Each thread owns a batch row:
-      // it masks its 64 gradients with ReLU (pooled value > 0), routes each to its arg-max position of the 2x2
-      // window (zeros elsewhere: dy is written densely) and the warp reduces the conv2 bias gradient.
-      const int px = n0 >> 6, ph = px / 7, pw = px - ph * 7;
-      const __nv_bfloat16* prow = p.mask + (long long)row * p.ld_mask + n0;
-      const unsigned char* arow = p.amax + (long long)row * p.ld_mask + n0;
-#pragma unroll 1
-      for (int c = 0; c < 64; c += 16) {
-        float v[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-        uint4 am4 = make_uint4(0, 0, 0, 0);
-        if (row_ok) {
-          am4 = *reinterpret_cast<const uint4*>(arow + c);
-          const uint4 p0 = *reinterpret_cast<const uint4*>(prow + c), p1 = *reinterpret_cast<const uint4*>(prow + c + 8);
-          const uint32_t pw32[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float pv = __uint_as_float((i & 1) ? (pw32[i >> 1] & 0xffff0000u) : (pw32[i >> 1] << 16));
-            v[i] = pv > 0.f ? v[i] * p.alpha : 0.f;
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = 0.f;
-        }
-        const uint32_t amw[4] = {am4.x, am4.y, am4.z, am4.w};
-        if (row_ok) {
-#pragma unroll
-          for (int qq = 0; qq < 4; ++qq) {
-            uint32_t o[8];
-#pragma unroll
-            for (int i = 0; i < 16; i += 2) {
-              const uint32_t a0 = (amw[i >> 2] >> ((i & 3) * 8)) & 0xff, a1 = (amw[(i + 1) >> 2] >> (((i + 1) & 3) * 8)) & 0xff;
-              o[i >> 1] = pack_bf16x2(a0 == (uint32_t)qq ? v[i] : 0.f, a1 == (uint32_t)qq ? v[i + 1] : 0.f);
-            }
-            __nv_bfloat16* d = p.out_bf16 + ((((long long)row * 14 + 2 * ph + (qq >> 1)) * 14) + 2 * pw + (qq & 1)) * 64 + c;
-            *reinterpret_cast<uint4*>(d) = make_uint4(o[0], o[1], o[2], o[3]);
-            *reinterpret_cast<uint4*>(d + 8) = make_uint4(o[4], o[5], o[6], o[7]);
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float sacc = v[i];
-#pragma unroll
-          for (int off = 16; off > 0; off >>= 1) sacc += __shfl_xor_sync(0xffffffffu, sacc, off);
-          if (lane == 0) atomicAdd(p.dbias + c + i, sacc);
-        }
-      }
     } else if (p.mode == TFD_EPI_STORE_BF16 && (p.ld_out & 7) == 0 && n0 + BN <= p.N) {
       // Coalesced bf16 store (bf16 gradient push): same staging idea, rows of BN*2 bytes.
       constexpr int kPitchB = BN * 2 + 16;  // bytes; odd multiple of 16 -> conflict-free
@@ -469,7 +418,7 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
                          const float* bias, const void* relu_mask, long long ld_mask, long long split_stride,
                          int seg_mode, int nseg, const int* seg_rows, void* const* out_ptrs,
                          const unsigned* const* wait_flags, unsigned wait_value, const unsigned* wait_value_ptr,
-                         const unsigned char* amax, float* dbias, int dtype, void* stream);
+                         int dtype, void* stream);
 
 // Segmented form: the sharded operand is given as nseg pieces.  seg_rows[nseg+1] are the row boundaries of the
 // sharded dimension (K for TFD_SEG_B_K, N for TFD_SEG_B_N, M for TFD_SEG_OUT_M; multiples of 128, first = 0).
@@ -482,7 +431,7 @@ extern "C" int tfd_gemm_bf16_seg(const void* A, long long lda, int a_mn, const v
                                  const unsigned* wait_value_ptr, void* stream) {
   return gemm_seg_impl(A, lda, a_mn, B_ptrs, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
                        ld_mask, split_stride, seg_mode, nseg, seg_rows, out_ptrs, wait_flags, wait_value, wait_value_ptr,
-                       nullptr, nullptr, TFD_DTYPE_BF16, stream);
+                       TFD_DTYPE_BF16, stream);
 }
 
 // Same GEMM with the operand type as a parameter: TFD_DTYPE_BF16 (bf16 in memory) or TFD_DTYPE_TF32 (fp32 in memory,
@@ -496,7 +445,7 @@ extern "C" int tfd_gemm_seg(int dtype, const void* A, long long lda, int a_mn, c
                             void* stream) {
   return gemm_seg_impl(A, lda, a_mn, B_ptrs, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
                        ld_mask, split_stride, seg_mode, nseg, seg_rows, out_ptrs, wait_flags, wait_value, wait_value_ptr,
-                       nullptr, nullptr, dtype, stream);
+                       dtype, stream);
 }
 
 static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* const* B_ptrs, long long ldb, int b_mn, int M,
@@ -504,7 +453,7 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
                          const float* bias, const void* relu_mask, long long ld_mask, long long split_stride,
                          int seg_mode, int nseg, const int* seg_rows, void* const* out_ptrs,
                          const unsigned* const* wait_flags, unsigned wait_value, const unsigned* wait_value_ptr,
-                         const unsigned char* amax, float* dbias, int dtype, void* stream) {
+                         int dtype, void* stream) {
   TFD_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
   TFD_REQUIRE(dtype == TFD_DTYPE_BF16 || dtype == TFD_DTYPE_TF32, "gemm: unknown operand type %d", dtype);
   const int tf = dtype == TFD_DTYPE_TF32;
@@ -537,9 +486,6 @@ static int gemm_seg_impl(const void* A, long long lda, int a_mn, const void* con
   p.mask = static_cast<const __nv_bfloat16*>(relu_mask); p.ld_mask = ld_mask;
   TFD_REQUIRE((mode != TFD_EPI_RELUMASK_BF16 && mode != TFD_EPI_RELUMASK_F32) || relu_mask,
               "gemm: relu-mask epilogue without a mask");
-  p.amax = amax; p.dbias = dbias;
-  TFD_REQUIRE(mode != TFD_EPI_POOL2_BWD || (bn == 64 && N == 3136 && p.splits == 1 && relu_mask && amax && dbias),
-              "gemm: the pool2-backward epilogue needs bn=64, N=3136, one split, pool2/argmax/dbias pointers");
 
   SegInfo sg;
   memset(&sg, 0, sizeof(sg));
@@ -607,19 +553,6 @@ extern "C" int tfd_gemm(int dtype, const void* A, long long lda, int a_mn, const
   const void* bp[1] = {B};
   return tfd_gemm_seg(dtype, A, lda, a_mn, bp, ldb, b_mn, M, N, K, bn, splits, mode, alpha, out, ld_out, bias, relu_mask,
                       ld_mask, split_stride, TFD_SEG_NONE, 1, nullptr, nullptr, nullptr, 0, nullptr, stream);
-}
-
-// fc1 data gradient fused with the ReLU + 2x2 max-pool backward of the conv2 block: dy2 (bf16 [M,14,14,64], written
-// densely) and the conv2 bias gradient come straight out of the GEMM epilogue; the [M,3136] gradient of pool2 never
-// touches memory.  W is the [3136,1024] fc1 weight (bf16, row-sharded over nseg ps GPUs as in TFD_SEG_B_N).
-extern "C" int tfd_gemm_dgrad_pool2(const void* dY, long long ldd, const void* const* W_ptrs, long long ldw, int M,
-                                    int nseg, const int* seg_rows, const unsigned* const* wait_flags,
-                                    unsigned wait_value, const unsigned* wait_value_ptr, const void* pool2,
-                                    const unsigned char* amax2, void* dy2, float* dbias, void* stream) {
-  const int full[2] = {0, 3136};
-  return gemm_seg_impl(dY, ldd, 0, W_ptrs, ldw, 0, M, 3136, 1024, 64, 1, TFD_EPI_POOL2_BWD, 1.0f, dy2, 0, nullptr, pool2,
-                       3136, 0, nseg > 1 ? TFD_SEG_B_N : TFD_SEG_NONE, nseg, nseg > 1 ? seg_rows : full, nullptr,
-                       wait_flags, wait_value, wait_value_ptr, amax2, dbias, TFD_DTYPE_BF16, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -156,7 +156,10 @@ int tfd_num_sms() {
   return n;
 }
 
-void tfd_prefer_max_smem(const void* kernel) {
+// Hint, once per (device, kernel): run this kernel with the largest shared-memory carve-out, the configuration the
+// tcgen05 kernels (200+ KB of shared memory) put an SM into -- so that its blocks can become resident NEXT to such a
+// CTA instead of waiting for the SM to drain and reconfigure.
+void tfd_prefer_max_carveout(const void* kernel) {
   static std::mutex mu;
   static std::set<std::pair<int, const void*>> done;
   int dev = 0;
@@ -166,13 +169,4 @@ void tfd_prefer_max_smem(const void* kernel) {
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) !=
       cudaSuccess)
     cudaGetLastError();  // a hint only: never fail a launch over it
-}
-
-int tfd_uniform_carveout() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("TFD_CARVEOUT");
-    v = (e && e[0] == '1') ? 1 : 0;
-  }
-  return v;
 }

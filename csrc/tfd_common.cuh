@@ -279,17 +279,11 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t target
 int tfd_pdl_enabled();
 int tfd_ensure_dyn_smem(const void* kernel, int bytes);  // per (device, kernel) opt-in to > 48 KB dynamic smem
 int tfd_num_sms();                                       // SM count of the current device
-void tfd_prefer_max_smem(const void* kernel);
-int tfd_uniform_carveout();
+void tfd_prefer_max_carveout(const void* kernel);        // per (device, kernel) hint: largest shared-memory carve-out
 #ifdef __CUDACC__
 template <typename... KArgs, typename... Args>
 inline cudaError_t tfd_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {
-  // One shared-memory carve-out for every kernel of the step.  The tcgen05 kernels need ~200 KB of shared memory
-  // per CTA; a kernel that runs with the default (L1-heavy) carve-out on the same SM forces the SM to drain and
-  // reconfigure before such a CTA can become resident.  Measured: no gain (the bubbles between overlapping
-  // kernels come from register-file occupancy, not the carve-out), so this is opt-in (TFD_CARVEOUT=1).
-  if (tfd_uniform_carveout()) tfd_prefer_max_smem(reinterpret_cast<const void*>(kernel));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;

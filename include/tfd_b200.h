@@ -26,7 +26,6 @@ int tfd_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, siz
 #define TFD_EPI_BIAS_RELU_BF16 2 /* out bf16 = relu(alpha*acc + bias)                               */
 #define TFD_EPI_STORE_BF16 3     /* out bf16 = alpha*acc (+bias)                                    */
 #define TFD_EPI_RELUMASK_BF16 4  /* out bf16 = mask>0 ? alpha*acc : 0   (dgrad through a ReLU)      */
-#define TFD_EPI_POOL2_BWD 5      /* fc1 dgrad -> ReLU' -> max-pool backward, see tfd_gemm_dgrad_pool2 */
 #define TFD_EPI_BIAS_RELU_F32 6  /* out fp32 = relu(alpha*acc + bias)              (tf32 arm)       */
 #define TFD_EPI_RELUMASK_F32 7   /* out fp32 = mask>0 ? alpha*acc : 0, mask fp32   (tf32 arm)       */
 
@@ -90,15 +89,6 @@ int tfd_gemm_seg(int dtype, const void* A, long long lda, int a_mn, const void* 
 int tfd_gemm_bf16_splitk_noalloc(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, int M,
                                  int N, int K, int bn, int splits, float* out, long long ld_out, const float* bias,
                                  int relu, void* stream);
-
-/* fc1 data gradient fused with the ReLU + 2x2 max-pool backward of the conv2 block (B5-B7 of SURVEY 2.3 in one
- * kernel): dy2 bf16 [M,14,14,64] (dense) and dbias[64] += come out of the GEMM epilogue.  dY bf16 [M,1024];
- * W = fc1 weight bf16 [3136,1024], whole (nseg = 1) or row-sharded over ps GPUs (seg_rows, W_ptrs per shard,
- * optional version gates as in tfd_gemm_bf16_seg); pool2 bf16 / amax2 u8 [M,3136] from the forward pass. */
-int tfd_gemm_dgrad_pool2(const void* dY, long long ldd, const void* const* W_ptrs, long long ldw, int M, int nseg,
-                         const int* seg_rows, const unsigned* const* wait_flags, unsigned wait_value,
-                         const unsigned* wait_value_ptr, const void* pool2, const unsigned char* amax2, void* dy2,
-                         float* dbias, void* stream);
 
 /* CUDA-core fp32 reference GEMM (validation only): D[M,N] = A[M,K](bf16,row) * B[K,N](bf16,row). */
 int tfd_gemm_ref(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, float* out,

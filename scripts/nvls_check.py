@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--hidden", type=int, default=512)
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--precision", default=None, choices=["tf32", "bf16"])
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -46,7 +47,7 @@ def main():
     batches = [stream.next_batch(128) for _ in range(a.steps)]
     results = []
     for cls in (GpuClusterEngine, NvlsClusterEngine):
-        eng = cls(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05)
+        eng = cls(spec, topo, rank, device, learning_rate=0.01, seed=3, init_stddev=0.05, precision=a.precision)
         losses = [eng.train_step(x, y, 1.0, fetch_loss=True) for x, y in batches]  # eager, eager, then graph replays
         torch.cuda.synchronize()
         dist.barrier()

@@ -60,6 +60,8 @@ class Flags:
     trace_file: str = ""            # write a Chrome trace of a window of steps (utils/trace.py)
     trace_start: int = 2            # first local step of the window (1-based)
     trace_steps: int = 3            # length of the window
+    server_generations: int = 1     # ps task: how many successive sets of clients it serves before it exits (0: until
+                                    # a SHUTDOWN message); later sets attach with --existing_servers=True
 
     def replace(self, **kw) -> "Flags":
         return dataclasses.replace(self, **kw)
@@ -113,6 +115,9 @@ _HELP_EXTRA = {
     "log_device_placement": "Print the variable -> ps shard placement table",
     "sync_init_tokens": "Tokens preloaded into the sync queue (-1 => replicas_to_aggregate)",
     "layout": "GPU cluster: colocated (every GPU is worker + ps shard) or dedicated ps GPUs",
+    "server_generations": "ps task (host:port clusters): serve this many successive sets of worker processes, keeping "
+                          "variables, Adam slots and global_step between them (0 = until a SHUTDOWN message); the later "
+                          "sets attach with --existing_servers=True (m:76-80, m:268-273)",
     "grad_dtype": "Storage type of pushed gradients in the ps staging slots on the GPU path: fp32 | bf16",
     "trace_file": "Write a Chrome trace (+ .txt per-op table) of a window of training steps",
     "trace_start": "First local step of the traced window (1-based)",

@@ -348,6 +348,7 @@ class NativeEngine:
 
     def _sequence(self, ws: Workspace, mode: str, keep_prob: float, mask_out=None) -> None:
         training = mode in ("train", "grads")
+        self._training_apply = (mode == "train")  # "grads" computes gradients without taking part in an update
         self._pre_step(ws, training)
         if self.spec.kind == "cnn":
             self._cnn_forward(ws, training, keep_prob, mask_out)

@@ -173,19 +173,6 @@ def gemm_bf16_seg(A, a_mn: int, B_ptrs, b_mn: int, M: int, N: int, K: int, out, 
     _count()
 
 
-def gemm_dgrad_pool2(dY, W_ptrs, ldw: int, M: int, pool2, amax2, dy2, dbias, seg_rows=None, wait_flags=None,
-                     wait_value: int = 0, wait_value_ptr=None) -> None:
-    """fc1 dgrad fused with ReLU + max-pool backward of the conv2 block (W whole or row-sharded over ps GPUs)."""
-    nseg = len(W_ptrs)
-    WP = (c_void_p * nseg)(*[c_void_p(int(x)) for x in W_ptrs])
-    SR = (c_int * (nseg + 1))(*[int(r) for r in (seg_rows if seg_rows is not None else [0, 3136])])
-    WF = (c_void_p * nseg)(*[c_void_p(int(x) if x else 0) for x in wait_flags]) if wait_flags is not None else None
-    _check(lib().tfd_gemm_dgrad_pool2(_p(dY), c_longlong(dY.stride(0)), WP, c_longlong(ldw), c_int(M), c_int(nseg), SR,
-                                      WF, c_uint(wait_value), _p(wait_value_ptr), _p(pool2), _p(amax2), _p(dy2),
-                                      _p(dbias), _stream()), "tfd_gemm_dgrad_pool2")
-    _count()
-
-
 def gemm_ref(A, B, M, N, K, out) -> None:
     _check(lib().tfd_gemm_ref(_p(A), c_longlong(A.stride(0)), _p(B), c_longlong(B.stride(0)), c_int(M), c_int(N),
                               c_int(K), _p(out), c_longlong(out.stride(0)), _stream()), "tfd_gemm_ref")

@@ -84,7 +84,15 @@ class PSServer:
             dist.send(torch.tensor([self.proto.dequeue_token()], dtype=torch.int64), dst=rank)
             self.served["token"] += 1
 
-    def serve_forever(self) -> None:
+    def new_generation(self) -> None:
+        """A new set of client processes attaches to this (long-lived) server: variables, Adam slots and global_step
+        stay; per-client protocol state (waiting token requests, DONE count, unconsumed tokens) starts afresh."""
+        self.pending_tokens = []
+        self.done = 0
+        self._make_protocol(self.global_step)
+
+    def serve_forever(self) -> str:
+        """Serve until every worker of this generation has said DONE ("done") or someone sent SHUTDOWN ("shutdown")."""
         hdr = torch.zeros(4, dtype=torch.int64)
         while True:
             src = dist.recv(hdr)
@@ -133,9 +141,9 @@ class PSServer:
             elif op == OP_DONE:
                 self.done += 1
                 if self.done >= self.N:
-                    return
+                    return "done"
             elif op == OP_SHUTDOWN:
-                return
+                return "shutdown"
             else:
                 raise RuntimeError("ps: unknown op %d from rank %d" % (op, src))
 

@@ -24,7 +24,7 @@ Sync mode with R = N only; async and backup workers stay on ``ps_gpu``.
 """
 from __future__ import annotations
 
-from typing import Dict, List
+from typing import Dict, List, Optional
 
 import torch
 import torch.distributed as dist
@@ -52,11 +52,11 @@ class NvlsLayout:
     local memory); the owner arenas use the ``num_shards`` placement and are sized for the largest shard.
     """
 
-    def __init__(self, spec: ModelSpec, num_shards: int):
-        self.spec, self.num_shards = spec, num_shards
+    def __init__(self, spec: ModelSpec, num_shards: int, precision: str = "bf16"):
+        self.spec, self.num_shards, self.precision = spec, num_shards, precision
         self.placement1 = Placement(spec, 1)
         self.placement = Placement(spec, num_shards)
-        _, self.shadow_off1, self.shadow_ld1, self.shadow_n1 = ShardState.layout(spec, self.placement1, 0)
+        _, self.shadow_off1, self.shadow_ld1, self.shadow_n1 = ShardState.layout(spec, self.placement1, 0, precision)
         self.n1 = self.placement1.shard_sizes[0]
         self.nmax = max(self.placement.shard_sizes)
         off = 0
@@ -77,7 +77,7 @@ class NvlsLayout:
             (q,) = self.placement1.pieces[p.var]  # where the whole variable sits in the single-shard arenas
             flat = q.offset + p.row_start * p.cols
             ld, soff = 0, 0
-            if needs_shadow(self.spec, p.var):
+            if needs_shadow(self.spec, p.var, self.precision):
                 ld = self.shadow_ld1[p.var]
                 if ld != p.cols:
                     raise ValueError("NVLS transport: %s has %d columns; bf16-published tensors need a multiple of 8"
@@ -94,13 +94,14 @@ class NvlsClusterEngine(NativeEngine):
     _prio_default = "1"
 
     def __init__(self, spec: ModelSpec, topo, rank: int, device, learning_rate: float = 0.01, seed: int = 0,
-                 init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False):
+                 init_stddev: float = 1.0, use_graphs: bool = True, conv2_ref: bool = False,
+                 precision: Optional[str] = None):
         if not dist.is_initialized():
             raise RuntimeError("NvlsClusterEngine needs torch.distributed (bootstrap only) to be initialised")
         nat.lib()
         import torch.distributed._symmetric_memory as symm
         self.spec, self.topo, self.rank = spec, topo, rank
-        self._set_precision("bf16")  # the multicast transport publishes bf16 shadows; tf32 stays on the peer transport
+        self._set_precision(precision, conv2_ref)  # tf32: fp32 mirrors only; bf16: fp32 mirrors + bf16 shadow mirrors
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
         nat.set_device(self.device.index or 0)
@@ -113,7 +114,7 @@ class NvlsClusterEngine(NativeEngine):
         self.is_ps, self.is_worker = self.my_shard is not None, self.my_worker is not None
         self.num_workers, self.num_shards = topo.num_workers, topo.num_shards
         self.async_mode, self.backup = False, False
-        L = self.layout = NvlsLayout(spec, topo.num_shards)
+        L = self.layout = NvlsLayout(spec, topo.num_shards, self.precision)
         # ---- symmetric heap: unicast view of every rank + one multicast alias ----
         self._buf = symm.empty(L.total, dtype=torch.uint8, device=self.device)
         self._buf.zero_()
@@ -135,7 +136,7 @@ class NvlsClusterEngine(NativeEngine):
             return torch.zeros(64, dtype=dtype, device=dev)  # Adam slots exist on the owner shards only
 
         self.placement = L.placement1
-        self.shard = ShardState(spec, L.placement1, 0, dev, alloc=alloc)
+        self.shard = ShardState(spec, L.placement1, 0, dev, alloc=alloc, precision=self.precision)
         self.grad = here(L.grad, L.n1, torch.float32)
         self.ctrl = self.shard.ctrl
         # ---- owner side ----
@@ -193,7 +194,7 @@ class NvlsClusterEngine(NativeEngine):
     # ---- public API -------------------------------------------------------------------------
     def workspace(self, B: int) -> Workspace:
         if B not in self.ws:
-            self.ws[B] = Workspace(self.spec, B if self.is_worker else 1, self.device)
+            self.ws[B] = Workspace(self.spec, B if self.is_worker else 1, self.device, self.precision)
             self.ws[B].B = B if self.is_worker else 1
         return self.ws[B]
 
@@ -202,7 +203,7 @@ class NvlsClusterEngine(NativeEngine):
             super().load_batch(ws, x, y)
 
     def describe(self) -> str:
-        return self.topo.describe() + " sync nvls"
+        return self.topo.describe() + " " + self.precision + " sync nvls"
 
     def _owner_word(self, shard: int, word: int) -> torch.Tensor:
         r = self.topo.ps_ranks[shard]
@@ -276,4 +277,4 @@ class NvlsClusterEngine(NativeEngine):
     def from_bench_args(cls, spec, a, rank: int, world: int, device) -> "NvlsClusterEngine":
         from .ps_gpu import Topology
         return cls(spec, Topology.make(world, a.layout, a.ps), rank, device, learning_rate=0.01, seed=0,
-                   init_stddev=a.init_stddev)
+                   init_stddev=a.init_stddev, precision=getattr(a, "precision", None))

@@ -134,18 +134,32 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
     if flags.log_device_placement:
         log(placement.table())
 
-    if not flags.existing_servers or flags.job_name == "ps":
-        ps_cpu.init_process_group(cluster, flags.job_name, flags.task_index, flags.step_timeout_secs)
-    else:
-        host, port = cluster.task_address("worker", flags.task_index).host_port
-        log("Using existing server at: %s" % ("grpc://%s:%d" % (host, port)))
-        ps_cpu.init_process_group(cluster, flags.job_name, flags.task_index, flags.step_timeout_secs)
-
     if flags.job_name == "ps":
+        # tf.train.Server + server.join() (m:158-161).  The server is long-lived: it serves `server_generations`
+        # successive sets of client processes (0 = until SHUTDOWN) and keeps variables, Adam slots and global_step
+        # between them -- what lets a worker started with --existing_servers=True attach to servers that outlive their
+        # clients (m:76-80, m:268-273).  One gloo group per generation, same endpoint.
         server = ps_cpu.PSServer(cluster, spec, placement, flags.task_index, flags.sync_replicas, R,
                                  flags.learning_rate)
-        server.serve_forever()  # server.join() (m:160-161); returns once every worker is DONE / on SHUTDOWN
-        return {"role": "ps", "global_step": server.global_step, "served": server.served}
+        generation, why = 0, "done"
+        while True:
+            ps_cpu.init_process_group(cluster, flags.job_name, flags.task_index,
+                                      flags.step_timeout_secs if generation == 0 else 24 * 3600.0)
+            if generation:
+                server.new_generation()
+                log("ps %d: serving client generation %d from global step %d" % (flags.task_index, generation,
+                                                                               server.global_step))
+            why = server.serve_forever()
+            torch.distributed.destroy_process_group()
+            generation += 1
+            if why == "shutdown" or (flags.server_generations and generation >= flags.server_generations):
+                break
+        return {"role": "ps", "global_step": server.global_step, "served": server.served, "generations": generation}
+
+    if flags.existing_servers:
+        host, port = cluster.task_address("worker", flags.task_index).host_port
+        log("Using existing server at: %s" % ("grpc://%s:%d" % (host, port)))
+    ps_cpu.init_process_group(cluster, flags.job_name, flags.task_index, flags.step_timeout_secs)
 
     is_chief = cl.is_chief(flags)
     device = cl.worker_device(flags, cluster)
@@ -176,8 +190,12 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
         client.set_state(blob["global_step"], ad["t"] if ad else 0, blob["variables"],
                          ad["m"] if ad else zeros, ad["v"] if ad else zeros)
 
-    sv.prepare_or_wait(init_fn=lambda: client.init_variables(eng.get_params()), restore_fn=_restore,
-                       wait_fn=lambda s: client.wait_ready(s, flags.step_timeout_secs))
+    if flags.existing_servers and client.ready():
+        # the servers outlived their previous clients: their variables are initialised and trained; attach as they are
+        log("Worker %d: attached to running servers at global step %d" % (flags.task_index, client.global_step()))
+    else:
+        sv.prepare_or_wait(init_fn=lambda: client.init_variables(eng.get_params()), restore_fn=_restore,
+                           wait_fn=lambda s: client.wait_ready(s, flags.step_timeout_secs))
     if sv.restored_from:
         log("Worker %d: restored variables from %s" % (flags.task_index, sv.restored_from))
     log("Worker %d: Session initialization complete." % flags.task_index)

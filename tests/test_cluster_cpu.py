@@ -162,3 +162,30 @@ def test_kill_and_resume_from_periodic_checkpoint(tmp_path, free_port):
     assert "training step 1 done (global step: 3)" in wout and "(global step: 5)" in wout
     assert wout.count(": training step") in (3, 4)  # the TF token preload may let the worker run one step ahead
     assert checkpoint.latest_checkpoint(str(tmp_path)).endswith("model.ckpt-5.pt")
+
+
+@pytest.mark.timeout(400)
+def test_existing_servers_attach_to_a_server_that_outlives_its_clients(free_port):
+    """m:76-80 / m:268-273: with --existing_servers a worker does not bring a server up, it attaches to one that is
+    already running.  The ps task here serves two successive sets of worker processes and keeps variables, Adam slots
+    and global_step in between: the second set finds an initialised, trained model and continues from its step."""
+    common = ["--model=mlp", "--hidden_units=16", "--init_stddev=0.1", "--keep_prob=1.0", "--batch_size=32",
+              "--validation_batch_size=100", "--validation_batches=1"]
+    ps = _launch("mnist_python_m.py", free_port, common + ["--server_generations=2", "--train_steps=3"])
+    first = [_launch(s, free_port, common + ["--train_steps=3"]) for s in ("mnist_python_w1.py", "mnist_python_w2.py")]
+    outs1 = [p.communicate(timeout=200)[0] for p in first]
+    assert all(p.returncode == 0 for p in first), "\n".join(outs1)
+    assert "Worker 0: Initializing session..." in outs1[0] and "(global step: 3)" in outs1[0]
+    assert ps.poll() is None  # the server is still there
+    second = [_launch(s, free_port, common + ["--train_steps=6", "--existing_servers=True"])
+              for s in ("mnist_python_w1.py", "mnist_python_w2.py")]
+    outs2 = [p.communicate(timeout=200)[0] for p in second]
+    assert all(p.returncode == 0 for p in second), "\n".join(outs2)
+    ps_out = ps.communicate(timeout=60)[0]
+    assert ps.returncode == 0, ps_out
+    assert "ps 0: serving client generation 1 from global step 3" in ps_out
+    for t, o in enumerate(outs2):
+        assert "Using existing server at: grpc://127.0.0.1:%d" % (free_port + 1 + t) in o
+        assert "Worker %d: attached to running servers at global step 3" % t in o
+        assert "training step 1 done (global step: 4)" in o and "(global step: 6)" in o
+        assert 3 <= o.count(": training step") <= 4  # (the default token preload lets a worker run one step ahead)
