@@ -104,6 +104,10 @@ def parse():
                     help="big-matrix pull: fused into the GEMMs (TMA from the ps GPU) or prefetched under the conv layers")
     ap.add_argument("--grad-dtype", dest="grad_dtype", default="fp32", choices=["fp32", "bf16"],
                     help="storage type of the pushed gradients in the ps staging slots (multi-GPU)")
+    ap.add_argument("--transport", default=None, choices=["auto", "peer", "nvls"],
+                    help="multi-GPU ps transport: peer (cudaIpc peer memory, unicast) or nvls (NVSwitch multicast: gradient "
+                         "sum in the switch, one-store parameter publish); default: env TFD_TRANSPORT or auto (nvls on dedicated "
+                         "ps GPUs when the box has multicast)")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--init-stddev", type=float, default=1.0)
     ap.add_argument("--min-seconds", dest="min_seconds", type=float, default=0.3,

@@ -94,6 +94,7 @@ struct GateList {
   const unsigned* flag[TFD_MAX_SEG];
   int n;
   const unsigned* want_ptr;
+  unsigned want_mul;  // a flag must reach want_mul * *want_ptr (the multicast transport counts one version per shard)
 };
 
 template <typename T>
@@ -113,7 +114,8 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
   float wr[25];
   float bias;
   if (gate.n > 0) {
-    if ((int)threadIdx.x < gate.n) spin_until_ge(gate.flag[threadIdx.x], *gate.want_ptr, "conv1: parameter version");
+    if ((int)threadIdx.x < gate.n)
+      spin_until_ge(gate.flag[threadIdx.x], gate.want_mul * *gate.want_ptr, "conv1: parameter version");
     __syncthreads();
 #pragma unroll
     for (int t = 0; t < 25; ++t) wr[t] = __ldcg(w + t * 32 + c);  // the mirror was written by another GPU: read at L2
@@ -688,7 +690,7 @@ extern "C" int tfd_cast_bf16(const float* src, long long ld_src, void* dst, long
 
 extern "C" int tfd_conv1_fwd(int dtype, const float* x, const float* w, const float* b, void* pool_out,
                              unsigned char* argmax, int B, const unsigned* const* gate_flags, int ngate,
-                             const unsigned* want_ptr, void* stream) {
+                             const unsigned* want_ptr, unsigned want_mul, void* stream) {
   TFD_ACT_CHECK("conv1_fwd");
   TFD_REQUIRE(ngate >= 0 && ngate <= TFD_MAX_SEG && (ngate == 0 || (gate_flags && want_ptr)),
               "conv1_fwd: bad gate list (%d flags)", ngate);
@@ -696,6 +698,7 @@ extern "C" int tfd_conv1_fwd(int dtype, const float* x, const float* w, const fl
   memset(&gl, 0, sizeof(gl));
   gl.n = ngate;
   gl.want_ptr = want_ptr;
+  gl.want_mul = want_mul ? want_mul : 1u;
   for (int i = 0; i < ngate; ++i) gl.flag[i] = gate_flags[i];
   if (dtype == TFD_DTYPE_TF32)
     TFD_CUDA_CHECK(tfd_launch(conv1_fwd_kernel<float>, dim3(B, 2), dim3(224), 0, ST(stream), x, w, b, (float*)pool_out, argmax, gl));

@@ -108,10 +108,10 @@ int tfd_random_normal(float* out, long long n, unsigned long long seed, float st
 /* conv1 5x5 SAME 1->32 + bias + ReLU + 2x2 max-pool (m:109-111).  x fp32 [B,784]; w fp32 [25,32] (HWIO);
  * out [B,14,14,32] (activation type); argmax u8 [B,14,14,32] (0..3 = position inside the 2x2 window).
  * gate_flags (optional, ngate <= TFD_MAX_SEG): every block first waits until each of these LOCAL version words has
- * reached *want_ptr -- the parameter-server worker's wait for the owner shards' updates, folded into the step's
- * first kernel (the owners store the words into this GPU's memory; nothing is polled over NVLink). */
+ * reached want_mul * *want_ptr -- the parameter-server worker's wait for the owner shards' updates, folded into
+ * the step's first kernel (the owners store the words into this GPU's memory; nothing is polled over NVLink). */
 int tfd_conv1_fwd(int dtype, const float* x, const float* w, const float* b, void* pool_out, unsigned char* argmax, int B,
-                  const unsigned* const* gate_flags, int ngate, const unsigned* want_ptr, void* stream);
+                  const unsigned* const* gate_flags, int ngate, const unsigned* want_ptr, unsigned want_mul, void* stream);
 /* conv1 filter/bias gradient with pool+ReLU backward folded in.  dpool fp32: nsplit partial planes of
  * d(loss)/d(pool1) [B,14,14,32], split_stride elements apart, added here in plane order.  dw fp32 [25,32] and db fp32
  * [32] are WRITTEN (fixed-order reduction through `scratch`, no atomics; they may be peer-mapped staging slots).

@@ -123,7 +123,10 @@ def run_ours(a, rank: int, world: int, local: int) -> Optional[dict]:
         import torch.distributed as dist
         if not dist.is_initialized():
             dist.init_process_group("nccl", device_id=device)
-        if os.environ.get("TFD_TRANSPORT", "peer") == "nvls":  # experimental multicast transport (parallel/ps_nvls.py)
+        from .parallel.ps_gpu import Topology, choose_transport
+        transport = choose_transport(getattr(a, "transport", None), Topology.make(world, a.layout, a.ps),
+                                     not getattr(a, "async_mode", False), True, getattr(a, "grad_dtype", "fp32"), local)
+        if transport == "nvls":  # NVSwitch multicast (parallel/ps_nvls.py)
             from .parallel.ps_nvls import NvlsClusterEngine
             eng = NvlsClusterEngine.from_bench_args(spec, a, rank, world, device)
         else:

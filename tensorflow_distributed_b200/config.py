@@ -57,6 +57,7 @@ class Flags:
     sync_init_tokens: int = -1      # get_init_tokens_op(num_tokens); -1 => replicas_to_aggregate (m:233)
     layout: str = "auto"            # GPU cluster: auto | colocated | dedicated ps GPUs
     grad_dtype: str = "fp32"        # dtype of pushed gradients on the GPU path: fp32 | bf16
+    transport: str = "auto"         # GPU cluster transport: auto | peer (cudaIpc peer memory) | nvls (NVSwitch multicast)
     trace_file: str = ""            # write a Chrome trace of a window of steps (utils/trace.py)
     trace_start: int = 2            # first local step of the window (1-based)
     trace_steps: int = 3            # length of the window
@@ -115,6 +116,9 @@ _HELP_EXTRA = {
     "log_device_placement": "Print the variable -> ps shard placement table",
     "sync_init_tokens": "Tokens preloaded into the sync queue (-1 => replicas_to_aggregate)",
     "layout": "GPU cluster: colocated (every GPU is worker + ps shard) or dedicated ps GPUs",
+    "transport": "GPU cluster transport: peer (cudaIpc peer memory, unicast), nvls (NVSwitch multicast: gradient sum in the "
+                 "switch, one-store parameter publish; strict sync only) or auto (nvls on dedicated ps GPUs when the box "
+                 "has multicast, else peer)",
     "server_generations": "ps task (host:port clusters): serve this many successive sets of worker processes, keeping "
                           "variables, Adam slots and global_step between them (0 = until a SHUTDOWN message); the later "
                           "sets attach with --existing_servers=True (m:76-80, m:268-273)",

@@ -205,12 +205,13 @@ def scratch_floats(kind: str, B: int) -> int:
     return int(fn(c_int(B)))
 
 
-def conv1_fwd(x, w, b, pool_out, argmax, B: int, tf32: bool = False, gate_flags=None, want_ptr=None) -> None:
+def conv1_fwd(x, w, b, pool_out, argmax, B: int, tf32: bool = False, gate_flags=None, want_ptr=None,
+              want_mul: int = 1) -> None:
     """gate_flags: LOCAL version words (ints or tensors) every block waits on (>= *want_ptr) before it reads w / b."""
     n = len(gate_flags) if gate_flags else 0
     G = (c_void_p * max(1, n))(*[c_void_p(int(f) if isinstance(f, int) else f.data_ptr()) for f in (gate_flags or [])])
     _check(lib().tfd_conv1_fwd(_dt(tf32), _p(x), _p(w), _p(b), _p(pool_out), _p(argmax), c_int(B), G, c_int(n),
-                               _p(want_ptr), _stream()), "tfd_conv1_fwd")
+                               _p(want_ptr), c_uint(want_mul), _stream()), "tfd_conv1_fwd")
     _count()
 
 

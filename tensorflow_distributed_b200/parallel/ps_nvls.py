@@ -173,8 +173,14 @@ class NvlsClusterEngine(NativeEngine):
         return self.ctrl[W_STEP:]
 
     def _pre_step(self, ws, training: bool) -> None:
-        # every shard adds 1 to the version per applied step: step k may start once it reads num_shards * k
-        nat.nvls_gate(self.ctrl[W_VERSION:], self.step_ptr(), self.num_shards, 0)
+        # every shard adds 1 to the version per applied step: step k may start once it reads num_shards * k.  The CNN's
+        # first kernel does the waiting itself (conv1_fwd below); the MLP has a one-block gate kernel.
+        if self.spec.kind != "cnn":
+            nat.nvls_gate(self.ctrl[W_VERSION:], self.step_ptr(), self.num_shards, 0)
+
+    def conv1_fwd(self, ws, training: bool = True) -> None:
+        nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, ws.B, tf32=self.tf32,
+                      gate_flags=[self.ctrl[W_VERSION:]], want_ptr=self.step_ptr(), want_mul=self.num_shards)
 
     def _post_backward(self, ws) -> None:
         if self._training_apply:  # "grads" mode computes gradients without taking part in an update

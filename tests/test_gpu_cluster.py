@@ -157,20 +157,34 @@ def test_gpu_backup_workers_drop_a_stragglers_stale_gradients(tmp_path):
     assert any("(global step: 12)" in o for o in outs[1:])
 
 
+def _multicast_supported() -> bool:
+    """NVSwitch multicast (NVLS) on device 0, asked of the driver (CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED)."""
+    try:
+        from cuda.bindings import driver as cu
+        cu.cuInit(0)
+        _, dev = cu.cuDeviceGet(0)
+        _, v = cu.cuDeviceGetAttribute(cu.CUdevice_attribute.CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev)
+        return bool(v)
+    except Exception:  # noqa: BLE001
+        return False
+
+
 @needs2
-@pytest.mark.skipif(os.environ.get("TFD_TEST_NVLS", "0") != "1",
-                    reason="experimental NVLS transport: opt in with TFD_TEST_NVLS=1 (not yet validated on hardware)")
-@pytest.mark.parametrize("layout,model", [("colocated", "cnn"), ("dedicated", "cnn"), ("colocated", "mlp")])
-def test_two_gpu_nvls_transport_matches_the_peer_memory_transport(layout, model):
+@pytest.mark.parametrize("layout,model,precision", [("colocated", "cnn", "tf32"), ("dedicated", "cnn", "tf32"),
+                                                    ("colocated", "cnn", "bf16"), ("colocated", "mlp", "tf32")])
+def test_two_gpu_nvls_transport_matches_the_peer_memory_transport(layout, model, precision):
+    """The NVSwitch-multicast transport (gradient sum in the switch by multimem.ld_reduce, one multimem.st publish)
+    against the peer-memory transport: same seed, same batches, parameters / Adam slots / loss trajectory agree."""
+    if not _multicast_supported():
+        pytest.skip("this box exposes no NVSwitch multicast (CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED = 0)")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
            "127.0.0.1", "--master-port", "29631", os.path.join(ROOT, "scripts", "nvls_check.py"), "--layout", layout,
-           "--model", model]
+           "--model", model, "--precision", precision]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert r.returncode == 0 and "OK" in r.stdout and "FAIL" not in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
-@pytest.mark.skipif(not torch.cuda.is_available() or os.environ.get("TFD_TEST_HYBRID", "0") != "1",
-                    reason="CPU-hosted ps + native GPU workers: opt in with TFD_TEST_HYBRID=1 (not yet validated on hardware)")
+@pytest.mark.skipif(not torch.cuda.is_available(), reason="needs a GPU")
 def test_cpu_ps_with_native_gpu_workers(tmp_path):
     """The reference's literal deployment (ps on a CPU host over the network transport, worker compute on a GPU):
     host:port cluster over gloo, --backend=cuda on the workers."""
