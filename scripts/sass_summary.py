@@ -6,7 +6,7 @@ import sys
 
 lib = sys.argv[1] if len(sys.argv) > 1 else "tensorflow_distributed_b200/_native/libtfd_b200.so"
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
-pats = ["UTCHMMA", "UTCBAR", "UTMALDG", "UTMAPF", "LDTM", "SYNCS", "UTCATOM", "RED.E", "REDG", "ATOMG", "LDG", "STG", "HMMA", "SHFL", "MEMBAR", "ERRBAR"]
+pats = ["UTCHMMA", "UTCBAR", "UTMALDG", "UTMAPF", "LDTM", "SYNCS", "UTCATOM", "LDGMC", "RED.E", "REDG", "ATOMG", "LDG", "STG", "HMMA", "SHFL", "MEMBAR", "ERRBAR"]
 cur, counts = None, collections.OrderedDict()
 for line in out.splitlines():
     m = re.search(r"Function : (\S+)", line)
