@@ -50,6 +50,8 @@ def timeit(fn, iters=30, warm=3, per_graph=10):
 
 
 def main():
+    tf32 = os.environ.get("TFD_PRECISION", "tf32") == "tf32"   # operand type of the GEMMs under test
+    dt, esz = (torch.float32, 4) if tf32 else (torch.bfloat16, 2)
     rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dev = torch.device("cuda:%d" % local)
@@ -66,9 +68,9 @@ def main():
     if rank == 0:
         shapes = [("cnn fc1 (wd1)", 128, 1024, 3136, 8, 3), ("mlp layer 8192x8192", 128, 8192, 8192, 1, 1)]
         for name, M, N, K, fsplit, dsplit in shapes:
-            x = torch.randn(M, K, device=dev).to(torch.bfloat16)
-            dy = torch.randn(M, N, device=dev).to(torch.bfloat16)
-            w_local = torch.randn(K, N, device=dev).to(torch.bfloat16)
+            x = torch.randn(M, K, device=dev).to(dt)
+            dy = torch.randn(M, N, device=dev).to(dt)
+            w_local = torch.randn(K, N, device=dev).to(dt)
             planes = torch.zeros(max(fsplit, 1), M, N, device=dev)
             dplanes = torch.zeros(max(dsplit, 1), M, K, device=dev)
             g_local = torch.zeros(K, N, device=dev)
@@ -77,25 +79,26 @@ def main():
 
             def fwd(bptr):
                 nat.gemm_bf16_seg(x, 0, [bptr], 1, M, N, K, planes, mode=nat.EPI_STORE_F32, lda=K, ldb=N, ld_out=N,
-                                  seg_mode=nat.SEG_B_K, seg_rows=[0, K], bn=64, splits=fsplit, split_stride=M * N)
+                                  seg_mode=nat.SEG_B_K, seg_rows=[0, K], bn=64, splits=fsplit, split_stride=M * N, tf32=tf32)
 
             def dgrad(bptr):
                 nat.gemm_bf16_seg(dy, 0, [bptr], 0, M, K, N, dplanes, mode=nat.EPI_STORE_F32, lda=N, ldb=N, ld_out=K,
-                                  seg_mode=nat.SEG_B_N, seg_rows=[0, K], bn=64, splits=dsplit, split_stride=M * K)
+                                  seg_mode=nat.SEG_B_N, seg_rows=[0, K], bn=64, splits=dsplit, split_stride=M * K, tf32=tf32)
 
             def wgrad(optr):
                 nat.gemm_bf16_seg(x, 1, [dy.data_ptr()], 1, K, N, M, None, mode=nat.EPI_STORE_F32, lda=K, ldb=N,
-                                  ld_out=N, seg_mode=nat.SEG_OUT_M, seg_rows=[0, K], out_ptrs=[optr], bn=128)
+                                  ld_out=N, seg_mode=nat.SEG_OUT_M, seg_rows=[0, K], out_ptrs=[optr], bn=128, tf32=tf32)
 
             for kind, fn, loc, rem, nbytes in (
-                    ("pull-fused forward GEMM (B tiles TMA-loaded from the ps GPU)", fwd, w_local.data_ptr(), w_peer, K * N * 2),
-                    ("pull-fused dgrad GEMM (B tiles TMA-loaded from the ps GPU)", dgrad, w_local.data_ptr(), w_peer, K * N * 2),
+                    ("pull-fused forward GEMM (B tiles TMA-loaded from the ps GPU)", fwd, w_local.data_ptr(), w_peer, K * N * esz),
+                    ("pull-fused dgrad GEMM (B tiles TMA-loaded from the ps GPU)", dgrad, w_local.data_ptr(), w_peer, K * N * esz),
                     ("push-fused wgrad GEMM (tiles stored into the slot on the ps GPU)", wgrad, g_local.data_ptr(), slot_peer, K * N * 4)):
                 t_loc = timeit(lambda: fn(loc))
                 t_rem = timeit(lambda: fn(rem))
-                roof_us = max(flops / (tflops * 1e12), nbytes / (NVLINK_GBS * 1e9)) * 1e6
-                roof_loc = max(flops / (tflops * 1e12), nbytes / (hbm * 1e9)) * 1e6
-                results.append({"shape": name, "M": M, "N": N, "K": K, "kernel": kind, "nvlink_bytes": nbytes,
+                peak = tflops * (0.5 if tf32 else 1.0)  # tf32 tensor throughput is half of bf16's
+                roof_us = max(flops / (peak * 1e12), nbytes / (NVLINK_GBS * 1e9)) * 1e6
+                roof_loc = max(flops / (peak * 1e12), nbytes / (hbm * 1e9)) * 1e6
+                results.append({"dtype": "tf32" if tf32 else "bf16", "shape": name, "M": M, "N": N, "K": K, "kernel": kind, "nvlink_bytes": nbytes,
                                 "flops": flops, "us_peer": round(t_rem, 2), "us_local": round(t_loc, 2),
                                 "roofline_us_peer": round(roof_us, 2), "fraction_of_roofline_peer": round(roof_us / t_rem, 3),
                                 "achieved_GBs_peer": round(nbytes / t_rem / 1e3, 1),

@@ -566,3 +566,55 @@ def test_backup_workers_decide_and_masked_apply(nat):
     nat.adam_apply_backup(w, m, v, None, ptrs, 3, 2, n, pieces, 0.01, ctrl[0:], ctrl[16:], ctrl[24:], ctrl[7:], ctrl[2:], ctrl[3:])
     torch.cuda.synchronize()
     assert ctrl[24].item() == 0 and ctrl[0].item() == 2 and torch.equal(w, before)
+
+
+def test_adam_apply_pub_signals_publishes_mirrors_and_releases_local_versions(nat):
+    """The strict-sync cluster step on ONE GPU: the shard's Adam kernel sends the colocated worker's arrival signal
+    itself, waits for it, updates, stores the small variable's new values into every worker's mirror (fp32 and bf16)
+    and releases every worker's local version word; a gate on those words then passes.  All "worker heaps" are local
+    buffers here, so the driver's single-GPU test run exercises the protocol kernels of the multi-GPU path."""
+    from tensorflow_distributed_b200.ops.native import Piece
+    torch.manual_seed(17)
+    small, big = 40 * 64, 64 * 128              # piece 0: mirrored small variable [40,64]; piece 1: a "direct" matrix
+    n = small + big
+    w0 = torch.randn(n, device=DEV)
+    w, m, v = w0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    shadow = torch.zeros(n, device=DEV, dtype=torch.bfloat16)
+    pieces = [Piece(0, small, 64, 64, 0), Piece(small, big, 128, 128, small)]
+    slot = torch.randn(n, device=DEV)
+    ctrl = torch.zeros(64, dtype=torch.int32, device=DEV)   # [0]=t [1]=blocks [2]=version [3]=gstep [4]=arrive [8]=step
+    nworkers = 3
+    heaps = [torch.full((65536,), 7, device=DEV, dtype=torch.uint8) for _ in range(nworkers)]  # fake worker heaps
+    F32_OFF, B16_OFF, VER_OFF = 1024, 32768, 0
+    pub = nat.make_pub([(F32_OFF, B16_OFF, 64), (-1, -1, 0)], [h.data_ptr() for h in heaps],
+                       [h.data_ptr() + VER_OFF for h in heaps], signal_arrive=[ctrl[4:].data_ptr()],
+                       local_step=ctrl[8:].data_ptr())
+    for h in heaps:
+        h[VER_OFF:VER_OFF + 4] = 0
+    ref = {"w": w0.clone().cpu()}
+    opt = oracle.TFAdam(0.01)
+    for step in range(2):
+        nat.adam_apply(w, m, v, shadow, [slot.data_ptr()], 1, 1.0, n, pieces, 0.01, ctrl[0:], ctrl[4:], ctrl[2:], ctrl[3:],
+                       pub=pub)
+        opt.apply(ref, {"w": slot.cpu()})
+    # the worker side: a gate on the local version words passes for step 2, conv1's folded gate too
+    want = torch.tensor([2], dtype=torch.int32, device=DEV)
+    nat.gate_flags([h.data_ptr() + VER_OFF for h in heaps], want)
+    torch.cuda.synchronize()
+    assert torch.allclose(w.cpu(), ref["w"], atol=1e-5, rtol=1e-5)
+    assert ctrl[0].item() == 2 and ctrl[2].item() == 2 and ctrl[3].item() == 2
+    assert ctrl[4].item() == 2 and ctrl[8].item() == 2     # two arrival signals sent, worker step counter advanced twice
+    for h in heaps:
+        assert h[VER_OFF:VER_OFF + 4].view(torch.int32).item() == 2
+        assert torch.equal(h[F32_OFF:F32_OFF + 4 * small].view(torch.float32), w[:small])
+        assert torch.equal(h[B16_OFF:B16_OFF + 2 * small].view(torch.bfloat16), bf(w[:small]))
+        assert torch.all(h[F32_OFF + 4 * small:B16_OFF] == 7) and torch.all(h[B16_OFF + 2 * small:] == 7)  # nothing else
+    assert torch.equal(shadow[small:], bf(w[small:]))      # the big matrix keeps its local shadow, is not mirrored
+
+
+def test_signal_arrive_counts_once_per_shard_and_advances_the_step(nat):
+    ctrl = torch.zeros(16, dtype=torch.int32, device=DEV)
+    for _ in range(3):
+        nat.signal_arrive([ctrl[0:].data_ptr(), ctrl[1:].data_ptr(), ctrl[2:].data_ptr()], ctrl[8:])
+    torch.cuda.synchronize()
+    assert ctrl[:3].tolist() == [3, 3, 3] and ctrl[8].item() == 3
