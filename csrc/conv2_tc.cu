@@ -9,6 +9,7 @@
 // memory; CTAs are persistent over pixel tiles with double-buffered TMEM accumulators.
 #include "../include/tfd_b200.h"
 #include "tfd_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -242,6 +243,195 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 }
 
 // ------------------------------------------------------------------------------------------------
+// One-box variant of the forward / dgrad kernel for operands with 128 B rows (tf32 forward and dgrad, bf16 dgrad).
+//
+// The kernel above fetches five boxes per tile (one per filter column), 120 KB of L2 -> SM traffic for 128 output
+// pixels, and that traffic is what bounds it (~5.5 TB/s aggregate).  Here a tile is 8 columns x 16 rows of one image
+// (accumulator row = h*8 + w) and ONE box {C, 16 w, 20 h} = 40 KB holds the inputs of all 25 taps: the A operand of
+// tap (kh,kw) is the same box read from a start address moved by (kh*16 + kw) rows.  The 8 rows of a core-matrix group
+// are 8 consecutive columns (1024 B contiguous), groups follow at the box's row pitch (SBO = 16 * 128 B), and because
+// the start is moved by kw rows -- not a multiple of the 8-row swizzle pattern -- the descriptor carries the phase of
+// its first row (base offset = kw).  3x less L2 -> SM traffic per tile; the pooling window is still inside one warp
+// (partners at lane ^ 1 and lane ^ 8).
+// ------------------------------------------------------------------------------------------------
+template <bool kFwd, int TF>
+struct BoxCfg {
+  static constexpr int kBoxBytes = 20 * 16 * 128;  // 40 KB
+  static constexpr int kStages = 3;
+  static constexpr int kN = TF ? 32 : 32;           // tf32: a 32-channel half; bf16 dgrad: the 32 input channels
+  static constexpr int kKSteps = 4;                 // 128 B of K per tap, 32 B per MMA
+  static constexpr int kSmem = kFilterBytes + kStages * kBoxBytes + 1024 + 512;
+};
+
+template <bool kFwd, int TF>
+__global__ void __launch_bounds__(kThreads, 1)
+conv2_box_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const float* __restrict__ bias, void* __restrict__ pool_out_v, unsigned char* __restrict__ amax,
+                 float* __restrict__ dx, int B, int num_tiles, long long dx_plane_stride, int use_base_offset) {
+  static_assert(TF == 1 || !kFwd, "the bf16 forward operand has 64 B rows: it stays on the five-box kernel");
+  using C = BoxCfg<kFwd, TF>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* filt = smem;
+  uint8_t* abuf = smem + kFilterBytes;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(abuf + C::kStages * C::kBoxBytes);
+  uint64_t* a_empty = a_full + C::kStages;
+  uint64_t* filt_full = a_empty + C::kStages;
+  uint64_t* acc_full = filt_full + 1;   // [2]
+  uint64_t* acc_empty = acc_full + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int half = TF ? (int)(blockIdx.x & 1) : 0;
+  const int tile0 = TF ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tstride = TF ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmW);
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    mbar_init(filt_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+    fence_barrier_init();
+    fence_proxy_async_smem();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * C::kN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  grid_dep_wait();
+  grid_dep_launch();
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    bool filter_sent = false;
+    for (int tile = tile0; tile < num_tiles; tile += tstride) {
+      const int n = tile >> 1, wt = tile & 1;
+      mbar_wait(&a_empty[stage], phase ^ 1);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&a_full[stage], C::kBoxBytes);
+        // box origin: column 8*wt - 2, row -2 (out-of-bounds pixels are zero-filled = SAME padding); the dgrad reads
+        // this CTA's half of dy's channels on the tf32 arm, all 64 on the bf16 arm (128 B either way)
+        tma_load_4d(abuf + stage * C::kBoxBytes, &tmA, &a_full[stage], (TF && !kFwd) ? half * 32 : 0, 8 * wt - 2, -2, n);
+        if (!filter_sent) load_filter(filt, &tmW, filt_full, TF ? half * 32 : 0);
+      }
+      __syncwarp();
+      filter_sent = true;
+      if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = TF ? make_idesc_tf32(128, C::kN, 0, kFwd ? 1 : 0) : make_idesc_bf16(128, C::kN, 0, 0);
+    // A: K-major, 128 B rows, 8-row groups 2048 B apart (the box's row pitch).  B: the filter tap tile.
+    const uint64_t da0 = make_smem_desc(smem_u32(abuf), 16, 2048, kSwz128);
+    const uint64_t db0 = (TF && kFwd) ? make_smem_desc(smem_u32(filt), 4096, 512, kSwz128B32)   // [32 ci][32 co] MN-major
+                                      : make_smem_desc(smem_u32(filt), 16, 1024, kSwz128);       // K-major (co = K)
+    constexpr uint32_t kBStep = (TF && kFwd) ? 1024u : 32u;
+    mbar_wait(filt_full, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tstride, ++it) {
+      const int buf = it & 1;
+      mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+      mbar_wait(&a_full[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t tacc = tmem_base + buf * C::kN;
+        const uint64_t da_s = desc_advance(da0, (uint32_t)(stage * C::kBoxBytes));
+#pragma unroll
+        for (int kh = 0; kh < 5; ++kh) {
+#pragma unroll
+          for (int kw = 0; kw < 5; ++kw) {
+            // forward: output (h, w) reads box pixel (h + kh, w + kw); dgrad: (h + 4 - kh, w + 4 - kw)
+            const int rh = kFwd ? kh : 4 - kh, rw = kFwd ? kw : 4 - kw;
+            uint64_t da_t = desc_advance(da_s, (uint32_t)((rh * 16 + rw) * 128));
+            if (use_base_offset) da_t = desc_with_base_offset(da_t, (uint32_t)rw);
+            const uint64_t db_t = desc_advance(db0, (uint32_t)((kh * 5 + kw) * 4096));
+#pragma unroll
+            for (int ks = 0; ks < C::kKSteps; ++ks) {
+              const uint32_t acc = (kh > 0 || kw > 0 || ks > 0) ? 1u : 0u;
+              if (TF) umma_tf32(tacc, desc_advance(da_t, ks * 32), desc_advance(db_t, ks * kBStep), idesc, acc);
+              else    umma_bf16(tacc, desc_advance(da_t, ks * 32), desc_advance(db_t, ks * kBStep), idesc, acc);
+            }
+          }
+        }
+        umma_commit(&a_empty[stage]);
+        umma_commit(&acc_full[buf]);
+      }
+      __syncwarp();
+      if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // epilogue: warp q owns accumulator rows 32q..32q+31 = image rows 4q..4q+3 of the tile's 8 columns
+    const int q = warp & 3;
+    const int hl = lane >> 3, wl = lane & 7;
+    int it = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tstride, ++it) {
+      const int buf = it & 1;
+      const int n = tile >> 1, wt = tile & 1;
+      const int h = 4 * q + hl, w = 8 * wt + wl;  // conv output pixel of this lane
+      mbar_wait(&acc_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + buf * C::kN + ((uint32_t)(q * 32) << 16);
+      if (kFwd) {
+        const int self = (hl & 1) * 2 + (wl & 1);
+        const int ph = h >> 1, pw = w >> 1;
+        const int cbase = half * 32;
+#pragma unroll 1
+        for (int j = 0; j < C::kN / 16; ++j) {
+          float v[16];
+          tmem_ld16(tacc + j * 16, v);
+          uint32_t am[4] = {0, 0, 0, 0};
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float x = fmaxf(v[i] + __ldg(bias + cbase + j * 16 + i), 0.f);
+            int xi = self;
+            float y = __shfl_xor_sync(0xffffffffu, x, 1);
+            int yi = self ^ 1;
+            if (y > x || (y == x && yi < xi)) { x = y; xi = yi; }
+            y = __shfl_xor_sync(0xffffffffu, x, 8);
+            yi = __shfl_xor_sync(0xffffffffu, xi, 8);
+            if (y > x || (y == x && yi < xi)) { x = y; xi = yi; }
+            v[i] = x;
+            am[i >> 2] |= (uint32_t)xi << ((i & 3) * 8);
+          }
+          if (j == self && w < 14 && h < 14 && n < B) {
+            const long long o = ((((long long)n * 7 + ph) * 7) + pw) * 64 + cbase + j * 16;
+            float* po = static_cast<float*>(pool_out_v) + o;
+#pragma unroll
+            for (int i = 0; i < 16; i += 4)
+              *reinterpret_cast<float4*>(po + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+            *reinterpret_cast<uint4*>(amax + o) = make_uint4(am[0], am[1], am[2], am[3]);
+          }
+        }
+      } else {
+        const bool ok = (w < 14) && (h < 14) && (n < B);
+        float* o = dx + (long long)half * dx_plane_stride + ((((long long)n * 14 + h) * 14) + w) * 32;
+#pragma unroll 1
+        for (int j = 0; j < 2; ++j) {
+          float v[16];
+          tmem_ld16(tacc + j * 16, v);
+          if (ok) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4)
+              *reinterpret_cast<float4*>(o + j * 16 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * C::kN);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // filter gradient: dW[(tap,ci), co] = sum_px in[px + shift(tap), ci] * dy[px, co].
 // GEMM view per tap group g (4 taps): M = 4*32 (tap_local, ci), N = 64 co, K = 128 pixels of the tile.
 //   A: four [128 px][32 ci] tiles (one TMA box per tap) read MN-major, stacked along M through LBO
@@ -420,6 +610,17 @@ int num_sms() { return tfd_num_sms(); }
 
 }  // namespace
 
+// TFD_CONV2_BOX: 1 = the one-box kernel where the operand rows are 128 B (tf32 forward / dgrad, bf16 dgrad), 0 = the
+// five-box kernel everywhere.  TFD_CONV2_BO: whether the shifted A descriptors carry a base offset (default 1).
+static int conv2_box_mode() {
+  static const int v = [] { const char* e = getenv("TFD_CONV2_BOX"); return e ? atoi(e) : 0; }();
+  return v;
+}
+static int conv2_box_bo() {
+  static const int v = [] { const char* e = getenv("TFD_CONV2_BO"); return e ? atoi(e) : 1; }();
+  return v;
+}
+
 static int conv2_grid(int tiles, int tf) {
   int grid = tf ? 2 * tiles : tiles;  // tf32: (tile, channel half) work items, even CTAs half 0 / odd CTAs half 1
   const int cap = tf ? (num_sms() & ~1) : num_sms();
@@ -440,7 +641,14 @@ extern "C" int tfd_conv2_fwd(int dtype, const void* in, const void* w, const flo
   const int tiles = B * 2;
   const int grid = conv2_grid(tiles, tf);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (tf) {
+  if (tf && conv2_box_mode()) {
+    using C = BoxCfg<true, 1>;
+    rc = tfd_make_tmap_nhwc(&tmA, in, B, 14, 14, 32, 1, 20, 16, 32, 128, 4);
+    if (rc) return rc;
+    if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_box_kernel<true, 1>), C::kSmem)) return arc;
+    TFD_CUDA_CHECK(tfd_launch(conv2_box_kernel<true, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW, b, pool_out,
+                              argmax, (float*)nullptr, B, tiles, 0LL, conv2_box_bo()));
+  } else if (tf) {
     using C = ConvCfg<true, 1>;
     if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<true, 1>), C::kSmem)) return arc;
     TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<true, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW, b, pool_out,
@@ -466,7 +674,24 @@ extern "C" int tfd_conv2_dgrad(int dtype, const void* dy, const void* w, float* 
   const int tiles = B * 2;
   const int grid = conv2_grid(tiles, tf);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (tf) {
+  if (conv2_box_mode()) {
+    rc = tf ? tfd_make_tmap_nhwc(&tmA, dy, B, 14, 14, 64, 1, 20, 16, 32, 128, 4)
+            : tfd_make_tmap_nhwc(&tmA, dy, B, 14, 14, 64, 1, 20, 16, 64, 128, 2);
+    if (rc) return rc;
+    if (tf) {
+      using C = BoxCfg<false, 1>;
+      if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_box_kernel<false, 1>), C::kSmem)) return arc;
+      TFD_CUDA_CHECK(tfd_launch(conv2_box_kernel<false, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW,
+                                (const float*)nullptr, (void*)nullptr, (unsigned char*)nullptr, dx, B, tiles,
+                                (long long)B * 14 * 14 * 32, conv2_box_bo()));
+    } else {
+      using C = BoxCfg<false, 0>;
+      if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_box_kernel<false, 0>), C::kSmem)) return arc;
+      TFD_CUDA_CHECK(tfd_launch(conv2_box_kernel<false, 0>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW,
+                                (const float*)nullptr, (void*)nullptr, (unsigned char*)nullptr, dx, B, tiles, 0LL,
+                                conv2_box_bo()));
+    }
+  } else if (tf) {
     using C = ConvCfg<false, 1>;
     if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<false, 1>), C::kSmem)) return arc;
     TFD_CUDA_CHECK(tfd_launch(conv2_tc_kernel<false, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW,

@@ -10,6 +10,9 @@ the convenient surface for users who want single ops.
                                                     ->  classifier_head
     random_normal (m:186-195)                       ->  random_normal
     AdamOptimizer apply (m:208)                     ->  adam_update
+
+Precision arm = the dtype of what you pass: fp32 tensors run the tf32 arm (fp32 in memory, ``tcgen05 kind::tf32``,
+fp32 activations out), bf16 tensors the bf16 arm.
 """
 from __future__ import annotations
 
@@ -31,6 +34,14 @@ def _cuda(t: torch.Tensor, dtype, name: str) -> torch.Tensor:
     return t.contiguous()
 
 
+def _arm(*tensors) -> bool:
+    """True = tf32 arm (all fp32), False = bf16 arm (all bf16)."""
+    dts = {t.dtype for t in tensors}
+    _need(len(dts) == 1 and dts <= {torch.float32, torch.bfloat16},
+          "tensor-core operands must all be fp32 (tf32 arm) or all be bf16, got %s" % sorted(map(str, dts)))
+    return dts == {torch.float32}
+
+
 def random_normal(shape, stddev: float = 1.0, seed: int = 0, device="cuda") -> torch.Tensor:
     """tf.random_normal(shape, stddev=stddev): Philox4x32-10 + Box-Muller, deterministic in ``seed``."""
     out = torch.empty(shape, dtype=torch.float32, device=device)
@@ -38,41 +49,52 @@ def random_normal(shape, stddev: float = 1.0, seed: int = 0, device="cuda") -> t
     return out
 
 
-def conv1_block(x: torch.Tensor, w_hwio: torch.Tensor, b: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-    """maxpool2d(relu(conv2d(x, w) + b)) for the 5x5, 1 -> 32 layer.  x fp32 [B,784] or [B,28,28,1];
-    returns (pooled bf16 [B,14,14,32], argmax u8 [B,14,14,32])."""
+def conv1_block(x: torch.Tensor, w_hwio: torch.Tensor, b: torch.Tensor,
+                out_dtype=torch.bfloat16) -> Tuple[torch.Tensor, torch.Tensor]:
+    """maxpool2d(relu(conv2d(x, w) + b)) for the 5x5, 1 -> 32 layer (CUDA cores, fp32 math).  x fp32 [B,784] or
+    [B,28,28,1]; returns (pooled [B,14,14,32] in ``out_dtype`` -- fp32 feeds the tf32 arm --, argmax u8)."""
     x = _cuda(x, torch.float32, "x").reshape(-1, 784)
     w = _cuda(w_hwio, torch.float32, "w").reshape(25, 32)
     b = _cuda(b, torch.float32, "b")
     B = x.shape[0]
-    pool = torch.empty(B, 14, 14, 32, dtype=torch.bfloat16, device=x.device)
+    _need(out_dtype in (torch.bfloat16, torch.float32), "out_dtype must be bfloat16 or float32")
+    pool = torch.empty(B, 14, 14, 32, dtype=out_dtype, device=x.device)
     am = torch.empty(B, 14, 14, 32, dtype=torch.uint8, device=x.device)
-    nat.conv1_fwd(x, w, b, pool, am, B)
+    nat.conv1_fwd(x, w, b, pool, am, B, tf32=out_dtype == torch.float32)
     return pool, am
 
 
 def conv2_block(x: torch.Tensor, w_hwio: torch.Tensor, b: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     """maxpool2d(relu(conv2d(x, w) + b)) for the 5x5, 32 -> 64 layer on tcgen05 (implicit GEMM, TMA im2col).
-    x bf16 [B,14,14,32], w bf16 [5,5,32,64]; returns (pooled bf16 [B,7,7,64], argmax u8 [B,7,7,64])."""
-    x = _cuda(x, torch.bfloat16, "x")
-    w = _cuda(w_hwio, torch.bfloat16, "w").reshape(800, 64)
+    x [B,14,14,32], w [5,5,32,64], both bf16 or both fp32; returns (pooled [B,7,7,64] in that type, argmax u8)."""
+    tf = _arm(x, w_hwio)
+    x = _cuda(x, x.dtype, "x")
+    w = _cuda(w_hwio, x.dtype, "w").reshape(800, 64)
     b = _cuda(b, torch.float32, "b")
     _need(tuple(x.shape[1:]) == (14, 14, 32), "x must be [B,14,14,32]")
     B = x.shape[0]
-    pool = torch.empty(B, 7, 7, 64, dtype=torch.bfloat16, device=x.device)
+    pool = torch.empty(B, 7, 7, 64, dtype=x.dtype, device=x.device)
     am = torch.empty(B, 7, 7, 64, dtype=torch.uint8, device=x.device)
-    nat.conv2_fwd(x, w, b, pool, am, B)
+    nat.conv2_fwd(x, w, b, pool, am, B, tf32=tf)
     return pool, am
 
 
 def dense(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
           out_dtype=torch.float32) -> torch.Tensor:
-    """tf.matmul(x, w) (+ bias) (+ relu) on tcgen05.  x bf16 [M,K], w bf16 [K,N] ([in,out], read in place as the
-    MN-major operand).  out fp32 (plain) or bf16 (``relu=True`` or ``out_dtype=torch.bfloat16``)."""
-    x, w = _cuda(x, torch.bfloat16, "x"), _cuda(w, torch.bfloat16, "w")
+    """tf.matmul(x, w) (+ bias) (+ relu) on tcgen05.  x [M,K], w [K,N] ([in,out], read in place as the MN-major
+    operand), both bf16 or both fp32 (tf32 arm: the output is always fp32).  bf16 arm: out fp32 (plain) or bf16
+    (``relu=True`` or ``out_dtype=torch.bfloat16``)."""
+    tf = _arm(x, w)
+    x, w = _cuda(x, x.dtype, "x"), _cuda(w, x.dtype, "w")
     _need(x.shape[1] == w.shape[0], "inner dimensions differ: %s x %s" % (tuple(x.shape), tuple(w.shape)))
     _need(x.shape[1] % 8 == 0 and w.shape[1] % 8 == 0, "K and N must be multiples of 8 (16-byte rows for TMA)")
     M, K, N = x.shape[0], x.shape[1], w.shape[1]
+    if tf:
+        out = torch.empty(M, N, dtype=torch.float32, device=x.device)
+        nat.gemm_bf16(x, 0, w, 1, M, N, K, out, mode=nat.EPI_BIAS_RELU_F32 if relu else nat.EPI_STORE_F32,
+                      bn=128 if N >= 128 else 64, bias=None if bias is None else _cuda(bias, torch.float32, "bias"),
+                      tf32=True)
+        return out
     if relu or out_dtype == torch.bfloat16:
         out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
         mode = nat.EPI_BIAS_RELU_BF16 if relu else nat.EPI_STORE_BF16
@@ -87,9 +109,18 @@ def dense(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
 def dense_grad_input(dy: torch.Tensor, w: torch.Tensor, relu_of: Optional[torch.Tensor] = None) -> torch.Tensor:
     """d(x) of y = x w: dy w^T (w read K-major in place).  With ``relu_of`` (the bf16 activation that fed the layer)
     the gradient is masked by relu'(activation) and returned in bf16; otherwise fp32."""
-    dy, w = _cuda(dy, torch.bfloat16, "dy"), _cuda(w, torch.bfloat16, "w")
+    tf = _arm(dy, w)
+    dy, w = _cuda(dy, dy.dtype, "dy"), _cuda(w, dy.dtype, "w")
     M, N, K = dy.shape[0], dy.shape[1], w.shape[0]
     _need(w.shape[1] == N, "dy [M,N] and w [K,N] disagree on N")
+    if tf:
+        out = torch.empty(M, K, dtype=torch.float32, device=dy.device)
+        if relu_of is not None:
+            nat.gemm_bf16(dy, 0, w, 0, M, K, N, out, mode=nat.EPI_RELUMASK_F32, bn=64,
+                          relu_mask=_cuda(relu_of, torch.float32, "relu_of"), tf32=True)
+        else:
+            nat.gemm_bf16(dy, 0, w, 0, M, K, N, out, mode=nat.EPI_STORE_F32, bn=64, tf32=True)
+        return out
     if relu_of is not None:
         out = torch.empty(M, K, dtype=torch.bfloat16, device=dy.device)
         nat.gemm_bf16(dy, 0, w, 0, M, K, N, out, mode=nat.EPI_RELUMASK_BF16, bn=64,
@@ -102,38 +133,43 @@ def dense_grad_input(dy: torch.Tensor, w: torch.Tensor, relu_of: Optional[torch.
 
 def dense_grad_weight(x: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
     """d(w) of y = x w: x^T dy, contraction over the batch, both operands read MN-major in place.  fp32 [K,N]."""
-    x, dy = _cuda(x, torch.bfloat16, "x"), _cuda(dy, torch.bfloat16, "dy")
+    tf = _arm(x, dy)
+    x, dy = _cuda(x, x.dtype, "x"), _cuda(dy, x.dtype, "dy")
     _need(x.shape[0] == dy.shape[0], "x and dy must have the same batch")
     K, N, Bsz = x.shape[1], dy.shape[1], x.shape[0]
     out = torch.empty(K, N, dtype=torch.float32, device=x.device)
-    nat.gemm_bf16(x, 1, dy, 1, K, N, Bsz, out, mode=nat.EPI_STORE_F32, bn=128 if N >= 128 else 64)
+    nat.gemm_bf16(x, 1, dy, 1, K, N, Bsz, out, mode=nat.EPI_STORE_F32, bn=128 if N >= 128 else 64, tf32=tf)
     return out
 
 
 def classifier_head(pre: torch.Tensor, hid_bias: torch.Tensor, out_w: torch.Tensor, out_b: torch.Tensor,
-                    labels: torch.Tensor, keep_prob: float = 1.0, seed: int = 0, step: int = 0, training: bool = True):
+                    labels: torch.Tensor, keep_prob: float = 1.0, seed: int = 0, step: int = 0, training: bool = True,
+                    act_dtype=torch.bfloat16):
     """relu(pre + hid_bias) -> dropout(keep_prob) -> @ out_w + out_b -> mean softmax cross entropy with dense labels
-    and accuracy, plus (training) every gradient of that tail.  pre fp32 [B,H].  Returns a dict."""
+    and accuracy, plus (training) every gradient of that tail.  pre fp32 [B,H]; the hidden activation and its gradient
+    come back in ``act_dtype`` (fp32 for the tf32 arm).  Returns a dict."""
     pre = _cuda(pre, torch.float32, "pre")
+    _need(act_dtype in (torch.bfloat16, torch.float32), "act_dtype must be bfloat16 or float32")
+    tf = act_dtype == torch.float32
     B, H = pre.shape
     dev = pre.device
-    hid = torch.empty(B, H, dtype=torch.bfloat16, device=dev)
-    dhid = torch.empty(B, H, dtype=torch.bfloat16, device=dev) if training else None
+    hid = torch.empty(B, H, dtype=act_dtype, device=dev)
+    dhid = torch.empty(B, H, dtype=act_dtype, device=dev) if training else None
     dlogits = torch.empty(B, 10, device=dev)
     loss_row = torch.empty(B, device=dev)
     hit = torch.empty(B, dtype=torch.uint8, device=dev)
     mask = torch.ones(B, H, dtype=torch.uint8, device=dev)
     nat.head_rows(pre, None, _cuda(hid_bias, torch.float32, "hid_bias"), _cuda(out_w, torch.float32, "out_w"),
                   _cuda(out_b, torch.float32, "out_b"), _cuda(labels, torch.float32, "labels"), B, H, H, keep_prob, seed,
-                  step, training, hid, dhid, dlogits, loss_row, hit, mask)
+                  step, training, hid, dhid, dlogits, loss_row, hit, mask, tf32=tf)
     scalars = torch.empty(2, device=dev)
     out = {"hidden": hid, "keep_mask": mask, "dlogits": dlogits}
     if training:
         d_out_w, d_hid_bias, d_out_b = torch.empty(H, 10, device=dev), torch.empty(H, device=dev), torch.empty(10, device=dev)
-        nat.head_cols(hid, dhid, H, dlogits, loss_row, hit, B, H, d_out_w, d_hid_bias, d_out_b, scalars)
+        nat.head_cols(hid, dhid, H, dlogits, loss_row, hit, B, H, d_out_w, d_hid_bias, d_out_b, scalars, tf32=tf)
         out.update(d_hidden=dhid, d_out_w=d_out_w, d_hid_bias=d_hid_bias, d_out_b=d_out_b)
     else:
-        nat.head_cols(None, None, H, dlogits, loss_row, hit, B, H, None, None, None, scalars)
+        nat.head_cols(None, None, H, dlogits, loss_row, hit, B, H, None, None, None, scalars, tf32=tf)
     out["loss"], out["accuracy"] = scalars[0], scalars[1]
     return out
 
