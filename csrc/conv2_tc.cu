@@ -249,10 +249,12 @@ conv2_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 // pixels, and that traffic is what bounds it (~5.5 TB/s aggregate).  Here a tile is 8 columns x 16 rows of one image
 // (accumulator row = h*8 + w) and ONE box {C, 16 w, 20 h} = 40 KB holds the inputs of all 25 taps: the A operand of
 // tap (kh,kw) is the same box read from a start address moved by (kh*16 + kw) rows.  The 8 rows of a core-matrix group
-// are 8 consecutive columns (1024 B contiguous), groups follow at the box's row pitch (SBO = 16 * 128 B), and because
-// the start is moved by kw rows -- not a multiple of the 8-row swizzle pattern -- the descriptor carries the phase of
-// its first row (base offset = kw).  3x less L2 -> SM traffic per tile; the pooling window is still inside one warp
-// (partners at lane ^ 1 and lane ^ 8).
+// are 8 consecutive columns (1024 B contiguous), groups follow at the box's row pitch (SBO = 16 * 128 B).  The start
+// is moved by kw rows, which is not a multiple of the 8-row swizzle pattern; measured on B200: the tensor core derives
+// the swizzle phase from the address bits (as TMA did when it wrote the box), so the descriptor needs NO base offset --
+// with (address >> 7) & 7 in the base-offset field the results are wrong, with 0 they match the oracle.  3x less
+// L2 -> SM traffic per tile (15.7 vs 17.2 us forward, 18.3 vs 19.3 us dgrad on the tf32 arm: the kernels are no longer
+// traffic-bound after it); the pooling window is still inside one warp (partners at lane ^ 1 and lane ^ 8).
 // ------------------------------------------------------------------------------------------------
 template <bool kFwd, int TF>
 struct BoxCfg {
@@ -267,7 +269,7 @@ template <bool kFwd, int TF>
 __global__ void __launch_bounds__(kThreads, 1)
 conv2_box_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const float* __restrict__ bias, void* __restrict__ pool_out_v, unsigned char* __restrict__ amax,
-                 float* __restrict__ dx, int B, int num_tiles, long long dx_plane_stride, int use_base_offset) {
+                 float* __restrict__ dx, int B, int num_tiles, long long dx_plane_stride) {
   static_assert(TF == 1 || !kFwd, "the bf16 forward operand has 64 B rows: it stays on the five-box kernel");
   using C = BoxCfg<kFwd, TF>;
   extern __shared__ uint8_t smem_raw[];
@@ -345,8 +347,7 @@ conv2_box_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int kw = 0; kw < 5; ++kw) {
             // forward: output (h, w) reads box pixel (h + kh, w + kw); dgrad: (h + 4 - kh, w + 4 - kw)
             const int rh = kFwd ? kh : 4 - kh, rw = kFwd ? kw : 4 - kw;
-            uint64_t da_t = desc_advance(da_s, (uint32_t)((rh * 16 + rw) * 128));
-            if (use_base_offset) da_t = desc_with_base_offset(da_t, (uint32_t)rw);
+            const uint64_t da_t = desc_advance(da_s, (uint32_t)((rh * 16 + rw) * 128));
             const uint64_t db_t = desc_advance(db0, (uint32_t)((kh * 5 + kw) * 4096));
 #pragma unroll
             for (int ks = 0; ks < C::kKSteps; ++ks) {
@@ -610,14 +611,10 @@ int num_sms() { return tfd_num_sms(); }
 
 }  // namespace
 
-// TFD_CONV2_BOX: 1 = the one-box kernel where the operand rows are 128 B (tf32 forward / dgrad, bf16 dgrad), 0 = the
-// five-box kernel everywhere.  TFD_CONV2_BO: whether the shifted A descriptors carry a base offset (default 1).
+// TFD_CONV2_BOX: 1 (default) = the one-box kernel where the operand rows are 128 B (tf32 forward / dgrad, bf16 dgrad),
+// 0 = the five-box kernel everywhere.
 static int conv2_box_mode() {
-  static const int v = [] { const char* e = getenv("TFD_CONV2_BOX"); return e ? atoi(e) : 0; }();
-  return v;
-}
-static int conv2_box_bo() {
-  static const int v = [] { const char* e = getenv("TFD_CONV2_BO"); return e ? atoi(e) : 1; }();
+  static const int v = [] { const char* e = getenv("TFD_CONV2_BOX"); return e ? atoi(e) : 1; }();
   return v;
 }
 
@@ -647,7 +644,7 @@ extern "C" int tfd_conv2_fwd(int dtype, const void* in, const void* w, const flo
     if (rc) return rc;
     if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_box_kernel<true, 1>), C::kSmem)) return arc;
     TFD_CUDA_CHECK(tfd_launch(conv2_box_kernel<true, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW, b, pool_out,
-                              argmax, (float*)nullptr, B, tiles, 0LL, conv2_box_bo()));
+                              argmax, (float*)nullptr, B, tiles, 0LL));
   } else if (tf) {
     using C = ConvCfg<true, 1>;
     if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_tc_kernel<true, 1>), C::kSmem)) return arc;
@@ -683,13 +680,12 @@ extern "C" int tfd_conv2_dgrad(int dtype, const void* dy, const void* w, float* 
       if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_box_kernel<false, 1>), C::kSmem)) return arc;
       TFD_CUDA_CHECK(tfd_launch(conv2_box_kernel<false, 1>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW,
                                 (const float*)nullptr, (void*)nullptr, (unsigned char*)nullptr, dx, B, tiles,
-                                (long long)B * 14 * 14 * 32, conv2_box_bo()));
+                                (long long)B * 14 * 14 * 32));
     } else {
       using C = BoxCfg<false, 0>;
       if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_box_kernel<false, 0>), C::kSmem)) return arc;
       TFD_CUDA_CHECK(tfd_launch(conv2_box_kernel<false, 0>, dim3(grid), dim3(kThreads), C::kSmem, st, tmA, tmW,
-                                (const float*)nullptr, (void*)nullptr, (unsigned char*)nullptr, dx, B, tiles, 0LL,
-                                conv2_box_bo()));
+                                (const float*)nullptr, (void*)nullptr, (unsigned char*)nullptr, dx, B, tiles, 0LL));
     }
   } else if (tf) {
     using C = ConvCfg<false, 1>;

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
 
 // conv1 filter gradient: pool/ReLU backward folded in (only the arg-max position of each 2x2 window carries
 // gradient).  One block of 16 warps per image: warp = pixel group, lane = channel; a thread touches at most 13 of the
-// 196 pooled pixels and all its global loads are in flight at once.  512 threads x <= 64 registers and 31 KB of shared
+// 196 pooled pixels and all its global loads are in flight at once.  512 threads x <= 64 registers and 18 KB of shared
 // memory leave room for a conv2 wgrad CTA (192 threads, ~194 KB) on the same SM: the two weight-gradient kernels of
 // the backward tail overlap instead of queueing (a 1024-thread shape owned the whole register file).  dpool arrives as nsplit partial planes (the tf32 conv2 dgrad
 // splits its K over two CTAs) that are added here in plane order.  Reduction without atomics: warps -> shared memory
@@ -176,26 +176,33 @@ __global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restric
   grid_dep_wait();
   grid_dep_launch();
   __shared__ float img[32][33];
-  __shared__ __align__(16) float red[8][26][32];
+  __shared__ __align__(16) float red[4][26][32];  // 13 KB: small enough to sit next to a conv2 wgrad CTA (~194 KB)
   const int n = blockIdx.x;
   const int c = threadIdx.x & 31, grp = threadIdx.x >> 5;  // 16 pixel groups
-  // this thread's pixels: grp, grp+16, ...; all their loads are issued before anything else
+  // this thread's pixels: grp, grp+16, ...  ALL their loads are unconditional and independent of each other (clamped
+  // index, second plane through a pointer that falls back to the first with weight 0), so the compiler issues the 52
+  // loads back to back; with the loads under `if (pix < 196)` / a dynamic plane loop they went out one round trip at a
+  // time and the kernel spent 13 serial L2 latencies (ncu: stall_lg on every use).
   constexpr int kPix = 13;  // ceil(196 / 16)
-  float gq[kPix];
+  const float* plane1 = nsplit > 1 ? dpool + split_stride : dpool;
+  const float w1 = nsplit > 1 ? 1.f : 0.f;
+  float g0[kPix], g1[kPix], pvq[kPix];
   int aq[kPix];
 #pragma unroll
   for (int it = 0; it < kPix; ++it) {
     const int pix = grp + it * 16;
-    gq[it] = 0.f;
-    aq[it] = 0;
-    if (pix < 196) {
-      const long long idx = ((long long)n * 196 + pix) * 32 + c;
-      float g = dpool[idx];
-      if (nsplit > 1) g += dpool[split_stride + idx];
-      for (int sp = 2; sp < nsplit; ++sp) g += dpool[sp * split_stride + idx];
-      gq[it] = (to_f(pool[idx]) > 0.f) ? g : 0.f;
-      aq[it] = amax[idx];
-    }
+    const long long idx = ((long long)n * 196 + (pix < 196 ? pix : 0)) * 32 + c;
+    g0[it] = __ldg(dpool + idx);
+    g1[it] = __ldg(plane1 + idx);
+    pvq[it] = to_f(pool[idx]);
+    aq[it] = amax[idx];
+  }
+  float gq[kPix];
+#pragma unroll
+  for (int it = 0; it < kPix; ++it) {
+    const int pix = grp + it * 16;
+    const float g = g0[it] + w1 * g1[it];
+    gq[it] = (pix < 196 && pvq[it] > 0.f) ? g : 0.f;
   }
   for (int i = threadIdx.x; i < 32 * 32; i += 512) {  // 32 x 32 zero-padded image
     const int r = (i >> 5) - 2, cc = (i & 31) - 2;
@@ -220,11 +227,11 @@ __global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restric
         for (int kw = 0; kw < 5; ++kw) acc[kh * 5 + kw] = fmaf(g, img[h + kh][wq + kw], acc[kh * 5 + kw]);
     }
   }
-  // 16 warps -> 8 rows of `red` in two passes (pass k: warps 8k..8k+7), a fixed order
+  // 16 warps -> 4 rows of `red` in four passes (pass k: warps 4k..4k+3), a fixed order
 #pragma unroll 1
-  for (int pass = 0; pass < 2; ++pass) {
-    if ((grp >> 3) == pass) {
-      const int row = grp & 7;
+  for (int pass = 0; pass < 4; ++pass) {
+    if ((grp >> 2) == pass) {
+      const int row = grp & 3;
       if (pass == 0) {
 #pragma unroll
         for (int t = 0; t < 25; ++t) red[row][t][c] = acc[t];
@@ -243,7 +250,7 @@ __global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restric
     const int t = i >> 5, cc = i & 31;
     float s = 0.f;
 #pragma unroll
-    for (int g8 = 0; g8 < 8; ++g8) s += red[g8][t][cc];
+    for (int g4 = 0; g4 < 4; ++g4) s += red[g4][t][cc];
     __stcg(parts + (size_t)blockIdx.x * 832 + i, s);
   }
   if (!last_block_arrives(counter, gridDim.x)) return;
@@ -301,16 +308,30 @@ __global__ void __launch_bounds__(256) pool2_bwd_kernel(const float* __restrict_
   float pv[4];
   int am[4];
   long long pp[4];
+  // up to 4 partial planes, every load unconditional (clamped pixel, absent planes alias plane 0 with weight 0) so
+  // that all 24 loads of a thread are in flight at once
+  const float* pl_ptr[4];
+  float pl_w[4];
+#pragma unroll
+  for (int sp = 0; sp < 4; ++sp) {
+    pl_ptr[sp] = sp < nsplit ? dpool + sp * split_stride : dpool;
+    pl_w[sp] = sp < nsplit ? 1.f : 0.f;
+  }
+  float gp[4][4];
 #pragma unroll
   for (int it = 0; it < 4; ++it) {
     pp[it] = (long long)blockIdx.x * 16 + it * 4 + pl;
-    const long long idx = pp[it] * 64 + c;
-    g[it] = 0.f; pv[it] = 0.f; am[it] = 0;
-    if (pp[it] < npix) {
-      for (int sp = 0; sp < nsplit; ++sp) g[it] += dpool[sp * split_stride + idx];
-      pv[it] = to_f(pool[idx]);
-      am[it] = amax[idx];
-    }
+    const long long idx = (pp[it] < npix ? pp[it] : 0) * 64 + c;
+#pragma unroll
+    for (int sp = 0; sp < 4; ++sp) gp[it][sp] = __ldg(pl_ptr[sp] + idx);
+    pv[it] = to_f(pool[idx]);
+    am[it] = amax[idx];
+  }
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    g[it] = 0.f;
+#pragma unroll
+    for (int sp = 0; sp < 4; ++sp) g[it] += pl_w[sp] * gp[it][sp];  // plane order: deterministic
   }
 #pragma unroll
   for (int it = 0; it < 4; ++it) {
@@ -715,7 +736,7 @@ extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, in
                                const void* pool_out, const unsigned char* argmax, float* dw, float* db, float* scratch,
                                int B, void* stream) {
   TFD_ACT_CHECK("conv1_wgrad");
-  TFD_REQUIRE(scratch != nullptr && nsplit >= 1, "conv1_wgrad: scratch missing or nsplit %d < 1", nsplit);
+  TFD_REQUIRE(scratch != nullptr && nsplit >= 1 && nsplit <= 2, "conv1_wgrad: scratch missing or nsplit %d not 1 or 2", nsplit);
   const dim3 grid(B);
   // runs next to the conv2 wgrad CTAs (one per SM, ~194 KB of shared memory): ask for the same carve-out
   tfd_prefer_max_carveout(reinterpret_cast<const void*>(conv1_wgrad_kernel<float>));
@@ -733,7 +754,7 @@ extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, in
 extern "C" int tfd_pool2_bwd(int dtype, const float* dpool, int nsplit, long long split_stride, const void* pool_out,
                              const unsigned char* argmax, void* dy, float* db, float* scratch, int B, void* stream) {
   TFD_ACT_CHECK("pool2_bwd");
-  TFD_REQUIRE(scratch != nullptr, "pool2_bwd: scratch missing");
+  TFD_REQUIRE(scratch != nullptr && nsplit <= 4, "pool2_bwd: scratch missing or more than 4 partial planes (%d)", nsplit);
   const long long npix = (long long)B * 49;
   const dim3 grid((unsigned)((npix + 15) / 16));
   if (dtype == TFD_DTYPE_TF32)

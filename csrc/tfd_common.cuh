@@ -198,13 +198,6 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
   return d;
 }
 
-// Descriptor of an operand whose start address is 128 B- but not pattern-aligned (a row offset that is not a multiple
-// of 8 rows inside a 128 B-swizzled box): bits 49..51 carry the phase of the first row inside the 1024 B swizzle
-// pattern, (start address >> 7) & 7.
-__device__ __forceinline__ uint64_t desc_with_base_offset(uint64_t d, uint32_t phase) {
-  return (d & ~((uint64_t)7 << 49)) | ((uint64_t)(phase & 7) << 49);
-}
-
 // the same descriptor with its start address moved by `bytes` (a multiple of 16; the result stays below 256 KB)
 __device__ __forceinline__ uint64_t desc_advance(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
 
