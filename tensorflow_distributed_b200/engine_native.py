@@ -326,7 +326,7 @@ class NativeEngine:
 
     def _side_streams(self):
         if not hasattr(self, "_sides"):
-            self._sides = [torch.cuda.Stream(device=self.device) for _ in range(2)]
+            self._sides = [torch.cuda.Stream(device=self.device) for _ in range(3)]
         return self._sides
 
     def _cnn_backward(self, ws: Workspace) -> None:

@@ -32,13 +32,18 @@ def backward(eng, ws: Workspace) -> None:
     head -> fc1 dgrad -> pool2 bwd -> conv2 dgrad -> conv1 wgrad."""
     B, tf = ws.B, eng.tf32
     main = torch.cuda.current_stream()
-    s1, s2 = eng._side_streams()
+    s1, s2, s3 = eng._side_streams()
+    # Two independent leaves right behind the head's row phase, each on its own branch: the fc1 weight gradient (200
+    # CTAs) runs under fc1 dgrad / pool2 backward and is gone before conv2 dgrad needs whole SMs -- queued behind the
+    # 14 us head_cols kernel it used to start just in front of conv2 dgrad and delay it by 5 us.
     s1.wait_stream(main)
+    s3.wait_stream(main)
     with torch.cuda.stream(s1):
-        nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, eng.G("weights/out"),
-                      eng.G("biases/bd1"), eng.G("biases/out"), ws.scalars, tf32=tf)
         # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
         eng.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
+    with torch.cuda.stream(s3):
+        nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, eng.G("weights/out"),
+                      eng.G("biases/bd1"), eng.G("biases/out"), ws.scalars, tf32=tf)
     # fc1 dgrad: dpool2[B,3136] = dhid wd1^T (wd1 read K-major in place), split-K partial planes summed by the
     # pool2 / ReLU backward kernel
     eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
@@ -53,3 +58,4 @@ def backward(eng, ws: Workspace) -> None:
                     tf32=tf, nsplit=ws.dp1_splits, split_stride=B * 14 * 14 * 32)
     main.wait_stream(s1)
     main.wait_stream(s2)
+    main.wait_stream(s3)
