@@ -640,6 +640,15 @@ extern "C" int tfd_pull_params(const float* src, float* dst, long long n, const 
   return tfd_pull_multi(s, d, ns, v, 1, version, nullptr, stream);
 }
 
+// Plain asynchronous copy (cudaMemcpyAsync, kind default: the driver sees a peer-mapped source and uses the copy
+// engines over NVLink).  The worker's prefetch of a big matrix from its owner shards goes through here: no SM is
+// involved, so the transfer really overlaps the conv layers that own every SM while it runs, and it is a memcpy node
+// in the captured step graph.  One call per copy.
+extern "C" int tfd_memcpy_async(void* dst, const void* src, size_t bytes, void* stream) {
+  TFD_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ST(stream)));
+  return 0;
+}
+
 // ---- symmetric heap over cudaIpc ----
 extern "C" int tfd_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out64) {
   TFD_CUDA_CHECK(cudaMalloc(dev_ptr, bytes));

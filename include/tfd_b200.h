@@ -324,6 +324,9 @@ int tfd_nvls_gate(const unsigned* version, const unsigned* step, unsigned per_st
 int tfd_nvls_signal(unsigned* mc_arrive, unsigned* step, void* stream);
 
 /* ---- peer memory (symmetric heap over cudaIpc) ---- */
+/* cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault): copy-engine transfer (src may be peer-mapped); used for the
+ * worker's prefetch of a big matrix from its owner shards so that no SM is spent on it. */
+int tfd_memcpy_async(void* dst, const void* src, size_t bytes, void* stream);
 int tfd_set_device(int device);
 int tfd_ipc_alloc(size_t bytes, void** dev_ptr, void* handle_out64);    /* cudaMalloc + cudaIpcGetMemHandle */
 int tfd_ipc_open(const void* handle64, void** dev_ptr);                  /* cudaIpcOpenMemHandle             */

@@ -36,18 +36,19 @@ def backward(eng, ws: Workspace) -> None:
     # Two independent leaves right behind the head's row phase, each on its own branch: the fc1 weight gradient (200
     # CTAs) runs under fc1 dgrad / pool2 backward and is gone before conv2 dgrad needs whole SMs -- queued behind the
     # 14 us head_cols kernel it used to start just in front of conv2 dgrad and delay it by 5 us.
-    s1.wait_stream(main)
-    s3.wait_stream(main)
+    ready = main.record_event()  # head_rows done: dhid / hid / dlogits exist
+    # fc1 dgrad FIRST in capture order (critical path; dpool2[B,3136] = dhid wd1^T, wd1 read K-major in place, split-K
+    # partial planes summed by the pool2 / ReLU backward kernel), then the two leaves on their branches
+    eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
+                   split_stride=B * 3136, ld_out=3136)
+    s1.wait_event(ready)
+    s3.wait_event(ready)
     with torch.cuda.stream(s1):
         # fc1 wgrad: dW[3136,1024] = pool2^T dhid   (both operands MN-major, K = batch)
         eng.gemm_wgrad("weights/wd1", ws.pool2.view(B, 3136), ws.dhid, B, bn=128)
     with torch.cuda.stream(s3):
         nat.head_cols(ws.hid, ws.dhid, 1024, ws.dlogits, ws.loss_row, ws.hit, B, 1024, eng.G("weights/out"),
                       eng.G("biases/bd1"), eng.G("biases/out"), ws.scalars, tf32=tf)
-    # fc1 dgrad: dpool2[B,3136] = dhid wd1^T (wd1 read K-major in place), split-K partial planes summed by the
-    # pool2 / ReLU backward kernel
-    eng.gemm_dgrad("weights/wd1", ws.dhid, B, ws.dpool2, mode=nat.EPI_STORE_F32, bn=64, splits=ws.dg_splits,
-                   split_stride=B * 3136, ld_out=3136)
     nat.pool2_bwd(ws.dpool2, ws.pool2, ws.am2, ws.dy2, eng.G("biases/bc2"), ws.p2b_scratch, B, nsplit=ws.dg_splits,
                   split_stride=B * 3136, tf32=tf)
     s2.wait_stream(main)

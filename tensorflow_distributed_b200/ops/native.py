@@ -419,6 +419,12 @@ def pull_multi_tag(srcs, dsts, ns, versions, want_segs, tag_seg: int, tag_out) -
     _count()
 
 
+def memcpy_async(dst: int, src: int, nbytes: int) -> None:
+    """Copy-engine transfer on the current stream (src may be a peer-mapped address); a memcpy node under capture."""
+    _check(lib().tfd_memcpy_async(c_void_p(int(dst)), c_void_p(int(src)), c_size_t(int(nbytes)), _stream()),
+           "tfd_memcpy_async")
+
+
 # ---- symmetric heap ----
 def ipc_alloc(nbytes: int):
     ptr = c_void_p()

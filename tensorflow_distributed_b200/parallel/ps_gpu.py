@@ -530,6 +530,14 @@ class GpuClusterEngine(NativeEngine):
             elif self.async_mode:
                 nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
                                      [self.ctrl.data_ptr() + 4 * (WCTRL_MYTICKET + s[4]) for s in p])
+            elif self.v2 and os.environ.get("TFD_PREFETCH", "ce") == "ce":
+                # strict sync: a one-block gate on the LOCAL version words of the owner shards, then one copy-engine
+                # transfer per shard piece.  A copy kernel lost its SMs to conv2 (one CTA per SM) and finished late
+                # (8 GPUs: 42 us, on the critical path of the fc1 GEMM); the copy engines run under the conv layers.
+                nat.gate_flags(sorted({s[3] for s in p}), self.step_ptr())
+                esz4 = 4  # segment lengths are counted in fp32 words
+                for src, dst, n, _ver, _shard in p:
+                    nat.memcpy_async(dst, src, n * esz4)
             else:
                 nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
                                want_ptr=self.step_ptr())

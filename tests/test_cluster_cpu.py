@@ -1,5 +1,6 @@
 """Config 2: 1 ps + 2 workers as three OS processes on CPU/gloo, launched like m / w1 / w2."""
 import os
+import re
 import subprocess
 import sys
 
@@ -187,5 +188,9 @@ def test_existing_servers_attach_to_a_server_that_outlives_its_clients(free_port
     for t, o in enumerate(outs2):
         assert "Using existing server at: grpc://127.0.0.1:%d" % (free_port + 1 + t) in o
         assert "Worker %d: attached to running servers at global step 3" % t in o
-        assert "training step 1 done (global step: 4)" in o and "(global step: 6)" in o
-        assert 3 <= o.count(": training step") <= 4  # (the default token preload lets a worker run one step ahead)
+        # the counter a worker reads after its first push may already hold the other worker's push, so only the
+        # order-independent facts are checked
+        first_gs = int(re.search(r"training step 1 done \(global step: (\d+)\)", o).group(1))
+        assert first_gs in (3, 4, 5), o  # 3: ran on a preloaded token before the first update landed
+        assert "After 6 training step(s)" in o
+        assert 3 <= o.count(": training step") <= 6  # (preloaded tokens let a worker run ahead of the update)
