@@ -14,6 +14,9 @@ KERNELS = {  # output file -> regex on the mangled name (templates: ...IL<type>.
     "conv2_fwd_bf16.sass": r"conv2_tc_kernelILb1ELi0E",
     "conv2_dgrad_tf32.sass": r"conv2_tc_kernelILb0ELi1E",
     "conv2_dgrad_bf16.sass": r"conv2_tc_kernelILb0ELi0E",
+    "conv2_box_fwd_tf32.sass": r"conv2_box_kernelILb1ELi1E",
+    "conv2_box_dgrad_tf32.sass": r"conv2_box_kernelILb0ELi1E",
+    "conv2_box_dgrad_bf16.sass": r"conv2_box_kernelILb0ELi0E",
     "conv2_wgrad_tf32.sass": r"conv2_wgrad_tc_kernelILi1E",
     "conv2_wgrad_bf16.sass": r"conv2_wgrad_tc_kernelILi0E",
     "gemm_fc1_fwd_kA_mnB_bn64_tf32.sass": r"gemm_tc_kernelILi0ELi1ELi64ELi1E",
