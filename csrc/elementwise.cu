@@ -97,6 +97,10 @@ struct GateList {
   unsigned want_mul;  // a flag must reach want_mul * *want_ptr (the multicast transport counts one version per shard)
 };
 
+// Phase stamps of the most recent conv1 forward on this GPU (globaltimer ns): [0] block (0,0) starts, [1] its gate
+// has passed, [2] it is done.  Read with tfd_debug_conv1_stamps.
+__device__ unsigned long long g_conv1_stamps[4];
+
 template <typename T>
 __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict__ x, const float* w, const float* b,
                                                         T* __restrict__ out, unsigned char* __restrict__ amax,
@@ -105,6 +109,8 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
   grid_dep_launch();
   __shared__ __align__(16) float patch[18][32];  // input rows 14*half-2 .. +17, cols -2 .. 29
   const int n = blockIdx.x, half = blockIdx.y;
+  const bool stamp = n == 0 && half == 0 && threadIdx.x == 0;
+  if (stamp) g_conv1_stamps[0] = globaltimer_ns();
   for (int i = threadIdx.x; i < 18 * 32; i += blockDim.x) {
     const int pr = i >> 5, pc = i & 31;
     const int r = 14 * half - 2 + pr, c = pc - 2;
@@ -117,6 +123,7 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
     if ((int)threadIdx.x < gate.n)
       spin_until_ge(gate.flag[threadIdx.x], gate.want_mul * *gate.want_ptr, "conv1: parameter version");
     __syncthreads();
+    if (stamp) g_conv1_stamps[1] = globaltimer_ns();
 #pragma unroll
     for (int t = 0; t < 25; ++t) wr[t] = __ldcg(w + t * 32 + c);  // the mirror was written by another GPU: read at L2
     bias = __ldcg(b + c);
@@ -157,7 +164,9 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
     out[o] = from_f<T>(best);
     amax[o] = (unsigned char)bi;
   }
+  if (stamp) g_conv1_stamps[2] = globaltimer_ns();
 }
+
 
 // conv1 filter gradient: pool/ReLU backward folded in (only the arg-max position of each 2x2 window carries
 // gradient).  One block of 16 warps per image: warp = pixel group, lane = channel; a thread touches at most 13 of the
@@ -686,6 +695,11 @@ __global__ void zero_multi_kernel(const __grid_constant__ ZeroTable t) {
 }
 
 }  // namespace
+
+extern "C" int tfd_debug_conv1_stamps(unsigned long long* out4) {
+  TFD_CUDA_CHECK(cudaMemcpyFromSymbol(out4, g_conv1_stamps, sizeof(g_conv1_stamps)));
+  return 0;
+}
 
 #define ST(s) static_cast<cudaStream_t>(s)
 

@@ -67,6 +67,11 @@ __device__ __forceinline__ float4 load_grad4(const float* slot, long long i, int
                      __uint_as_float(r.y & 0xffff0000u));
 }
 
+// Phase stamps of the most recent Adam kernel on this GPU (globaltimer ns; a handful of stores by one thread):
+// [0] block 0 starts, [1] arrive signals issued, [2] all arrivals seen, [3] block 0 leaves the update loop,
+// [4] the last block sees every block done, [5] version words released.  Read with tfd_debug_adam_stamps.
+__device__ unsigned long long g_adam_stamps[8];
+
 __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __grid_constant__ PieceTable pt,
                                                          const __grid_constant__ PubTable pub) {
   grid_dep_wait();
@@ -74,10 +79,11 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   // Colocated strict sync: this rank's worker half signals "my gradients are in your slots" to every shard from here
   // (the gradient kernels of this step ran earlier in the same stream and stored straight into the owners' slots), so
   // no stand-alone push kernel exists.  One thread per shard: the NVLink round trips of the releases overlap.
-  if (blockIdx.x == 0 && (int)threadIdx.x < a.n_signal) {
-    __threadfence_system();
-    red_add_release_sys_u32(a.signal_arrive[threadIdx.x], 1u);
-  }
+  const bool stamp = blockIdx.x == 0 && threadIdx.x == 0;
+  if (stamp) g_adam_stamps[0] = globaltimer_ns();
+  // (the gradient stores belong to kernels that have completed; the release of the reduction is the only fence)
+  if (blockIdx.x == 0 && (int)threadIdx.x < a.n_signal) red_add_release_sys_u32(a.signal_arrive[threadIdx.x], 1u);
+  if (stamp) g_adam_stamps[1] = globaltimer_ns();
   // Every thread derives the step index and lr_t itself (one broadcast load + a few SFU ops): no block barrier
   // and no serial prologue in front of the streaming loop.  Only one thread per block waits for the arrivals.
   const unsigned t = a.t_counter[0] + 1;  // this update's 1-based index
@@ -85,6 +91,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
     if (threadIdx.x == 0) spin_until_ge(a.wait_counter, (unsigned)a.num_slots * t, "adam: gradient arrivals");
     __syncthreads();
   }
+  if (stamp) g_adam_stamps[2] = globaltimer_ns();
   // backup workers (R of N): only the slots named in the mask are summed, the average is over their count; an empty
   // mask means the ps is being released
   unsigned use_mask = 0xffffffffu;
@@ -130,6 +137,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
   const float* g0 = serve_slot ? serve_slot : a.slots[first];
   const int nslots = serve_slot ? 1 : a.num_slots;
   int cur = 0;  // cached piece index for the shadow lookup
+  int stored_remote = 0;  // this thread has written into another GPU's mirror
   for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += 2 * stride4) {
     const long long j0 = i4, j1 = i4 + stride4;
     long long idx[2] = {j0 << 2, j1 << 2};
@@ -196,6 +204,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
           // whole float4 groups, so the tail of a 10-element bias needs no special case)
           if (pub.nworkers > 0) {
             const PubPiece& pp = pub.pc[cur];
+            stored_remote |= (pp.f32_off >= 0) | (pp.b16_off >= 0);
             if (pp.f32_off >= 0) {
               const float4 o4 = make_float4(wv[0], wv[1], wv[2], wv[3]);
               for (int wk = 0; wk < pub.nworkers; ++wk)
@@ -221,31 +230,34 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
       }
     }
   }
-  // publish: last block bumps the counters and releases the new parameter version.  One fence per block (the
-  // barrier orders every thread's stores before it; system scope because mirrors live on other GPUs).
-  __syncthreads();
+  // publish: the last block bumps the counters and releases the new parameter version.  One fence per block (the
+  // barrier orders every thread's stores before it): system scope only in a block that stored into another GPU's
+  // mirror -- it has to see those stores acknowledged over NVLink -- and GPU scope otherwise (arena, moments and
+  // shadow live in this GPU's L2, which is also where a peer's loads and copies read them).
+  const int any_remote = __syncthreads_or(stored_remote);
   __shared__ unsigned s_last;
+  if (stamp) g_adam_stamps[3] = globaltimer_ns();
   if (threadIdx.x == 0) {
-    if (pub.nworkers > 0) __threadfence_system(); else __threadfence();
+    if (any_remote) __threadfence_system(); else __threadfence();
     const unsigned done = atomicAdd(&a.t_counter[1], 1u);
     s_last = (done == gridDim.x - 1) ? 1u : 0u;
     if (s_last) {
+      g_adam_stamps[4] = globaltimer_ns();
       a.t_counter[1] = 0;
       a.t_counter[0] = t;
       if (a.queue) a.queue[(t - 1) % (unsigned)a.qlen] = 0;
       if (a.global_step) *a.global_step = *a.global_step + 1;
       if (a.local_step) *a.local_step = *a.local_step + 1;
-      __threadfence_system();
-      if (a.version_flag) st_release_sys_u32(a.version_flag, t);
     }
   }
-  if (pub.nworkers > 0) {
-    __syncthreads();
-    // one thread per worker: the release stores' round trips overlap
-    if (s_last && (int)threadIdx.x < pub.nworkers) {
-      __threadfence_system();
-      st_release_sys_u32(pub.wver[threadIdx.x], t);
-    }
+  __syncthreads();
+  // Releases by separate threads of the last block, so their fences and NVLink round trips overlap: thread k < nworkers
+  // stores worker k's version word, thread nworkers the shard's own.  Each is a release at system scope issued after
+  // the barrier behind thread 0's bookkeeping and its observation that every block had fenced and counted itself.
+  if (s_last) {
+    if ((int)threadIdx.x < pub.nworkers) st_release_sys_u32(pub.wver[threadIdx.x], t);
+    if ((int)threadIdx.x == pub.nworkers && a.version_flag) st_release_sys_u32(a.version_flag, t);
+    if ((int)threadIdx.x == pub.nworkers) g_adam_stamps[5] = globaltimer_ns();
   }
 }
 
@@ -361,6 +373,11 @@ __global__ void __launch_bounds__(256) pull_kernel(const __grid_constant__ PullT
 }
 
 }  // namespace
+
+extern "C" int tfd_debug_adam_stamps(unsigned long long* out8) {
+  TFD_CUDA_CHECK(cudaMemcpyFromSymbol(out8, g_adam_stamps, sizeof(g_adam_stamps)));
+  return 0;
+}
 
 #define ST(s) static_cast<cudaStream_t>(s)
 

@@ -323,6 +323,12 @@ int tfd_nvls_apply(float* w, float* m, float* v, const float* mc_grad, float* mc
 int tfd_nvls_gate(const unsigned* version, const unsigned* step, unsigned per_step, unsigned base, void* stream);
 int tfd_nvls_signal(unsigned* mc_arrive, unsigned* step, void* stream);
 
+/* ---- diagnostics: globaltimer phase stamps of the most recent Adam / conv1-forward kernel on the current GPU ----
+ * adam: [0] start, [1] arrive signals issued, [2] arrivals complete, [3] block 0 done updating, [4] all blocks done,
+ * [5] versions released.  conv1: [0] block (0,0) start, [1] gate passed, [2] done. */
+int tfd_debug_adam_stamps(unsigned long long* out8);
+int tfd_debug_conv1_stamps(unsigned long long* out4);
+
 /* ---- peer memory (symmetric heap over cudaIpc) ---- */
 /* cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault): copy-engine transfer (src may be peer-mapped); used for the
  * worker's prefetch of a big matrix from its owner shards so that no SM is spent on it. */

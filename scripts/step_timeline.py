@@ -44,23 +44,38 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
         flush.fill_(1.0)
         eng.train_step_resident(ws, KEEP)
     torch.cuda.synchronize()
+from tensorflow_distributed_b200.ops import native as nat  # noqa: E402
+adam_s, conv1_s = nat.debug_stamps()  # phase stamps of the last step's Adam / conv1 kernels (this GPU's globaltimer)
 if world > 1:
     dist.barrier()
-if rank != 0:
-    eng.shutdown()
-    sys.exit(0)
-out = os.path.join("gpurun_out", "step_trace.json")
+out = os.path.join("gpurun_out", "step_trace_rank%d.json" % rank)
 prof.export_chrome_trace(out)
-ev = [e for e in json.load(open(out))["traceEvents"] if e.get("cat") == "kernel"]
+ev = [e for e in json.load(open(out))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy")]
+os.remove(out)
 ev.sort(key=lambda e: e["ts"])
 # last step = kernels after the last fill kernel
 idx = max(i for i, e in enumerate(ev) if "fill" in e["name"].lower() or "FillFunctor" in e["name"])
 step = ev[idx + 1:]
 t0 = step[0]["ts"]
-print("%-52s %6s %8s %8s %8s" % ("kernel", "stream", "start", "end", "dur"))
+lines = ["%-52s %6s %8s %8s %8s" % ("kernel", "stream", "start", "end", "dur")]
 for e in step:
     name = e["name"].replace("(anonymous namespace)::", "").split("(")[0][:52]
-    print("%-52s %6s %8.1f %8.1f %8.1f" % (name, e["args"].get("stream", "?"), e["ts"] - t0, e["ts"] + e["dur"] - t0, e["dur"]))
-print("step span: %.1f us" % (step[-1]["ts"] + step[-1]["dur"] - t0))
+    lines.append("%-52s %6s %8.1f %8.1f %8.1f" % (name, e["args"].get("stream", "?"), e["ts"] - t0,
+                                                  e["ts"] + e["dur"] - t0, e["dur"]))
+lines.append("step span: %.1f us" % (max(e["ts"] + e["dur"] for e in step) - t0))
+us = lambda a, b: (b - a) / 1e3
+lines.append("conv1 phases (us): gate wait %.1f, compute %.1f" % (us(conv1_s[0], conv1_s[1]) if conv1_s[1] > conv1_s[0] else 0.0,
+                                                               us(max(conv1_s[0], conv1_s[1]), conv1_s[2])))
+lines.append("adam phases (us): signal %.1f, wait for arrivals %.1f, block-0 update %.1f, all blocks done at %.1f, "
+             "release %.1f, total %.1f; conv1 start -> adam start %.1f"
+             % (us(adam_s[0], adam_s[1]), us(adam_s[1], adam_s[2]), us(adam_s[2], adam_s[3]), us(adam_s[0], adam_s[4]),
+                us(adam_s[4], adam_s[5]) if adam_s[5] > adam_s[4] else 0.0, us(adam_s[0], max(adam_s[4], adam_s[5])),
+                us(conv1_s[0], adam_s[0])))
+# every rank leaves its own timeline (which rank is late decides how long the others' Adam kernels wait); rank 0 prints
+with open(os.path.join("gpurun_out", "timeline_%dgpu_rank%d.txt" % (world, rank)), "w") as f:
+    f.write("\n".join(lines) + "\n")
+if rank == 0:
+    print("\n".join(lines))
 if world > 1:
+    dist.barrier()
     eng.shutdown()

@@ -419,6 +419,15 @@ def pull_multi_tag(srcs, dsts, ns, versions, want_segs, tag_seg: int, tag_out) -
     _count()
 
 
+def debug_stamps():
+    """(adam[8], conv1[4]) globaltimer stamps of the last Adam / conv1-forward kernel on the current GPU (synchronises)."""
+    import ctypes
+    a, c = (ctypes.c_ulonglong * 8)(), (ctypes.c_ulonglong * 4)()
+    _check(lib().tfd_debug_adam_stamps(a), "tfd_debug_adam_stamps")
+    _check(lib().tfd_debug_conv1_stamps(c), "tfd_debug_conv1_stamps")
+    return list(a), list(c)
+
+
 def memcpy_async(dst: int, src: int, nbytes: int) -> None:
     """Copy-engine transfer on the current stream (src may be a peer-mapped address); a memcpy node under capture."""
     _check(lib().tfd_memcpy_async(c_void_p(int(dst)), c_void_p(int(src)), c_size_t(int(nbytes)), _stream()),

@@ -482,6 +482,11 @@ class GpuClusterEngine(NativeEngine):
         # update this step builds on (which also means my slots have been consumed and may be overwritten)
         nat.conv1_fwd(ws.x, self.P("weights/wc1"), self.P("biases/bc1"), ws.pool1, ws.am1, ws.B, tf32=self.tf32,
                       gate_flags=self._gate, want_ptr=self.step_ptr())
+        if getattr(self, "_pf_local", None):  # the device-local part of the prefetch goes behind conv1, under conv2
+            main = torch.cuda.current_stream()
+            self._pf_stream.wait_stream(main)
+            with torch.cuda.stream(self._pf_stream):
+                self._issue_local_prefetch()
 
     def _pre_step(self, ws, training: bool) -> None:
         """Pull (X1).  v2: nothing to copy -- the owners have already stored the small parameters into my mirror; only
@@ -519,6 +524,7 @@ class GpuClusterEngine(NativeEngine):
         main = torch.cuda.current_stream()
         if not hasattr(self, "_pf_stream"):
             self._pf_stream = torch.cuda.Stream(device=self.device)
+            self._pf_branches, self._pf_used, self._pf_local = [], 0, []
         self._pf_stream.wait_stream(main)
         p = self._prefetch
         with torch.cuda.stream(self._pf_stream):
@@ -532,20 +538,42 @@ class GpuClusterEngine(NativeEngine):
                                      [self.ctrl.data_ptr() + 4 * (WCTRL_MYTICKET + s[4]) for s in p])
             elif self.v2 and os.environ.get("TFD_PREFETCH", "ce") == "ce":
                 # strict sync: a one-block gate on the LOCAL version words of the owner shards, then one copy-engine
-                # transfer per shard piece.  A copy kernel lost its SMs to conv2 (one CTA per SM) and finished late
-                # (8 GPUs: 42 us, on the critical path of the fc1 GEMM); the copy engines run under the conv layers.
+                # transfer per remote shard piece, each on its own graph branch (a peer copy takes ~7 us to start; in
+                # one stream seven of them would queue up).  A copy kernel lost its SMs to conv2 (one CTA per SM) and
+                # finished late (8 GPUs: 42 us, on the critical path of the fc1 GEMM); copy engines need no SM.
                 nat.gate_flags(sorted({s[3] for s in p}), self.step_ptr())
-                esz4 = 4  # segment lengths are counted in fp32 words
-                for src, dst, n, _ver, _shard in p:
-                    nat.memcpy_async(dst, src, n * esz4)
+                gated = self._pf_stream.record_event()
+                mine = self.my_shard if self.is_ps else -1
+                remote = [s for s in p if s[4] != mine]
+                while len(self._pf_branches) < len(remote):
+                    self._pf_branches.append(torch.cuda.Stream(device=self.device))
+                for br, (src, dst, n, _ver, _shard) in zip(self._pf_branches, remote):
+                    br.wait_event(gated)
+                    with torch.cuda.stream(br):
+                        nat.memcpy_async(dst, src, n * 4)  # piece lengths are counted in fp32 words
+                self._pf_used = len(remote)
+                # my own shard's piece is a device-local copy, which the driver runs as a kernel: next to conv1 it
+                # took that kernel's SMs (conv1 17 us instead of 9), so the CNN issues it behind conv1 (conv1_fwd)
+                self._pf_local = [s for s in p if s[4] == mine]
+                if self.spec.kind != "cnn":
+                    self._issue_local_prefetch()
             else:
                 nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
                                want_ptr=self.step_ptr())
         self._pf_pending = True
 
+    def _issue_local_prefetch(self) -> None:
+        for src, dst, n, _ver, _shard in self._pf_local:
+            nat.memcpy_async(dst, src, n * 4)
+        self._pf_local = []
+
     def _join_prefetch(self) -> None:
         if getattr(self, "_pf_pending", False):
-            torch.cuda.current_stream().wait_stream(self._pf_stream)
+            main = torch.cuda.current_stream()
+            main.wait_stream(self._pf_stream)
+            for br in self._pf_branches[:self._pf_used]:
+                main.wait_stream(br)
+            self._pf_used = 0
             self._pf_pending = False
 
     def _post_backward(self, ws) -> None:

@@ -238,3 +238,17 @@ def test_train_step_back_to_back_feeds_the_batch_it_was_given():
     for i, (x, y) in enumerate(seen):
         assert torch.equal(x.cpu(), torch.from_numpy(xs[i])), "step %d trained on another batch" % i
         assert torch.equal(y.cpu(), torch.from_numpy(ys[i]))
+
+
+def test_phase_stamps_of_the_last_step_are_ordered():
+    """The Adam and conv1-forward kernels leave globaltimer stamps of their phases (diagnostics for the multi-GPU
+    protocol: how long a step waits for arrivals / for the parameter version); on one GPU they must be monotone and the
+    Adam kernel must come after the conv1 forward of the same step."""
+    from tensorflow_distributed_b200.ops import native as nat
+    eng = _engine(cnn_spec(), seed=0, init_stddev=0.05, device="cuda:0")
+    x, y = _batch(128)
+    for _ in range(3):
+        eng.train_step(x.numpy(), y.numpy(), 0.75)
+    adam, conv1 = nat.debug_stamps()
+    assert 0 < conv1[0] <= conv1[2] < adam[0] <= adam[1] <= adam[2] <= adam[3]
+    assert adam[4] >= adam[2] and (adam[4] - adam[0]) < 5_000_000  # an Adam kernel of ~10 us, not milliseconds
