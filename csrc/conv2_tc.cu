@@ -730,10 +730,14 @@ extern "C" int tfd_conv2_wgrad(int dtype, const void* in, const void* dy, float*
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (tf) {
     if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel<1>), WgCfg<1>::kSmem)) return arc;
+    // 194 KB alone would put the SM at the 196 KB carve-out; at the largest one a conv1-wgrad block (18.5 KB) fits next to it
+    tfd_prefer_max_carveout(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel<1>));
     TFD_CUDA_CHECK(tfd_launch(conv2_wgrad_tc_kernel<1>, dim3(chunks, 7), dim3(kThreads), WgCfg<1>::kSmem, st, tmIn, tmDy, dw,
                               scratch, tiles));
   } else {
     if (int arc = tfd_ensure_dyn_smem(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel<0>), WgCfg<0>::kSmem)) return arc;
+    // 194 KB alone would put the SM at the 196 KB carve-out; at the largest one a conv1-wgrad block (18.5 KB) fits next to it
+    tfd_prefer_max_carveout(reinterpret_cast<const void*>(conv2_wgrad_tc_kernel<0>));
     TFD_CUDA_CHECK(tfd_launch(conv2_wgrad_tc_kernel<0>, dim3(chunks, 7), dim3(kThreads), WgCfg<0>::kSmem, st, tmIn, tmDy, dw,
                               scratch, tiles));
   }

@@ -176,22 +176,35 @@ __global__ void __launch_bounds__(224) conv1_fwd_kernel(const float* __restrict_
 // splits its K over two CTAs) that are added here in plane order.  Reduction without atomics: warps -> shared memory
 // in four fixed passes -> one partial [26][32] per image in `scratch` -> the last block to finish sums the images'
 // partials in a fixed order and writes dw / db (which may be staging slots on another GPU).
-// scratch = 16 counter words + B * 832 floats, zeroed once by the caller.
+// scratch = 16 counter words + (B + 15) * 832 floats (tfd_conv1_wgrad_scratch_floats), zeroed once by the caller.
 template <typename T>
-__global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
+__global__ void __launch_bounds__(512, 2) conv1_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dpool,
                                                           int nsplit, long long split_stride, const T* __restrict__ pool,
                                                           const unsigned char* __restrict__ amax, float* __restrict__ dw,
-                                                          float* __restrict__ db, float* __restrict__ scratch, int B) {
+                                                          float* __restrict__ db, float* __restrict__ scratch, int B,
+                                                          int gsz) {
   grid_dep_wait();
   grid_dep_launch();
-  __shared__ float img[32][33];
+  // row stride 34: a warp holds the 32 channels of ONE pooled pixel, whose argmax picks one of the four positions of
+  // its 2x2 window -- with 34 words per row those four land in four different banks (offsets 0, 1, 34, 35), with 33
+  // two of them shared a bank and every LDS of the tap loop was a two-way conflict
+  __shared__ float img[32][34];
   __shared__ __align__(16) float red[4][26][32];  // 13 KB: small enough to sit next to a conv2 wgrad CTA (~194 KB)
   const int n = blockIdx.x;
   const int c = threadIdx.x & 31, grp = threadIdx.x >> 5;  // 16 pixel groups
-  // this thread's pixels: grp, grp+16, ...  ALL their loads are unconditional and independent of each other (clamped
-  // index, second plane through a pointer that falls back to the first with weight 0), so the compiler issues the 52
-  // loads back to back; with the loads under `if (pix < 196)` / a dynamic plane loop they went out one round trip at a
-  // time and the kernel spent 13 serial L2 latencies (ncu: stall_lg on every use).
+  // the image first (two loads per thread), then this thread's pixels: grp, grp+16, ...  ALL loads are unconditional
+  // and independent of each other (clamped index, second plane through a pointer that falls back to the first with
+  // weight 0), so the compiler issues the 54 loads back to back; with the loads under `if (pix < 196)` / a dynamic
+  // plane loop they went out one round trip at a time and the kernel spent 13 serial L2 latencies.
+  float xv[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int i = threadIdx.x + k * 512;
+    const int r = (i >> 5) - 2, cc = (i & 31) - 2;
+    const bool in = r >= 0 && r < 28 && cc >= 0 && cc < 28;
+    xv[k] = __ldg(x + (long long)n * 784 + (in ? r * 28 + cc : 0));
+    if (!in) xv[k] = 0.f;
+  }
   constexpr int kPix = 13;  // ceil(196 / 16)
   const float* plane1 = nsplit > 1 ? dpool + split_stride : dpool;
   const float w1 = nsplit > 1 ? 1.f : 0.f;
@@ -206,16 +219,17 @@ __global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restric
     pvq[it] = to_f(pool[idx]);
     aq[it] = amax[idx];
   }
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {  // 32 x 32 zero-padded image
+    const int i = threadIdx.x + k * 512;
+    img[i >> 5][i & 31] = xv[k];
+  }
   float gq[kPix];
 #pragma unroll
   for (int it = 0; it < kPix; ++it) {
     const int pix = grp + it * 16;
     const float g = g0[it] + w1 * g1[it];
     gq[it] = (pix < 196 && pvq[it] > 0.f) ? g : 0.f;
-  }
-  for (int i = threadIdx.x; i < 32 * 32; i += 512) {  // 32 x 32 zero-padded image
-    const int r = (i >> 5) - 2, cc = (i & 31) - 2;
-    img[i >> 5][i & 31] = (r >= 0 && r < 28 && cc >= 0 && cc < 28) ? x[(long long)n * 784 + r * 28 + cc] : 0.f;
   }
   __syncthreads();
   float acc[25];
@@ -253,8 +267,15 @@ __global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restric
     }
     __syncthreads();
   }
-  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
-  float* parts = scratch + 16;
+  // Two-level sum in a fixed order.  Level 1: the last block of every group of `gsz` images adds the group's partials
+  // (all of a thread's loads in flight at once); level 2: the last group to finish adds the <= 15 group sums.  One
+  // block summing all B partials needed four dependent rounds of loads (~4 us at the tail of the step).
+  unsigned* counters = reinterpret_cast<unsigned*>(scratch);  // [0] launch-wide, [1 + g] group g
+  float* parts = scratch + 16;                                  // [B][832]
+  float4* gparts4 = reinterpret_cast<float4*>(parts + (size_t)gridDim.x * 832);  // [ngroups][208]
+  const int ngroups = ((int)gridDim.x + gsz - 1) / gsz;
+  const int grpi = (int)blockIdx.x / gsz, g_first = grpi * gsz;
+  const int g_n = min(gsz, (int)gridDim.x - g_first);
   for (int i = threadIdx.x; i < 832; i += 512) {
     const int t = i >> 5, cc = i & 31;
     float s = 0.f;
@@ -262,37 +283,35 @@ __global__ void __launch_bounds__(512) conv1_wgrad_kernel(const float* __restric
     for (int g4 = 0; g4 < 4; ++g4) s += red[g4][t][cc];
     __stcg(parts + (size_t)blockIdx.x * 832 + i, s);
   }
-  if (!last_block_arrives(counter, gridDim.x)) return;
-  // final sum over the images' partials: 208 float4 outputs x 2 interleaved groups of images, each summed in image
-  // order with 16 loads in flight, then the group sums are added in group order
-  float4* red4 = reinterpret_cast<float4*>(&red[0][0][0]);  // [4][208] (groups 2, 3 stay zero)
-  const int o4 = threadIdx.x % 208, grp4 = threadIdx.x / 208;
-  if (threadIdx.x < 416) red4[(grp4 + 2) * 208 + o4] = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (grp4 < 2) {
-    const float4* p4 = reinterpret_cast<const float4*>(parts) + o4;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    int bk = grp4;
-    for (; bk + 30 < (int)gridDim.x; bk += 32) {
-      float4 v[16];
+  if (!last_block_arrives(counters + 1 + grpi, (unsigned)g_n)) return;
+  float4* red4 = reinterpret_cast<float4*>(&red[0][0][0]);  // [2][208]
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (threadIdx.x < 416) {  // 208 float4 outputs x 2 interleaved halves of the group
+    const int o4 = threadIdx.x % 208, half = threadIdx.x / 208;
+    const float4* p4 = reinterpret_cast<const float4*>(parts) + (size_t)g_first * 208 + o4;
+    float4 s = zero4;
+    for (int bk = half; bk < g_n; bk += 16) {
+      float4 v[8];
 #pragma unroll
-      for (int u = 0; u < 16; ++u) v[u] = __ldcg(p4 + (size_t)(bk + 2 * u) * 208);
+      for (int u = 0; u < 8; ++u) v[u] = (bk + 2 * u < g_n) ? __ldcg(p4 + (size_t)(bk + 2 * u) * 208) : zero4;
 #pragma unroll
-      for (int u = 0; u < 16; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+      for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
     }
-    for (; bk < (int)gridDim.x; bk += 2) {
-      const float4 v = __ldcg(p4 + (size_t)bk * 208);
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-    }
-    red4[grp4 * 208 + o4] = s;
+    red4[half * 208 + o4] = s;
   }
   __syncthreads();
   if (threadIdx.x < 208) {
-    float4 s = red4[threadIdx.x];
+    const float4 a = red4[threadIdx.x], b = red4[208 + threadIdx.x];
+    __stcg(gparts4 + (size_t)grpi * 208 + threadIdx.x, make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w));
+  }
+  if (!last_block_arrives(counters, (unsigned)ngroups)) return;
+  if (threadIdx.x < 208) {
+    float4 v[15];
 #pragma unroll
-    for (int g4 = 1; g4 < 4; ++g4) {
-      const float4 v = red4[g4 * 208 + threadIdx.x];
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-    }
+    for (int g = 0; g < 15; ++g) v[g] = g < ngroups ? __ldcg(gparts4 + (size_t)g * 208 + threadIdx.x) : zero4;
+    float4 s = zero4;
+#pragma unroll
+    for (int g = 0; g < 15; ++g) { s.x += v[g].x; s.y += v[g].y; s.z += v[g].z; s.w += v[g].w; }
     const int i = threadIdx.x * 4;
     if (i < 800) *reinterpret_cast<float4*>(dw + i) = s;
     else *reinterpret_cast<float4*>(db + (i - 800)) = s;
@@ -743,7 +762,8 @@ extern "C" int tfd_conv1_fwd(int dtype, const float* x, const float* w, const fl
   return 0;
 }
 
-extern "C" long long tfd_conv1_wgrad_scratch_floats(int B) { return 16 + (long long)B * 832; }
+// 16 counter words, one [26][32] partial per image, up to 15 group sums
+extern "C" long long tfd_conv1_wgrad_scratch_floats(int B) { return 16 + (long long)B * 832 + 15 * 832; }
 extern "C" long long tfd_pool2_bwd_scratch_floats(int B) { return 16 + (((long long)B * 49 + 15) / 16) * 64; }
 
 extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, int nsplit, long long split_stride,
@@ -752,15 +772,16 @@ extern "C" int tfd_conv1_wgrad(int dtype, const float* x, const float* dpool, in
   TFD_ACT_CHECK("conv1_wgrad");
   TFD_REQUIRE(scratch != nullptr && nsplit >= 1 && nsplit <= 2, "conv1_wgrad: scratch missing or nsplit %d not 1 or 2", nsplit);
   const dim3 grid(B);
+  const int gsz = B <= 240 ? 16 : (B + 14) / 15;  // images per first-level group of the final sum (at most 15 groups)
   // runs next to the conv2 wgrad CTAs (one per SM, ~194 KB of shared memory): ask for the same carve-out
   tfd_prefer_max_carveout(reinterpret_cast<const void*>(conv1_wgrad_kernel<float>));
   tfd_prefer_max_carveout(reinterpret_cast<const void*>(conv1_wgrad_kernel<bf16>));
   if (dtype == TFD_DTYPE_TF32)
     TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<float>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
-                              (const float*)pool_out, argmax, dw, db, scratch, B));
+                              (const float*)pool_out, argmax, dw, db, scratch, B, gsz));
   else
     TFD_CUDA_CHECK(tfd_launch(conv1_wgrad_kernel<bf16>, grid, dim3(512), 0, ST(stream), x, dpool, nsplit, split_stride,
-                              (const bf16*)pool_out, argmax, dw, db, scratch, B));
+                              (const bf16*)pool_out, argmax, dw, db, scratch, B, gsz));
   TFD_LAUNCH_CHECK();
   return 0;
 }
