@@ -366,6 +366,7 @@ class GpuClusterEngine(NativeEngine):
         self._arrive = [self._ctrl_ptr(s, CTRL_ARRIVE) for s in range(S)]
         # per direct variable: shard pieces in row order
         self._direct_info = {}
+        self._wg_stage, self._push_branches, self._push_used = {}, [], 0
         self._prefetch = []
         for name in self.direct:
             pcs = sorted(self.placement.pieces[name], key=lambda q: q.row_start)
@@ -379,7 +380,7 @@ class GpuClusterEngine(NativeEngine):
             self._direct_info[name] = {
                 "rows": [q.row_start for q in pcs] + [pcs[-1].row_end], "cols": pcs[0].cols, "ld": ld,
                 "shadow": [self._tc_ptr(q.shard, name) for q in pcs],
-                "slot": [self._slot_ptr(q.shard, q.offset) for q in pcs],
+                "slot": [self._slot_ptr(q.shard, q.offset) for q in pcs], "shard": [q.shard for q in pcs],
                 "ver": None if (self.async_mode or self.backup) else [ver_of(q.shard) for q in pcs]}
 
     def _build_pub(self):
@@ -469,10 +470,39 @@ class GpuClusterEngine(NativeEngine):
             return super().gemm_wgrad(wname, X, dY, Bsz, bn=bn)
         d = self._direct_info[wname]
         nseg = len(d["slot"])
+        out_ptrs, copies = d["slot"], []
+        if self.v2 and os.environ.get("TFD_PUSH", "ce") == "ce":
+            # Strict sync: the GEMM stores only MY shard's rows straight into their slot; the other shards' rows go
+            # into a local staging matrix and from there to their owners by copy engine, one branch per owner, under
+            # the conv backward kernels.  Stored from the epilogue over NVLink they kept the GEMM's CTAs resident
+            # 6-10 us longer (2-8 GPUs) and slowed the kernels that share its SMs -- fc1 dgrad, pool2 backward and the
+            # head -- by as much, on the critical path.
+            st = self._wg_stage.get(wname)
+            if st is None:
+                st = self._wg_stage[wname] = torch.empty(d["rows"][-1], d["cols"], dtype=torch.float32,
+                                                         device=self.device)
+            mine = self.my_shard if self.is_ps else -1
+            out_ptrs = []
+            for i in range(nseg):
+                if d["shard"][i] == mine:
+                    out_ptrs.append(d["slot"][i])
+                else:
+                    sp = st.data_ptr() + 4 * d["rows"][i] * d["cols"]
+                    out_ptrs.append(sp)
+                    copies.append((d["slot"][i], sp, 4 * (d["rows"][i + 1] - d["rows"][i]) * d["cols"]))
         nat.gemm_bf16_seg(X, 1, [dY.data_ptr()] + [0] * (nseg - 1), 1, d["rows"][-1], d["cols"], Bsz, None,
                           mode=nat.EPI_STORE_BF16 if self.grad_dtype == "bf16" else nat.EPI_STORE_F32, lda=X.stride(0),
                           ldb=dY.stride(0), ld_out=d["cols"], seg_mode=nat.SEG_OUT_M, seg_rows=d["rows"],
-                          out_ptrs=d["slot"], bn=bn, tf32=self.tf32)
+                          out_ptrs=out_ptrs, bn=bn, tf32=self.tf32)
+        if copies:
+            done = torch.cuda.current_stream().record_event()
+            while len(self._push_branches) < len(copies):
+                self._push_branches.append(torch.cuda.Stream(device=self.device))
+            for br, (dst, src, nbytes) in zip(self._push_branches, copies):
+                br.wait_event(done)
+                with torch.cuda.stream(br):
+                    nat.memcpy_async(dst, src, nbytes)
+            self._push_used = max(self._push_used, len(copies))
 
     # ---- step pieces -----------------------------------------------------------------------
     def conv1_fwd(self, ws, training: bool = True) -> None:
@@ -581,6 +611,10 @@ class GpuClusterEngine(NativeEngine):
         kernels have already written the slots; a colocated rank signals from inside its Adam kernel, a worker on a
         GPU without a shard with one tiny block."""
         if self.v2:
+            main = torch.cuda.current_stream()
+            for br in self._push_branches[:self._push_used]:  # copy-engine pushes of the big gradients
+                main.wait_stream(br)
+            self._push_used = 0
             if not self.is_ps:
                 nat.signal_arrive(self._arrive, self.ctrl[WCTRL_STEP:])
             return
