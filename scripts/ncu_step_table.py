@@ -23,6 +23,8 @@ WORK = {
     "conv1_fwd_kernel": (B * 784 * 4 + B * 196 * 32 * 5, B * 784 * 4 + B * 196 * 32 * 3, 0, 2 * B * 784 * 32 * 25),
     "conv2_tc_kernel<1": (B * 196 * 32 * 4 + 204800 + B * 49 * 64 * 5, B * 196 * 32 * 2 + 102400 + B * 49 * 64 * 3, 2 * B * 196 * 64 * 800, 0),
     "conv2_tc_kernel<0": (B * 196 * 64 * 4 + 204800 + 2 * B * 196 * 32 * 4, B * 196 * 64 * 2 + 102400 + B * 196 * 32 * 4, 2 * B * 196 * 64 * 800, 0),
+    "conv2_box_kernel<1": (B * 196 * 32 * 4 + 204800 + B * 49 * 64 * 5, B * 196 * 32 * 2 + 102400 + B * 49 * 64 * 3, 2 * B * 196 * 64 * 800, 0),
+    "conv2_box_kernel<0": (B * 196 * 64 * 4 + 204800 + 2 * B * 196 * 32 * 4, B * 196 * 64 * 2 + 102400 + B * 196 * 32 * 4, 2 * B * 196 * 64 * 800, 0),
     "conv2_wgrad_tc_kernel": (B * 196 * 96 * 4 + 204800, B * 196 * 96 * 2 + 204800, 2 * B * 196 * 64 * 800, 0),
     "gemm_tc_kernel<0, 1": (3136 * 1024 * 4 + B * 3136 * 4 + 8 * B * 1024 * 4, 3136 * 1024 * 2 + B * 3136 * 2 + 8 * B * 1024 * 4, 2 * B * 1024 * 3136, 0),
     "gemm_tc_kernel<0, 0": (3136 * 1024 * 4 + B * 1024 * 4 + 3 * B * 3136 * 4, 3136 * 1024 * 2 + B * 1024 * 2 + 3 * B * 3136 * 4, 2 * B * 1024 * 3136, 0),
@@ -73,6 +75,9 @@ def table(path, arm):
 
 
 print("# ncu --set full of one CNN training step (B = 128, 1 GPU, round 2 final kernels)\n")
+print("Capture dates: tf32 arm after the one-box conv2 kernels, the Adam fence changes and the dgrad-first capture order, but BEFORE the\n"
+      "conv1-wgrad rewrite (conflict-free image rows + two-level final sum: 24.2 -> 16.7 us in the step graph, `profiles/step_timeline.md`);\n"
+      "bf16 arm one change set earlier (five-box conv2 forward, one-box dgrad not yet default).  The GPU budget of the round ended before a re-capture.\n")
 print("Captured with `ncu --set full --clock-control none --import-source on -s 60 -c 12 python bench.py --steps 2 ...` after the same\n"
       "command had exited 0 without ncu.  ncu serialises the kernels and starts each one on cold caches, so durations are\n"
       "30-60 %% above the in-graph durations of `profiles/step_timeline.md`; the columns to read are the shares and the\n"

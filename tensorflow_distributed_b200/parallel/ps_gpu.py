@@ -471,7 +471,7 @@ class GpuClusterEngine(NativeEngine):
         d = self._direct_info[wname]
         nseg = len(d["slot"])
         out_ptrs, copies = d["slot"], []
-        if self.v2 and os.environ.get("TFD_PUSH", "ce") == "ce":
+        if self._use_ce("TFD_PUSH", len([x for x in d["shard"] if not (self.is_ps and x == self.my_shard)])):
             # Strict sync: the GEMM stores only MY shard's rows straight into their slot; the other shards' rows go
             # into a local staging matrix and from there to their owners by copy engine, one branch per owner, under
             # the conv backward kernels.  Stored from the epilogue over NVLink they kept the GEMM's CTAs resident
@@ -566,7 +566,7 @@ class GpuClusterEngine(NativeEngine):
             elif self.async_mode:
                 nat.pull_multi_async([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p],
                                      [self.ctrl.data_ptr() + 4 * (WCTRL_MYTICKET + s[4]) for s in p])
-            elif self.v2 and os.environ.get("TFD_PREFETCH", "ce") == "ce":
+            elif self._use_ce("TFD_PREFETCH", len([s for s in p if not (self.is_ps and s[4] == self.my_shard)])):
                 # strict sync: a one-block gate on the LOCAL version words of the owner shards, then one copy-engine
                 # transfer per remote shard piece, each on its own graph branch (a peer copy takes ~7 us to start; in
                 # one stream seven of them would queue up).  A copy kernel lost its SMs to conv2 (one CTA per SM) and
@@ -591,6 +591,20 @@ class GpuClusterEngine(NativeEngine):
                 nat.pull_multi([s[0] for s in p], [s[1] for s in p], [s[2] for s in p], [s[3] for s in p], 0,
                                want_ptr=self.step_ptr())
         self._pf_pending = True
+
+    def _use_ce(self, env: str, n_remote: int) -> bool:
+        """Copy engines instead of SM kernels / epilogue stores for the big-matrix prefetch (env TFD_PREFETCH) and
+        gradient push (TFD_PUSH) of strict-sync mode: `ce`, `kernel`, or `auto` (default).  Measured: with ONE remote
+        piece per matrix (2 colocated GPUs) the copy-engine paths are faster; with
+        seven (8 GPUs) the memcpy nodes of one GPU queue behind each other (~5 us start latency each) and the step got
+        30 us SLOWER than with the kernel paths, so `auto` uses the copy engines only in the measured-good case: a
+        colocated rank with exactly one remote piece."""
+        if not self.v2:
+            return False
+        mode = os.environ.get(env, "auto")
+        if mode in ("ce", "kernel"):
+            return mode == "ce"
+        return self.is_ps and self.is_worker and n_remote == 1
 
     def _issue_local_prefetch(self) -> None:
         for src, dst, n, _ver, _shard in self._pf_local:
