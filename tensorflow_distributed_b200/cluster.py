@@ -155,3 +155,10 @@ def effective_replicas_to_aggregate(flags: Flags, num_workers: int) -> int:
 def device_filters(flags: Flags) -> List[str]:
     """A worker only sees the ps job and itself (m:258)."""
     return ["/job:ps", "/job:worker/task:%d" % flags.task_index]
+
+
+def filter_allows(filters: List[str], job: str, task_index: int) -> bool:
+    """tf.ConfigProto(device_filters=...) semantics: a remote task is visible when one filter is a prefix of its name
+    ('/job:ps' admits every ps task, '/job:worker/task:1' only that worker)."""
+    name = "/job:%s/task:%d" % (job, task_index)
+    return any(name == f or name.startswith(f + "/") for f in filters)

@@ -151,18 +151,28 @@ class PSServer:
 class PSClient:
     """Worker-side handle on all ps shards."""
 
-    def __init__(self, cluster: ClusterSpec, spec: ModelSpec, placement: Placement, task_index: int):
+    def __init__(self, cluster: ClusterSpec, spec: ModelSpec, placement: Placement, task_index: int,
+                 device_filters: Optional[List[str]] = None):
         self.cluster, self.spec, self.placement, self.task = cluster, spec, placement, task_index
         self.S = placement.num_shards
         self._arenas = [torch.zeros(n) for n in placement.shard_sizes]
+        # the session's device filters (m:258): every peer this client talks to is resolved through peer_rank, which
+        # refuses a task outside the filters -- a worker cannot address another worker
+        self.device_filters = device_filters
+
+    def peer_rank(self, job: str, task_index: int) -> int:
+        from ..cluster import filter_allows
+        if self.device_filters is not None and not filter_allows(self.device_filters, job, task_index):
+            raise PermissionError("/job:%s/task:%d is outside this session's device filters %s"
+                                  % (job, task_index, self.device_filters))
+        return self.cluster.rank_of(job, task_index)
 
     def _hdr(self, shard: int, op: int, local_step: int = 0, aux: int = 0) -> None:
-        dist.send(torch.tensor([op, self.task, local_step, aux], dtype=torch.int64),
-                  dst=self.cluster.rank_of("ps", shard))
+        dist.send(torch.tensor([op, self.task, local_step, aux], dtype=torch.int64), dst=self.peer_rank("ps", shard))
 
     def _recv_i64(self, shard: int, n: int = 1) -> List[int]:
         t = torch.zeros(n, dtype=torch.int64)
-        dist.recv(t, src=self.cluster.rank_of("ps", shard))
+        dist.recv(t, src=self.peer_rank("ps", shard))
         return [int(v) for v in t]
 
     # X1
@@ -173,7 +183,7 @@ class PSClient:
         for s in range(self.S):
             self._hdr(s, OP_PULL)
             self._recv_i64(s)
-            dist.recv(self._arenas[s], src=self.cluster.rank_of("ps", s))
+            dist.recv(self._arenas[s], src=self.peer_rank("ps", s))
         return self.placement.gather(self._arenas)
 
     # X2 / X3
@@ -183,7 +193,7 @@ class PSClient:
         steps = []
         for s in range(self.S):
             self._hdr(s, OP_PUSH, local_step)
-            dist.send(flat[s], dst=self.cluster.rank_of("ps", s))
+            dist.send(flat[s], dst=self.peer_rank("ps", s))
             if not sync:
                 steps.append(self._recv_i64(s)[0])
         return None if sync else steps[self.placement.global_step_shard]
@@ -206,7 +216,7 @@ class PSClient:
         self.placement.scatter(params, flat)
         for s in range(self.S):
             self._hdr(s, OP_INIT)
-            dist.send(flat[s], dst=self.cluster.rank_of("ps", s))
+            dist.send(flat[s], dst=self.peer_rank("ps", s))
 
     def init_tokens(self, num_tokens: int) -> None:
         self._hdr(self.placement.global_step_shard, OP_INIT_TOKENS, aux=num_tokens)
@@ -232,7 +242,7 @@ class PSClient:
             meta.append(self._recv_i64(s, 2))
             trio = [torch.zeros(self.placement.shard_sizes[s]) for _ in range(3)]
             for t in trio:
-                dist.recv(t, src=self.cluster.rank_of("ps", s))
+                dist.recv(t, src=self.peer_rank("ps", s))
             arenas.append(trio[0]); ms.append(trio[1]); vs.append(trio[2])
         g = self.placement.global_step_shard
         return {"global_step": meta[g][0], "t": meta[g][1], "params": self.placement.gather(arenas),
@@ -246,9 +256,9 @@ class PSClient:
             trios.append(flat)
         for s in range(self.S):
             self._hdr(s, OP_SET_STATE)
-            dist.send(torch.tensor([global_step, t], dtype=torch.int64), dst=self.cluster.rank_of("ps", s))
+            dist.send(torch.tensor([global_step, t], dtype=torch.int64), dst=self.peer_rank("ps", s))
             for k in range(3):
-                dist.send(trios[k][s], dst=self.cluster.rank_of("ps", s))
+                dist.send(trios[k][s], dst=self.peer_rank("ps", s))
 
     def done(self) -> None:
         for s in range(self.S):

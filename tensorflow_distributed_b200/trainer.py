@@ -176,7 +176,7 @@ def _run_cpu_cluster_task(flags: Flags, cluster: cl.ClusterSpec, mnist, log) -> 
                            if torch.cuda.is_available() else "cpu")
         # per-worker dropout stream
         eng._gen.manual_seed(flags.seed + 7919 + 31 * flags.task_index)
-    client = ps_cpu.PSClient(cluster, spec, placement, flags.task_index)
+    client = ps_cpu.PSClient(cluster, spec, placement, flags.task_index, device_filters=cl.device_filters(flags))
     sv = Supervisor(is_chief, spec, flags.train_dir, recovery_wait_secs=1.0, log=log)
 
     if is_chief:

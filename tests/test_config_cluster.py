@@ -71,6 +71,25 @@ def test_chief_and_devices():
     assert c.all_gpu and cl.worker_device(g, c) == "/job:worker/task:1/gpu:2"
     assert cl.torch_device_of("/job:worker/task:1/gpu:2") == "cuda:2"
     assert cl.device_filters(g) == ["/job:ps", "/job:worker/task:1"]
+    f = cl.device_filters(g)
+    assert cl.filter_allows(f, "ps", 0) and cl.filter_allows(f, "ps", 3) and cl.filter_allows(f, "worker", 1)
+    assert not cl.filter_allows(f, "worker", 0) and not cl.filter_allows(f, "worker", 10)
+
+
+def test_ps_client_refuses_a_peer_outside_its_device_filters():
+    """m:258: a worker's session sees the ps job and itself.  The CPU transport resolves every peer through the
+    filters, so a client cannot address another worker."""
+    from tensorflow_distributed_b200.models.spec import mlp_spec
+    from tensorflow_distributed_b200.parallel.placement import Placement
+    from tensorflow_distributed_b200.parallel.ps_cpu import PSClient
+    g = Flags(job_name="worker", task_index=1, ps_hosts="h:1,h:2", worker_hosts="h:3,h:4")
+    c = cl.ClusterSpec.from_flags(g)
+    spec = mlp_spec(16, 1)
+    client = PSClient(c, spec, Placement(spec, 2), 1, device_filters=cl.device_filters(g))
+    assert client.peer_rank("ps", 0) == c.rank_of("ps", 0) and client.peer_rank("ps", 1) == c.rank_of("ps", 1)
+    assert client.peer_rank("worker", 1) == c.rank_of("worker", 1)
+    with pytest.raises(PermissionError):
+        client.peer_rank("worker", 0)
 
 
 def test_replicas_to_aggregate_documented_default():
