@@ -242,6 +242,7 @@ __global__ void __launch_bounds__(256) adam_apply_kernel(AdamArgs a, const __gri
     const unsigned done = atomicAdd(&a.t_counter[1], 1u);
     s_last = (done == gridDim.x - 1) ? 1u : 0u;
     if (s_last) {
+      __threadfence();  // acquire side of the counter: the other blocks' fenced stores are ordered before what follows
       g_adam_stamps[4] = globaltimer_ns();
       a.t_counter[1] = 0;
       a.t_counter[0] = t;
