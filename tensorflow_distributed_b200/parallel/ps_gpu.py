@@ -471,7 +471,11 @@ class GpuClusterEngine(NativeEngine):
         d = self._direct_info[wname]
         nseg = len(d["slot"])
         out_ptrs, copies = d["slot"], []
-        if self._use_ce("TFD_PUSH", len([x for x in d["shard"] if not (self.is_ps and x == self.my_shard)])):
+        # (`auto`: only for the few-MB matrices that are also prefetched -- the CNN's wd1, the measured case; the
+        # epilogue push of an 8192 x 8192 MLP layer already runs at 0.93 of the NVLink roofline inside the GEMM)
+        forced = os.environ.get("TFD_PUSH", "auto") == "ce"
+        if (forced or wname in self.prefetched) and self._use_ce(
+                "TFD_PUSH", len([x for x in d["shard"] if not (self.is_ps and x == self.my_shard)])):
             # Strict sync: the GEMM stores only MY shard's rows straight into their slot; the other shards' rows go
             # into a local staging matrix and from there to their owners by copy engine, one branch per owner, under
             # the conv backward kernels.  Stored from the epilogue over NVLink they kept the GEMM's CTAs resident
